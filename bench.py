@@ -1,0 +1,380 @@
+#!/usr/bin/env python
+"""bench.py — image pairs matched/s and G descriptor-comparisons/s of the pairwise matching stage.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload c3|c5|c1] [--mode knn2_ratio|crosscheck] [--variant auto|popc|popc_csa|tensor]
+
+One step = one pass of the hot path over the whole pair list of the workload (default C3:
+synthetic 21 images x 50 000 ORB descriptors, all 210 pairs, kNN k=2 + ratio test — the
+configuration BASELINE.json quotes its metric and its >=100x target on).  Prints ONE JSON line.
+
+  value     pairs/s with the descriptor bank already resident in HBM (CUDA events, max over ranks)
+  e2e       the same through the public API with HOST buffers: pinned host bank -> device (+ NCCL
+            broadcast at N>1), match, survivors gathered and copied back to the host, every step
+  roofline  dominant kernel against the integer-pipe roofline of SURVEY.md §8(d) plus HBM GB/s
+  cpu_baseline  cv2.BFMatcher (the reference's own CPU call) on a bounded sample, rank 0, N=1
+
+--impl reference times the reference's CPU implementation of the path (cv2.BFMatcher with all
+host threads, custom_bruteforce_matcher.py:160-172 / :193-199) on a bounded sample per step.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "c3": dict(n_images=21, n_desc=50_000, seed=0,
+               name="synthetic 21 images x 50k ORB 256-bit descriptors, all 210 pairs"),
+    "c5": dict(n_images=200, n_desc=20_000, seed=1,
+               name="synthetic 200-image sweep x 20k descriptors, 19900 pairs"),
+    "c1": dict(n_images=21, n_desc=1_000, seed=0,
+               name="synthetic stand-in for example_01b: 21 images x 1000 descriptors, 210 pairs"),
+}
+POPC_PER_COMPARISON = 8          # algorithmic: 8 x (32-bit XOR + POPC) per 256-bit distance
+BYTES_PER_ROW = 32
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=list(WORKLOADS))
+    ap.add_argument("--mode", default="knn2_ratio", choices=["knn2_ratio", "crosscheck"])
+    ap.add_argument("--variant", default="auto")
+    ap.add_argument("--cpu-sample-pairs", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ---- clocks during the timed region -------------------------------------------------------------
+class ClockSampler:
+    """Samples SM clock / throttle reasons of one GPU every 100 ms through NVML."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap", 0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index=0):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                get = getattr(self.nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                    self.nv.nvmlDeviceGetCurrentClocksThrottleReasons
+                mask = get(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thread:
+            self._thread.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                    "note": "NVML unavailable"}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ---- CPU reference arm ----------------------------------------------------------------------------
+def cv_match_pair(cv, q, t, mode):
+    """The reference's own CPU call for one pair; returns the number of surviving matches."""
+    if mode == "crosscheck":
+        return len(cv.BFMatcher(cv.NORM_HAMMING, crossCheck=True).match(cv.UMat(q), cv.UMat(t)))
+    good = 0
+    for m, n in cv.BFMatcher(cv.NORM_HAMMING).knnMatch(q, t, k=2):
+        if m.distance < 0.75 * n.distance:
+            good += 1
+    return good
+
+
+def cpu_sample(sets, pairs, mode, n_sample):
+    import cv2 as cv
+    cv.setNumThreads(os.cpu_count() or 1)
+    n_sample = max(1, min(n_sample, len(pairs)))
+    stride = max(1, len(pairs) // n_sample)
+    sample = [pairs[i * stride] for i in range(n_sample)]
+    t0 = time.perf_counter()
+    cmps = 0
+    for a, b in sample:
+        cv_match_pair(cv, sets[a], sets[b], mode)
+        cmps += sets[a].shape[0] * sets[b].shape[0]
+    dt = time.perf_counter() - t0
+    return {"pairs": len(sample), "seconds": dt, "pairs_per_s": len(sample) / dt, "gcmp_per_s": cmps / dt / 1e9,
+            "cores": cv.getNumThreads(), "cv2": cv.__version__}
+
+
+def run_reference(args, wl, sets, pairs):
+    """--impl reference: cv2.BFMatcher on a bounded sample per step (one pair per step)."""
+    import cv2 as cv
+    cv.setNumThreads(os.cpu_count() or 1)
+    rng = np.random.default_rng(0)
+    order = rng.permutation(len(pairs))
+    per_step = 1
+    k = 0
+
+    def step():
+        nonlocal k
+        cmps = 0
+        for _ in range(per_step):
+            a, b = pairs[order[k % len(pairs)]]
+            k += 1
+            cv_match_pair(cv, sets[a], sets[b], args.mode)
+            cmps += sets[a].shape[0] * sets[b].shape[0]
+        return cmps
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    cmps = sum(step() for _ in range(args.steps))
+    dt = time.perf_counter() - t0
+    value = args.steps * per_step / dt
+    sample = (f"cv2 {cv.__version__} BFMatcher {'crossCheck match' if args.mode == 'crosscheck' else 'knnMatch(k=2)+ratio 0.75'}, "
+              f"{per_step} of {len(pairs)} pairs per step, {cv.getNumThreads()} threads")
+    return {
+        "impl": "reference", "metric": "image_pairs_matched_per_sec", "value": value, "unit": "pairs/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 popcount", "data": "synthetic",
+        "config": {"workload": wl["name"], "mode": args.mode, "pairs": len(pairs)},
+        "gcmp_per_s": cmps / dt / 1e9,
+        "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": cv.getNumThreads(), "kind": "reference",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+# ---- our arm --------------------------------------------------------------------------------------
+def popc_peak_per_clk_per_sm():
+    """POPC issue rate measured on this pool's B200 by tools/pipe_microbench (committed summary),
+    else the CUDA programming-guide planning figure."""
+    path = os.path.join(ROOT, "profiles", "pipe_microbench_r01.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["popc"]), "measured (profiles/pipe_microbench_r01.json)"
+    except Exception:
+        return 16.0, "planning figure (CUDA programming guide, 16 POPC/clk/SM)"
+
+
+def measured_hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_ours(args, wl, sets, pairs):
+    import torch
+    import ssp_b200
+    from ssp_b200.distributed import shard_pairs, broadcast_descriptor_bank, gather_matches
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+
+    eng = ssp_b200.Engine(local_rank)
+    stream = torch.cuda.current_stream(dev)
+    eng.set_stream(stream.cuda_stream)
+
+    # host-side bank in pinned memory (rank 0 owns the input, like the reference's single process)
+    bank = offs = pinned = None
+    if rank == 0:
+        bank_np, offs = ssp_b200.Engine.pack_descriptors(sets)
+        pinned = torch.from_numpy(bank_np).pin_memory()
+        bank = pinned.numpy()
+    bank_bytes = int(sum(s.shape[0] for s in sets)) * BYTES_PER_ROW
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- resident bank for the `value` leg ----------------------------------------------------
+    if world > 1:
+        bank_t, offs_all = broadcast_descriptor_bank(bank, offs, 0)
+    else:
+        bank_t, offs_all = pinned.to(dev), offs
+    eng.bind_descriptor_bank(bank_t.data_ptr(), offs_all, keepalive=bank_t)
+    local_pairs, local_pos = shard_pairs(pairs, rank, world)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step_resident():
+        flush.zero_()
+        return eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant, fetch=False)
+
+    kernel_ms, launches = [], 0
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    with ClockSampler(local_rank) as clocks:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(args.steps):
+            res = step_resident()
+            st = eng.hamming_last_stats()
+            kernel_ms.append(st["main_kernel_ms"])
+            launches += st["launches"]
+        ev1.record(stream)
+        barrier()
+    elapsed_ms = ev0.elapsed_time(ev1)
+    comparisons_local = eng.hamming_last_stats()["comparisons"]
+    n_matches_local = int(res.offsets[-1])
+    if dist is not None:
+        t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+        c = torch.tensor([comparisons_local, n_matches_local, launches], dtype=torch.int64, device=dev)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        comparisons, n_matches, launches = int(c[0]), int(c[1]), int(c[2])
+    else:
+        comparisons, n_matches = comparisons_local, n_matches_local
+    ms_per_step = elapsed_ms / args.steps
+    value = len(pairs) / (ms_per_step / 1e3)
+
+    # ---- e2e leg: host buffers in, host buffers out, every step -------------------------------
+    def step_e2e():
+        if world > 1:
+            b_t, o_all = broadcast_descriptor_bank(bank, offs, 0)       # H2D on rank 0 + NCCL broadcast
+            eng.bind_descriptor_bank(b_t.data_ptr(), o_all, keepalive=b_t)
+            local = eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant)  # D2H of survivors
+            return gather_matches(local, local_pos, len(pairs), dst=0)   # NCCL gather + D2H on rank 0
+        eng.upload_descriptor_bank(bank, offs)                           # pinned host -> device
+        return eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant)
+
+    e2e_steps = max(1, min(args.steps, 3))
+    step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        out = step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = len(pairs) * e2e_steps / e2e_s
+    d2h = (int(out.offsets[-1]) * 12 + (len(pairs) + 1) * 8) if rank == 0 else 0
+    if rank == 0:
+        assert int(out.offsets[-1]) == n_matches, "e2e and resident legs disagree on the survivor count"
+
+    # ---- roofline of the dominant kernel -------------------------------------------------------
+    info = eng.device_info()
+    clk = clocks.summary()
+    main_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
+    achieved = comparisons_local / (main_ms / 1e3) / 1e9 if main_ms > 0 else 0.0   # Gcmp/s, this rank
+    popc_rate, popc_src = popc_peak_per_clk_per_sm()
+    sm_max_mhz = clk.get("sm_max_mhz") or info["sm_clock_khz"] / 1e3
+    peak = info["sm_count"] * popc_rate * sm_max_mhz * 1e6 / POPC_PER_COMPARISON / 1e9
+    hbm_peak, hbm_src = measured_hbm_peak()
+    rows_q = sum(sets[a].shape[0] for a, _ in local_pairs)
+    rows_t = sum(sets[b].shape[0] for _, b in local_pairs)
+    algo_bytes = (rows_q + rows_t) * BYTES_PER_ROW + rows_q * 16    # each operand once + best-2 records
+    roofline = {
+        "bound": "int-pipe (POPC)", "kernel": "hamming_popc_kernel" if args.variant != "tensor" else "hamming_tensor_kernel",
+        "achieved": achieved, "peak": peak, "unit": "Gcmp/s", "frac": achieved / peak if peak else None,
+        "peak_definition": f"{info['sm_count']} SMs x {popc_rate:g} POPC/clk/SM [{popc_src}] x {sm_max_mhz:g} MHz / "
+                           f"{POPC_PER_COMPARISON} POPC per 256-bit comparison",
+        "frac_at_held_clock": (achieved / (peak * clk["sm_mhz"] / sm_max_mhz)) if clk.get("sm_mhz") else None,
+        "kernel_ms_per_launch": main_ms, "comparisons_per_launch": comparisons_local,
+        "traffic": None,
+        "hbm": {"achieved": algo_bytes / (main_ms / 1e3) / 1e9 if main_ms > 0 else None, "peak": hbm_peak,
+                "unit": "GB/s", "algorithmic_bytes_per_launch": algo_bytes, "peak_source": hbm_src,
+                "frac": (algo_bytes / (main_ms / 1e3) / 1e9) / hbm_peak if main_ms > 0 else None},
+    }
+
+    line = None
+    if rank == 0:
+        line = {
+            "metric": "image_pairs_matched_per_sec", "value": value, "unit": "pairs/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u32 popcount",
+            "data": "synthetic",
+            "config": {"workload": wl["name"], "mode": args.mode, "variant": args.variant, "pairs": len(pairs),
+                       "descriptors_per_image": wl["n_desc"], "sharding": f"pairs round-robin over {world} rank(s)",
+                       "l2": "256 MiB device memset between steps (inside the timed region) flushes the 126 MB L2"},
+            "gcmp_per_s": comparisons / (ms_per_step / 1e3) / 1e9,
+            "matches_per_step": n_matches,
+            "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": bank_bytes + len(pairs) * 8,
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                    "gcmp_per_s": comparisons * e2e_steps / e2e_s / 1e9},
+            "gpu_launches": launches,
+            "clocks": clk,
+            "roofline": roofline,
+        }
+    eng.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return line
+
+
+def main():
+    args = parse()
+    wl = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    if args.impl == "reference" and rank != 0:
+        return 0  # rank 0 alone runs the CPU arm
+    from ssp_b200 import synthetic as synth
+    # every rank generates the same seeded input (cheap next to shipping it); rank 0's copy is
+    # the "host input" of the e2e leg
+    sets = synth.descriptor_bank(wl["n_images"], wl["n_desc"], seed=wl["seed"])
+    pairs = synth.all_pairs(wl["n_images"])
+    if args.impl == "reference":
+        print(json.dumps(run_reference(args, wl, sets, pairs)), flush=True)
+        return 0
+    line = run_ours(args, wl, sets, pairs)
+    if rank == 0:
+        if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not args.no_cpu_baseline:
+            cpu = cpu_sample(sets, pairs, args.mode, args.cpu_sample_pairs)
+            line["cpu_baseline"] = {
+                "value": cpu["pairs_per_s"], "unit": "pairs/s", "cores": cpu["cores"], "kind": "reference",
+                "gcmp_per_s": cpu["gcmp_per_s"],
+                "sample": f"cv2 {cpu['cv2']} BFMatcher ({args.mode}) on {cpu['pairs']} of {len(pairs)} pairs "
+                          f"({cpu['seconds']:.1f} s), {cpu['cores']} threads; the reference's own CPU call"}
+        print(json.dumps(line), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

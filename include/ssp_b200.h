@@ -1,0 +1,203 @@
+/*
+ * ssp_b200.h — C ABI of the B200 pair-matching engine (libssp_b200.so).
+ *
+ * This is the drop-in boundary for the pairwise image-matching stage of
+ * joachim-broser/opencv-starry-sky-panorama-stitcher.  Every entry point names the reference
+ * interface it stands in for (paths relative to the reference checkout).  The reference is
+ * pure Python, so the binding a maintainer adds is a ctypes stub (INTEGRATION.md shows it).
+ *
+ * Conventions
+ *   - plain C: pointers, sizes, ints.  No torch / cv2 / C++ types cross this boundary.
+ *   - every function returns SSP_OK (0) or a negative SSP_ERR_* code; the message is
+ *     available from ssp_last_error().  No exceptions cross the ABI.
+ *   - `mem_kind` says whether a data pointer is host memory (SSP_MEM_HOST) or memory of the
+ *     context's CUDA device (SSP_MEM_DEVICE, e.g. torch.Tensor.data_ptr()).  Index/offset
+ *     arrays documented as "host" are always host memory.
+ *   - the caller owns every buffer it passes; inputs are read-only and copied (or, for
+ *     ssp_bind_descriptor_bank, referenced until the next upload/bind/destroy).
+ *   - a context is bound to one CUDA device and is not re-entrant: one host thread per
+ *     context (the reference is single-threaded, custom_bruteforce_matcher.py:615-620).
+ *   - there is no CPU fallback: if no CUDA device is usable ssp_create fails.
+ */
+#ifndef SSP_B200_H
+#define SSP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSP_ABI_VERSION 1
+
+/* status codes */
+#define SSP_OK 0
+#define SSP_ERR_INVALID (-1)  /* bad argument (null pointer, out-of-range index, misaligned buffer) */
+#define SSP_ERR_CUDA (-2)     /* a CUDA runtime call or kernel failed */
+#define SSP_ERR_STATE (-3)    /* call order violated (e.g. match before bank upload) */
+#define SSP_ERR_CAPACITY (-4) /* caller buffer too small */
+#define SSP_ERR_DOMAIN (-5)   /* a polygon hit the reference's math.acos domain error (cbpm:134) */
+
+/* mem_kind */
+#define SSP_MEM_HOST 0
+#define SSP_MEM_DEVICE 1
+
+/* Hamming match mode */
+#define SSP_MODE_KNN2_RATIO 0 /* custom_bruteforce_matcher.py:160-172  knnMatch(k=2) + Lowe ratio  */
+#define SSP_MODE_CROSSCHECK 1 /* custom_bruteforce_matcher.py:193-199  BFMatcher(crossCheck=True)   */
+
+/* Hamming kernel variant */
+#define SSP_HAMMING_AUTO 0
+#define SSP_HAMMING_POPC 1     /* LOP3 + POPC CUDA-core kernel, TMA-bulk staged train tiles         */
+#define SSP_HAMMING_POPC_CSA 2 /* same, carry-save-adder compression before POPC (4 POPC/compare)   */
+#define SSP_HAMMING_TENSOR 3   /* tcgen05 kind::i8 contraction on 0/1-expanded descriptors          */
+
+/* polygon compare options */
+#define SSP_SHIFT_CANONICAL 0       /* parity mode: reference compares shift 0 only (cbpm:992-1016) */
+#define SSP_SHIFT_MIN_OVER_SHIFTS 1 /* non-parity: minimum over the 5 cyclic vertex shifts          */
+#define SSP_PRECISION_FP64 0        /* parity mode: bit-exact numpy float64 evaluation order         */
+#define SSP_PRECISION_FP32 1        /* non-parity fast mode                                          */
+
+/* per-candidate status written by ssp_polygon_measure */
+#define SSP_POLY_VALID 0
+#define SSP_POLY_SHORT_SIDE 1 /* some pixel distance < min_side_px (cbpm:515)        */
+#define SSP_POLY_NOT_CONVEX 2 /* not all 5 stars are hull vertices (cbpm:520-526)    */
+#define SSP_POLY_DOMAIN 3     /* |acos argument| > 1 (cbpm:134 raises ValueError)    */
+#define SSP_POLY_BAD_INDEX 4  /* a star index is outside the image's star table        */
+
+typedef struct ssp_ctx ssp_ctx;
+
+/* ---- lifetime ------------------------------------------------------------------------ */
+
+/* Creates an engine context on CUDA device `device`.  One per CustomBruteForceMatcher instance
+ * (it replaces the per-matcher state custom_bruteforce_matcher.py:57-59 keeps). */
+int ssp_create(ssp_ctx** ctx, int device);
+int ssp_destroy(ssp_ctx* ctx);
+/* Last error message of `ctx` (or of the last failed ssp_create when ctx == NULL). */
+const char* ssp_last_error(const ssp_ctx* ctx);
+int ssp_abi_version(void);
+/* Run all subsequent work on `cuda_stream` (a cudaStream_t, e.g. torch's current stream
+ * handle).  NULL selects the context's own stream. */
+int ssp_set_stream(ssp_ctx* ctx, void* cuda_stream);
+int ssp_synchronize(ssp_ctx* ctx);
+/* Device facts used by the roofline report: SM count and SM clock in kHz (max). */
+int ssp_device_info(ssp_ctx* ctx, int* sm_count, int* sm_clock_khz, int64_t* hbm_bytes);
+
+/* ---- descriptor bank ------------------------------------------------------------------
+ * Replaces the per-pair `ft.descriptors.get()[0:n_orb, :]` host slices handed to
+ * cv.BFMatcher at custom_bruteforce_matcher.py:197-198.  `desc` holds the ORB rows of all
+ * images back to back, 32 bytes per row (uint8 (N,32) C-contiguous); image i owns rows
+ * [row_offsets[i], row_offsets[i+1]).  `row_offsets` is host memory, n_images+1 entries.
+ * Rows per image must be < 2^22 (OpenCV itself asserts < 2^18 per train set). */
+int ssp_upload_descriptor_bank(ssp_ctx* ctx, const uint8_t* desc, const int64_t* row_offsets,
+                               int n_images, int mem_kind);
+/* Zero-copy variant: use the caller's device buffer in place (must be 16-byte aligned and stay
+ * alive and unmodified until the next upload/bind or ssp_destroy). */
+int ssp_bind_descriptor_bank(ssp_ctx* ctx, const uint8_t* d_desc, const int64_t* row_offsets,
+                             int n_images);
+
+/* ---- kernel 1: Hamming all-pairs ------------------------------------------------------
+ * Replaces cv.BFMatcher(cv.NORM_HAMMING[, crossCheck=True]).match / .knnMatch(k=2) + ratio
+ * test for a whole list of image pairs in one call (the pair loop
+ * custom_bruteforce_matcher.py:615-620).  `pairs` is host memory, n_pairs x 2 int32
+ * (query image, train image).
+ *
+ *   SSP_MODE_KNN2_RATIO : per query row the two nearest train rows in the order of a stable
+ *       ascending sort (lowest train index first among equal distances); a query survives iff
+ *       ratio_den * d1 < ratio_num * d2 (0.75 -> 3, 4; exact integer form of :171).
+ *       Train sets with fewer than 2 rows produce no survivors (the reference's `for m, n in`
+ *       would raise; the Python layer raises ValueError for that case).
+ *   SSP_MODE_CROSSCHECK : (q, t) survives iff t = argmin_t D[q,.] and q = argmin_q D[.,t],
+ *       both with the lowest index on ties (OpenCV batchDistance crosscheck semantics).
+ *
+ * Survivors of pair p are reported in ascending query index (OpenCV's order) at positions
+ * [match_offsets[p], match_offsets[p+1]) of the arrays ssp_hamming_fetch_matches returns.
+ * `match_offsets` is host memory with n_pairs+1 entries.  The call synchronises the stream. */
+int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode,
+                            int ratio_num, int ratio_den, int variant, int64_t* match_offsets);
+/* Copies the survivors of the last ssp_hamming_match_pairs call: queryIdx, trainIdx and the
+ * integer Hamming distance (DMatch.distance is this value as float32).  `capacity` is the
+ * number of entries each array can hold (>= match_offsets[n_pairs]). */
+int ssp_hamming_fetch_matches(ssp_ctx* ctx, int32_t* query_idx, int32_t* train_idx,
+                              int32_t* distance, int64_t capacity, int mem_kind);
+/* Optional: the raw per-query nearest neighbours of the last call, one int32[4] record
+ * {idx1, dist1, idx2, dist2} per query row, pairs back to back in call order (for
+ * SSP_MODE_CROSSCHECK the forward direction only; idx2/dist2 are -1 there and whenever the
+ * train set has a single row).  `capacity_rows` >= sum of query rows over the pairs. */
+int ssp_hamming_fetch_best2(ssp_ctx* ctx, int32_t* best2, int64_t capacity_rows, int mem_kind);
+/* Number of kernel launches and device time (ms, CUDA events on the context's stream) of the
+ * dominant Hamming kernel during the last ssp_hamming_match_pairs call. */
+int ssp_hamming_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
+                           int64_t* comparisons);
+
+/* ---- kernel 2: star -> sphere projection and polygon measure --------------------------
+ * Star table of all images (the `keypoints[n_orb:]` star keypoints of
+ * custom_bf_polygon_matcher.py:710 plus their get_star_brightness values,
+ * image_processors.py:222-254).  xy: float64 (n_stars, 2) pixel coordinates; brightness:
+ * float64 (n_stars); image i owns stars [star_offsets[i], star_offsets[i+1]) (host array).
+ * img_w/img_h/focal_px are the pinhole intrinsics of angle_distance (cbpm:86-108): each star
+ * becomes the unit ray of (x - int(img_w/2), y - int(img_h/2), focal_px).  Replaces the whole
+ * star table; polygon banks measured earlier are kept (they own copies of their measures). */
+int ssp_upload_star_bank(ssp_ctx* ctx, const double* xy, const double* brightness,
+                         const int64_t* star_offsets, int n_images, int img_w, int img_h,
+                         double focal_px, int mem_kind);
+/* Reads back the unit rays (n_stars x 3 float64) computed at upload. */
+int ssp_fetch_star_rays(ssp_ctx* ctx, double* rays, int64_t capacity_stars, int mem_kind);
+
+/* Measures the candidate 5-star polygons of one image: the per-candidate body of
+ * get_polygons_characteristics (cbpm:500-600) and the normalisation of cbpm:722-740.
+ * `candidates`: int32 (n_candidates, 5) star indices local to `image`.  Valid polygons are
+ * stored, in candidate order, in the context's polygon bank for that image (replacing
+ * polygon_data_store[img_id], cbpm:744-748).  `status` (optional, host, n_candidates bytes)
+ * receives SSP_POLY_* per candidate; `n_valid` receives the number of stored polygons.
+ * Returns SSP_ERR_DOMAIN (after storing everything else) if any candidate hit the acos domain
+ * error on which the reference raises. */
+int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int64_t n_candidates,
+                        double min_side_px, int mem_kind, uint8_t* status, int64_t* n_valid);
+/* Reads back the stored polygons of `image`, any pointer may be NULL.  All arrays are
+ * (P, 5) row-major in the canonical vertex order (hull order, orientation of cbpm:537-543,
+ * rotated so the smallest vertex angle is element 0, cbpm:578-591):
+ *   star_idx int32, angle / side float64 in radians (un-normalised), brightness float64
+ *   (un-normalised), feat float64 (P, 15) = [angle/pi, side/max side, brightness/max
+ *   brightness] exactly as the reference stores them after cbpm:722-740. */
+int ssp_polygon_fetch(ssp_ctx* ctx, int image, int32_t* star_idx, double* angle, double* side,
+                      double* brightness, double* feat, int64_t capacity, int mem_kind);
+int ssp_polygon_count(ssp_ctx* ctx, int image, int64_t* n_polygons);
+/* Loads a polygon bank directly (normalised 15-dim rows + star indices, which may be NULL);
+ * used for synthetic banks and for resuming from a pickled polygon_data_store. */
+int ssp_polygon_upload_features(ssp_ctx* ctx, int image, const double* feat,
+                                const int32_t* star_idx, int64_t n_polygons, int mem_kind);
+
+/* ---- kernel 3: polygon versus polygon -------------------------------------------------
+ * Replaces the all-pairs distance block cbpm:992-1034, the row argmin cbpm:1063-1067 and
+ * the threshold cbpm:1145-1148 for a list of image pairs.  For each polygon r of the first
+ * image: c* = first argmin_c dist[r,c]; (r, c*, dist) is reported iff dist < threshold
+ * (reference: 0.1566), in ascending r.  SSP_PRECISION_FP64 + SSP_SHIFT_CANONICAL reproduces
+ * numpy's float64 result bit for bit (same summation order, no FMA contraction). */
+int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, double threshold,
+                            int shift_mode, int precision, int64_t* match_offsets);
+int ssp_polygon_fetch_matches(ssp_ctx* ctx, int32_t* poly1, int32_t* poly2, double* dist,
+                              int64_t capacity, int mem_kind);
+/* Optional: per polygon of the first image of every pair, the argmin column and minimum
+ * distance before thresholding (pairs back to back). */
+int ssp_polygon_fetch_rowmin(ssp_ctx* ctx, int32_t* argmin, double* mindist,
+                             int64_t capacity_rows, int mem_kind);
+int ssp_polygon_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
+                           int64_t* evaluations);
+
+/* ---- row N1: star brightness ----------------------------------------------------------
+ * get_star_brightness (image_processors.py:222-254) for many stars of one image:
+ * sum of the 10 largest gray values inside the filled circle cv.circle(center=(int(x), int(y)),
+ * radius=10).  `gray`: uint8 (h, w), the cv.cvtColor(BGR2GRAY) image the reference recomputes
+ * for every star (the host converts once per image with OpenCV itself); `center_xy`: int32
+ * (n, 2) already truncated like the reference's int(); `disc_dxdy`: int32 (n_disc, 2) pixel
+ * offsets of the rasterised disc (the host obtains them from cv.circle once, so the mask is
+ * OpenCV's own); result int32 (n). */
+int ssp_star_brightness(ssp_ctx* ctx, const uint8_t* gray, int h, int w, const int32_t* center_xy,
+                        int64_t n, const int32_t* disc_dxdy, int n_disc, int top_k,
+                        int32_t* brightness, int mem_kind);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSP_B200_H */

@@ -1,0 +1,446 @@
+// Kernel 1 — all-pairs Hamming nearest neighbours on 256-bit ORB descriptors (sm_100a).
+//
+// Replaces cv.BFMatcher(NORM_HAMMING).knnMatch(k=2) + ratio test
+// (custom_bruteforce_matcher.py:160-172) and cv.BFMatcher(NORM_HAMMING, crossCheck=True).match
+// (custom_bruteforce_matcher.py:193-199) for a whole list of image pairs.
+//
+// POPC variant.  One CTA owns a tile of HB_THREADS*R query rows of one directed work item
+// (query image -> train image); every thread keeps R query descriptors (8 x b32 each) in
+// registers.  A dedicated producer warp streams the train image through a ring of shared-memory
+// stages with TMA 1-D bulk copies (cp.async.bulk + mbarrier complete_tx); the 8 consumer warps
+// read each train row as two broadcast LDS.128 and evaluate it against their R queries with
+// LOP3 (xor / carry-save adders) + POPC.  The running best-2 per query lives in registers as a
+// packed key (distance << 22 | train index): an unsigned min on the key IS the
+// (distance, lowest index) order OpenCV's stable insertion produces, so no tie handling is
+// needed anywhere.  Finalize kernels apply the ratio test / mutual-nearest test on the device
+// and compact the survivors in ascending query order.
+#include "common.cuh"
+
+namespace ssp {
+
+constexpr int HB_THREADS = 256;          // consumer threads per CTA
+constexpr int HB_CHUNK = 256;            // train rows per shared-memory stage (8 KB)
+constexpr int HB_STAGES = 4;
+constexpr uint32_t KEY_SHIFT = 22;       // distance <= 256 -> key < 2^31
+constexpr uint32_t KEY_IDX_MASK = (1u << KEY_SHIFT) - 1u;
+constexpr uint32_t KEY_NONE = 0xFFFFFFFFu;
+
+__device__ __forceinline__ void csa(uint32_t a, uint32_t b, uint32_t c, uint32_t& sum,
+                                    uint32_t& carry) {
+  // one LOP3 each: 0x96 = a^b^c, 0xE8 = majority(a,b,c)
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(sum) : "r"(a), "r"(b), "r"(c));
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(carry) : "r"(a), "r"(b), "r"(c));
+}
+
+// Hamming distance of two 256-bit rows.  NPOPC selects how many POPC instructions are spent:
+//   8: xor + popc per word (the textbook form, 8 LOP3 + 8 POPC + adds)
+//   4: Harley-Seal carry-save compression, 8 LOP3 (xor) + 8 LOP3 (4 CSA) + 4 POPC
+template <int NPOPC>
+__device__ __forceinline__ uint32_t ham256(const uint32_t (&q)[8], const uint4 t0, const uint4 t1) {
+  const uint32_t x0 = q[0] ^ t0.x, x1 = q[1] ^ t0.y, x2 = q[2] ^ t0.z, x3 = q[3] ^ t0.w;
+  const uint32_t x4 = q[4] ^ t1.x, x5 = q[5] ^ t1.y, x6 = q[6] ^ t1.z, x7 = q[7] ^ t1.w;
+  if (NPOPC == 8) {
+    return (__popc(x0) + __popc(x1) + __popc(x2)) + (__popc(x3) + __popc(x4) + __popc(x5)) +
+           (__popc(x6) + __popc(x7));
+  } else {
+    uint32_t s0, c0, s1, c1, s2, c2, s3, c3;
+    csa(x0, x1, x2, s0, c0);
+    csa(x3, x4, x5, s1, c1);
+    csa(s0, s1, x6, s2, c2);   // ones: s2, x7
+    csa(c0, c1, c2, s3, c3);   // twos: s3 ; fours: c3
+    return (__popc(s2) + __popc(x7)) + 2u * __popc(s3) + 4u * __popc(c3);
+  }
+}
+
+template <int R, int NPOPC, int K>
+__global__ void __launch_bounds__(HB_THREADS + 32)
+hamming_popc_kernel(const HammingWork* __restrict__ work, int4* __restrict__ best2) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  uint4* stage_buf = reinterpret_cast<uint4*>(smem_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)HB_STAGES * HB_CHUNK * 32);
+  uint64_t* empty = full + HB_STAGES;
+
+  const HammingWork w = work[blockIdx.x];
+  const int tile_base = blockIdx.y * (HB_THREADS * R);
+  if (tile_base >= w.nq) return;  // uniform per CTA
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < HB_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], HB_THREADS / 32);
+    }
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  const int n_chunks = (w.nt + HB_CHUNK - 1) / HB_CHUNK;
+
+  if (warp == HB_THREADS / 32) {
+    // ---- producer warp: one elected lane feeds the ring -----------------------------------
+    if ((tid & 31) == 0) {
+      for (int c = 0; c < n_chunks; ++c) {
+        const int s = c % HB_STAGES;
+        const uint32_t ph = (uint32_t)(c / HB_STAGES) & 1u;
+        if (c >= HB_STAGES) mbar_wait(&empty[s], ph ^ 1u);
+        const int rows = min(HB_CHUNK, w.nt - c * HB_CHUNK);
+        const uint32_t bytes = (uint32_t)rows * 32u;
+        mbar_arrive_expect_tx(&full[s], bytes);
+        tma_bulk_g2s(stage_buf + (size_t)s * HB_CHUNK * 2, w.t + (size_t)c * HB_CHUNK * 2, bytes,
+                     &full[s]);
+      }
+    }
+    return;
+  }
+
+  // ---- consumers --------------------------------------------------------------------------
+  uint32_t q[R][8];
+  uint32_t b1[R], b2[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int row = tile_base + r * HB_THREADS + tid;
+    uint4 a = make_uint4(0, 0, 0, 0), b = a;
+    if (row < w.nq) {
+      a = __ldg(w.q + (size_t)row * 2);
+      b = __ldg(w.q + (size_t)row * 2 + 1);
+    }
+    q[r][0] = a.x; q[r][1] = a.y; q[r][2] = a.z; q[r][3] = a.w;
+    q[r][4] = b.x; q[r][5] = b.y; q[r][6] = b.z; q[r][7] = b.w;
+    b1[r] = KEY_NONE;
+    b2[r] = KEY_NONE;
+  }
+
+  for (int c = 0; c < n_chunks; ++c) {
+    const int s = c % HB_STAGES;
+    const uint32_t ph = (uint32_t)(c / HB_STAGES) & 1u;
+    mbar_wait(&full[s], ph);
+    const uint4* tb = stage_buf + (size_t)s * HB_CHUNK * 2;
+    const int rows = min(HB_CHUNK, w.nt - c * HB_CHUNK);
+    const uint32_t base = (uint32_t)c * HB_CHUNK;
+#pragma unroll 2
+    for (int j = 0; j < rows; ++j) {
+      const uint4 t0 = tb[2 * j];
+      const uint4 t1 = tb[2 * j + 1];
+      const uint32_t idx = base + (uint32_t)j;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const uint32_t d = ham256<NPOPC>(q[r], t0, t1);
+        const uint32_t key = d * (1u << KEY_SHIFT) + idx;
+        if (K == 2) b2[r] = min(b2[r], max(b1[r], key));
+        b1[r] = min(b1[r], key);
+      }
+    }
+    __syncwarp();
+    if ((tid & 31) == 0) mbar_arrive(&empty[s]);
+  }
+
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int row = tile_base + r * HB_THREADS + tid;
+    if (row < w.nq) {
+      int4 o;
+      o.x = (b1[r] == KEY_NONE) ? -1 : (int)(b1[r] & KEY_IDX_MASK);
+      o.y = (b1[r] == KEY_NONE) ? -1 : (int)(b1[r] >> KEY_SHIFT);
+      o.z = (K == 1 || b2[r] == KEY_NONE) ? -1 : (int)(b2[r] & KEY_IDX_MASK);
+      o.w = (K == 1 || b2[r] == KEY_NONE) ? -1 : (int)(b2[r] >> KEY_SHIFT);
+      best2[w.out_row + row] = o;
+    }
+  }
+}
+
+// ---- finalize: survivor test, per-pair count, scan over pairs, ordered compaction ----------
+
+__device__ __forceinline__ bool survives(const HammingPair& p, const int4* __restrict__ best2,
+                                         int q, int mode, int rnum, int rden, int4& rec) {
+  rec = best2[p.fwd_row + q];
+  if (mode == SSP_MODE_KNN2_RATIO) {
+    // m.distance < ratio * n.distance  <=>  den*d1 < num*d2 (exact for ratio = num/den)
+    return rec.z >= 0 && (long long)rden * rec.y < (long long)rnum * rec.w;
+  }
+  if (rec.x < 0) return false;
+  return best2[p.rev_row + rec.x].x == q;
+}
+
+constexpr int FIN_THREADS = 512;
+
+__global__ void __launch_bounds__(FIN_THREADS)
+hamming_count_kernel(const HammingPair* __restrict__ pairs, const int4* __restrict__ best2,
+                     int mode, int rnum, int rden, int* __restrict__ counts) {
+  const HammingPair p = pairs[blockIdx.x];
+  int local = 0;
+  for (int q = threadIdx.x; q < p.nq; q += FIN_THREADS) {
+    int4 rec;
+    local += survives(p, best2, q, mode, rnum, rden, rec) ? 1 : 0;
+  }
+  __shared__ int warp_sum[FIN_THREADS / 32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int tot = 0;
+    for (int i = 0; i < FIN_THREADS / 32; ++i) tot += warp_sum[i];
+    counts[blockIdx.x] = tot;
+  }
+}
+
+__global__ void __launch_bounds__(FIN_THREADS)
+hamming_compact_kernel(const HammingPair* __restrict__ pairs, const int4* __restrict__ best2,
+                       int mode, int rnum, int rden, const long long* __restrict__ offsets,
+                       int* __restrict__ mq, int* __restrict__ mt, int* __restrict__ md) {
+  const HammingPair p = pairs[blockIdx.x];
+  __shared__ int warp_cnt[FIN_THREADS / 32];
+  __shared__ long long run;
+  if (threadIdx.x == 0) run = offsets[blockIdx.x];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int base = 0; base < p.nq; base += FIN_THREADS) {
+    const int q = base + threadIdx.x;
+    int4 rec = make_int4(0, 0, 0, 0);
+    const bool keep = (q < p.nq) && survives(p, best2, q, mode, rnum, rden, rec);
+    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) warp_cnt[wid] = __popc(ballot);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int i = 0; i < FIN_THREADS / 32; ++i) {
+      const int c = warp_cnt[i];
+      before += (i < wid) ? c : 0;
+      total += c;
+    }
+    if (keep) {
+      const long long pos = run + before + __popc(ballot & ((1u << lane) - 1u));
+      mq[pos] = q;
+      mt[pos] = rec.x;
+      md[pos] = rec.y;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) run += total;
+    __syncthreads();
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------
+
+template <int R, int NPOPC, int K>
+static cudaError_t launch_popc(ssp_ctx* ctx, int n_work, int max_nq) {
+  const size_t smem = (size_t)HB_STAGES * HB_CHUNK * 32 + 2 * HB_STAGES * sizeof(uint64_t);
+  auto kern = hamming_popc_kernel<R, NPOPC, K>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int tiles = (max_nq + HB_THREADS * R - 1) / (HB_THREADS * R);
+  dim3 grid((unsigned)n_work, (unsigned)tiles);
+  kern<<<grid, HB_THREADS + 32, smem, ctx->stream>>>(ctx->h_work.as<HammingWork>(),
+                                                       ctx->h_best2.as<int4>());
+  return cudaGetLastError();
+}
+
+// implemented in hamming_tensor.cu
+cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& work, int k,
+                                  std::string* why_not);
+
+}  // namespace ssp
+
+extern "C" {
+
+int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode,
+                            int ratio_num, int ratio_den, int variant, int64_t* match_offsets) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, ctx->d_desc != nullptr || (!ctx->row_off.empty() && ctx->row_off.back() == 0),
+              SSP_ERR_STATE, "ssp_hamming_match_pairs: no descriptor bank uploaded");
+  SSP_REQUIRE(ctx, !ctx->row_off.empty(), SSP_ERR_STATE,
+              "ssp_hamming_match_pairs: no descriptor bank uploaded");
+  SSP_REQUIRE(ctx, n_pairs >= 0 && (n_pairs == 0 || pairs != nullptr), SSP_ERR_INVALID,
+              "ssp_hamming_match_pairs: bad pair list");
+  SSP_REQUIRE(ctx, match_offsets != nullptr, SSP_ERR_INVALID,
+              "ssp_hamming_match_pairs: match_offsets is NULL");
+  SSP_REQUIRE(ctx, mode == SSP_MODE_KNN2_RATIO || mode == SSP_MODE_CROSSCHECK, SSP_ERR_INVALID,
+              "ssp_hamming_match_pairs: unknown mode %d", mode);
+  SSP_REQUIRE(ctx, variant >= SSP_HAMMING_AUTO && variant <= SSP_HAMMING_TENSOR, SSP_ERR_INVALID,
+              "ssp_hamming_match_pairs: unknown variant %d", variant);
+  if (mode == SSP_MODE_KNN2_RATIO)
+    SSP_REQUIRE(ctx, ratio_num > 0 && ratio_den > 0, SSP_ERR_INVALID,
+                "ssp_hamming_match_pairs: ratio must be positive");
+  const int n_images = (int)ctx->row_off.size() - 1;
+
+  ctx->h_n_matches = -1;
+  ctx->h_launches = 0;
+  ctx->h_main_ms = 0.f;
+  ctx->h_comparisons = 0;
+  ctx->h_match_offsets.assign((size_t)n_pairs + 1, 0);
+  if (n_pairs == 0) {
+    match_offsets[0] = 0;
+    ctx->h_n_matches = 0;
+    ctx->h_total_rows = 0;
+    return SSP_OK;
+  }
+
+  // directed work items + per-pair finalize records
+  const bool cross = (mode == SSP_MODE_CROSSCHECK);
+  std::vector<HammingWork> work;
+  std::vector<HammingPair> hp((size_t)n_pairs);
+  work.reserve((size_t)n_pairs * (cross ? 2 : 1));
+  const uint4* bank = reinterpret_cast<const uint4*>(ctx->d_desc);
+  long long fwd_rows = 0, rows = 0;
+  int max_nq = 0;
+  for (int p = 0; p < n_pairs; ++p) {
+    const int qi = pairs[2 * p], ti = pairs[2 * p + 1];
+    SSP_REQUIRE(ctx, qi >= 0 && qi < n_images && ti >= 0 && ti < n_images, SSP_ERR_INVALID,
+                "ssp_hamming_match_pairs: pair %d = (%d, %d) out of range [0, %d)", p, qi, ti,
+                n_images);
+    fwd_rows += ctx->row_off[qi + 1] - ctx->row_off[qi];
+  }
+  long long rev_cursor = fwd_rows;
+  for (int p = 0; p < n_pairs; ++p) {
+    const int qi = pairs[2 * p], ti = pairs[2 * p + 1];
+    const int nq = (int)(ctx->row_off[qi + 1] - ctx->row_off[qi]);
+    const int nt = (int)(ctx->row_off[ti + 1] - ctx->row_off[ti]);
+    HammingWork f;
+    f.q = bank + ctx->row_off[qi] * 2;
+    f.t = bank + ctx->row_off[ti] * 2;
+    f.nq = nq;
+    f.nt = nt;
+    f.out_row = rows;
+    hp[p].fwd_row = rows;
+    hp[p].rev_row = -1;
+    hp[p].nq = nq;
+    hp[p].nt = nt;
+    rows += nq;
+    if (nq > 0) work.push_back(f);
+    max_nq = nq > max_nq ? nq : max_nq;
+    ctx->h_comparisons += (long long)nq * nt;
+    if (cross) {
+      HammingWork r;
+      r.q = f.t;
+      r.t = f.q;
+      r.nq = nt;
+      r.nt = nq;
+      r.out_row = rev_cursor;
+      hp[p].rev_row = rev_cursor;
+      rev_cursor += nt;
+      if (nt > 0) work.push_back(r);
+      max_nq = nt > max_nq ? nt : max_nq;
+    }
+  }
+  const long long total_rows = cross ? rev_cursor : rows;
+  ctx->h_total_rows = rows;
+
+  SSP_CUDA_TRY(ctx, ctx->h_best2.ensure((size_t)(total_rows + 1) * sizeof(int4)));
+  SSP_CUDA_TRY(ctx, ctx->h_pairs.ensure(hp.size() * sizeof(HammingPair)));
+  SSP_CUDA_TRY(ctx, ctx->h_counts.ensure((size_t)n_pairs * sizeof(int)));
+  SSP_CUDA_TRY(ctx, ctx->h_offsets.ensure(((size_t)n_pairs + 1) * sizeof(long long)));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_pairs.p, hp.data(), hp.size() * sizeof(HammingPair),
+                                    cudaMemcpyHostToDevice, ctx->stream));
+  // rows of empty train sets are never written by a kernel: make them read as "no neighbour"
+  SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_best2.p, 0xFF, (size_t)(total_rows + 1) * sizeof(int4),
+                                    ctx->stream));
+
+  const int k = cross ? 1 : 2;
+  if (!work.empty()) {
+    int v = variant;
+    if (v == SSP_HAMMING_AUTO) v = SSP_HAMMING_POPC_CSA;
+    SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    if (v == SSP_HAMMING_TENSOR) {
+      std::string why;
+      cudaError_t e = launch_hamming_tensor(ctx, work, k, &why);
+      if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
+      SSP_CUDA_TRY(ctx, e);
+    } else {
+      SSP_CUDA_TRY(ctx, ctx->h_work.ensure(work.size() * sizeof(HammingWork)));
+      SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_work.p, work.data(),
+                                        work.size() * sizeof(HammingWork), cudaMemcpyHostToDevice,
+                                        ctx->stream));
+      cudaError_t e;
+      const int nw = (int)work.size();
+      if (v == SSP_HAMMING_POPC)
+        e = (k == 2) ? launch_popc<4, 8, 2>(ctx, nw, max_nq) : launch_popc<4, 8, 1>(ctx, nw, max_nq);
+      else
+        e = (k == 2) ? launch_popc<4, 4, 2>(ctx, nw, max_nq) : launch_popc<4, 4, 1>(ctx, nw, max_nq);
+      SSP_CUDA_TRY(ctx, e);
+      ctx->h_launches += 1;
+    }
+    SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  }
+
+  hamming_count_kernel<<<n_pairs, FIN_THREADS, 0, ctx->stream>>>(
+      ctx->h_pairs.as<HammingPair>(), ctx->h_best2.as<int4>(), mode, ratio_num, ratio_den,
+      ctx->h_counts.as<int>());
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->h_counts.as<int>(), n_pairs,
+                                                  ctx->h_offsets.as<long long>());
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  ctx->h_launches += 2;
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_match_offsets.data(), ctx->h_offsets.p,
+                                    ((size_t)n_pairs + 1) * sizeof(long long),
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  const long long total = ctx->h_match_offsets[(size_t)n_pairs];
+  SSP_CUDA_TRY(ctx, ctx->h_mq.ensure((size_t)(total + 1) * sizeof(int)));
+  SSP_CUDA_TRY(ctx, ctx->h_mt.ensure((size_t)(total + 1) * sizeof(int)));
+  SSP_CUDA_TRY(ctx, ctx->h_md.ensure((size_t)(total + 1) * sizeof(int)));
+  hamming_compact_kernel<<<n_pairs, FIN_THREADS, 0, ctx->stream>>>(
+      ctx->h_pairs.as<HammingPair>(), ctx->h_best2.as<int4>(), mode, ratio_num, ratio_den,
+      ctx->h_offsets.as<long long>(), ctx->h_mq.as<int>(), ctx->h_mt.as<int>(),
+      ctx->h_md.as<int>());
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  ctx->h_launches += 1;
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (!work.empty()) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->h_main_ms, ctx->ev0, ctx->ev1));
+  for (int p = 0; p <= n_pairs; ++p) match_offsets[p] = ctx->h_match_offsets[(size_t)p];
+  ctx->h_n_matches = total;
+  return SSP_OK;
+}
+
+int ssp_hamming_fetch_matches(ssp_ctx* ctx, int32_t* query_idx, int32_t* train_idx,
+                              int32_t* distance, int64_t capacity, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, ctx->h_n_matches >= 0, SSP_ERR_STATE,
+              "ssp_hamming_fetch_matches: no completed ssp_hamming_match_pairs call");
+  const long long n = ctx->h_n_matches;
+  SSP_REQUIRE(ctx, capacity >= n, SSP_ERR_CAPACITY,
+              "ssp_hamming_fetch_matches: capacity %lld < %lld matches", (long long)capacity, n);
+  if (n == 0) return SSP_OK;
+  const cudaMemcpyKind kind = from_device_kind(mem_kind);
+  if (query_idx)
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(query_idx, ctx->h_mq.p, (size_t)n * 4, kind, ctx->stream));
+  if (train_idx)
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(train_idx, ctx->h_mt.p, (size_t)n * 4, kind, ctx->stream));
+  if (distance)
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(distance, ctx->h_md.p, (size_t)n * 4, kind, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+int ssp_hamming_fetch_best2(ssp_ctx* ctx, int32_t* best2, int64_t capacity_rows, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, ctx->h_n_matches >= 0, SSP_ERR_STATE,
+              "ssp_hamming_fetch_best2: no completed ssp_hamming_match_pairs call");
+  SSP_REQUIRE(ctx, best2 != nullptr, SSP_ERR_INVALID, "ssp_hamming_fetch_best2: NULL buffer");
+  SSP_REQUIRE(ctx, capacity_rows >= ctx->h_total_rows, SSP_ERR_CAPACITY,
+              "ssp_hamming_fetch_best2: capacity %lld < %lld rows", (long long)capacity_rows,
+              ctx->h_total_rows);
+  if (ctx->h_total_rows == 0) return SSP_OK;
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(best2, ctx->h_best2.p, (size_t)ctx->h_total_rows * 16,
+                                    from_device_kind(mem_kind), ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+int ssp_hamming_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
+                           int64_t* comparisons) {
+  if (!ctx) return SSP_ERR_INVALID;
+  if (n_launches) *n_launches = ctx->h_launches;
+  if (main_kernel_ms) *main_kernel_ms = ctx->h_main_ms;
+  if (comparisons) *comparisons = ctx->h_comparisons;
+  return SSP_OK;
+}
+
+}  // extern "C"

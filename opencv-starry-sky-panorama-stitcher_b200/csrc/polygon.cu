@@ -1,0 +1,786 @@
+// Kernel 2 (star -> sphere projection, polygon measure) and kernel 3 (polygon vs polygon) of
+// libssp_b200.so.  FP64 throughout and in the reference's operation order
+// (custom_bf_polygon_matcher.py:70-135, :500-600, :722-740, :992-1067): the spherical law of
+// cosines used there is ill-conditioned, FP32 cannot hold the 1e-5 rad parity bound.
+#include "common.cuh"
+
+namespace ssp {
+
+// ---------------------------------------------------------------------------------------------
+// star -> unit ray (angle_distance, cbpm:101-106, unit_vector cbpm:74-76)
+// ---------------------------------------------------------------------------------------------
+__global__ void star_rays_kernel(const double* __restrict__ xy, long long n, double half_w,
+                                 double half_h, double focal, double* __restrict__ rays) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double vx = xy[2 * i] - half_w;
+  const double vy = xy[2 * i + 1] - half_h;
+  const double vz = focal;
+  const double nn = __dadd_rn(__dadd_rn(__dmul_rn(vx, vx), __dmul_rn(vy, vy)), __dmul_rn(vz, vz));
+  const double norm = sqrt(nn);
+  rays[3 * i] = __ddiv_rn(vx, norm);
+  rays[3 * i + 1] = __ddiv_rn(vy, norm);
+  rays[3 * i + 2] = __ddiv_rn(vz, norm);
+}
+
+struct StarView {
+  const double* xy;      // n x 2
+  const double* bright;  // n
+  const double* rays;    // n x 3
+  int n;
+};
+
+// angle_between of two unit rays: arccos(clip(dot, -1, 1))  (cbpm:78-84)
+__device__ __forceinline__ double ray_angle(const double* a, const double* b) {
+  double d = __dadd_rn(__dadd_rn(__dmul_rn(a[0], b[0]), __dmul_rn(a[1], b[1])), __dmul_rn(a[2], b[2]));
+  d = fmin(fmax(d, -1.0), 1.0);
+  return acos(d);
+}
+
+// sign-exact 2-D orientation for float32-valued pixel coordinates (products are exact in
+// double); > 0: c is left of a->b in (x right, y up) axes.
+__device__ __forceinline__ double orient2d(double ax, double ay, double bx, double by, double cx,
+                                           double cy) {
+  return __dsub_rn(__dmul_rn(bx - ax, cy - ay), __dmul_rn(by - ay, cx - ax));
+}
+
+// One thread per candidate polygon: the body of get_polygons_characteristics (cbpm:500-600)
+// plus the normalisation of cbpm:722-740.  Results go to per-candidate slots; a stable
+// compaction keeps the valid ones afterwards.
+__global__ void __launch_bounds__(128)
+poly_measure_kernel(StarView sv, const int* __restrict__ cand, long long n_cand, double min_side,
+                    unsigned char* __restrict__ status, int* __restrict__ flags,
+                    int* __restrict__ n_domain, int* __restrict__ o_idx,
+                    double* __restrict__ o_angle, double* __restrict__ o_side,
+                    double* __restrict__ o_bright, double* __restrict__ o_feat) {
+  const long long pidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pidx >= n_cand) return;
+  int id[5];
+  double x[5], y[5];
+  bool bad = false;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    id[k] = cand[pidx * 5 + k];
+    if (id[k] < 0 || id[k] >= sv.n) {
+      bad = true;
+      id[k] = 0;
+    }
+    x[k] = sv.xy[2 * (long long)id[k]];
+    y[k] = sv.xy[2 * (long long)id[k] + 1];
+  }
+  if (bad) {
+    status[pidx] = SSP_POLY_BAD_INDEX;
+    flags[pidx] = 0;
+    return;
+  }
+  // (1) reject polygons with a pixel distance below min_side (cbpm:515, dist_between_2_points)
+  bool short_side = false;
+#pragma unroll
+  for (int i = 0; i < 5; ++i)
+#pragma unroll
+    for (int j = i + 1; j < 5; ++j) {
+      const double dx = x[j] - x[i], dy = y[j] - y[i];
+      const double d = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+      short_side |= (d < min_side);
+    }
+  if (short_side) {
+    status[pidx] = SSP_POLY_SHORT_SIDE;
+    flags[pidx] = 0;
+    return;
+  }
+  // (2) convex hull of the 5 points by gift wrapping; all 5 must be strict hull vertices
+  //     (alphashape(pts, 0) == MultiPoint.convex_hull drops interior and collinear points,
+  //     cbpm:520-526).  Start at the lowest point (min y, then min x).
+  int start = 0;
+#pragma unroll
+  for (int k = 1; k < 5; ++k)
+    if (y[k] < y[start] || (y[k] == y[start] && x[k] < x[start])) start = k;
+  int ord[5];
+  int cnt = 1, cur = start;
+  ord[0] = start;
+  bool closed = false;
+  for (int step = 0; step < 5; ++step) {
+    int nxt = -1;
+    for (int s = 0; s < 5; ++s) {
+      if (s == cur) continue;
+      if (nxt < 0) {
+        nxt = s;
+        continue;
+      }
+      const double o = orient2d(x[cur], y[cur], x[nxt], y[nxt], x[s], y[s]);
+      if (o < 0.0) {
+        nxt = s;
+      } else if (o == 0.0) {
+        const double dn = (x[nxt] - x[cur]) * (x[nxt] - x[cur]) + (y[nxt] - y[cur]) * (y[nxt] - y[cur]);
+        const double ds = (x[s] - x[cur]) * (x[s] - x[cur]) + (y[s] - y[cur]) * (y[s] - y[cur]);
+        if (ds > dn) nxt = s;
+      }
+    }
+    cur = nxt;
+    if (cur == start) {
+      closed = true;
+      break;
+    }
+    if (cnt < 5) ord[cnt] = cur;
+    ++cnt;
+  }
+  if (!closed || cnt != 5) {
+    status[pidx] = SSP_POLY_NOT_CONVEX;
+    flags[pidx] = 0;
+    return;
+  }
+  // gift wrapping above walks counter-clockwise in (x right, y up) axes, i.e. positive
+  // shoelace area; the reference keeps the ring with NEGATIVE signed area (cbpm:537-543):
+  // same start vertex, opposite direction.
+  int ring[5];
+  ring[0] = ord[0];
+  ring[1] = ord[4];
+  ring[2] = ord[3];
+  ring[3] = ord[2];
+  ring[4] = ord[1];
+
+  // (3) spherical measures.  side[i] = angle(ring[i], ring[i+1]) (cbpm:569-576);
+  //     vertex angle i from (prev, cur, next) by the spherical law of cosines (cbpm:127-135)
+  double ray[5][3];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const long long s = id[ring[k]];
+    ray[k][0] = sv.rays[3 * s];
+    ray[k][1] = sv.rays[3 * s + 1];
+    ray[k][2] = sv.rays[3 * s + 2];
+  }
+  double side[5], angle[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) side[k] = ray_angle(ray[k], ray[(k + 1) % 5]);
+  bool domain = false;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const int prev = (k + 4) % 5, next = (k + 1) % 5;
+    const double b = side[prev];                   // angle_p1_p2
+    const double c = side[k];                      // angle_p2_p3
+    const double a = ray_angle(ray[next], ray[prev]);  // angle_p3_p1
+    const double num = __dsub_rn(cos(a), __dmul_rn(cos(b), cos(c)));
+    const double den = __dmul_rn(sin(b), sin(c));
+    const double v = __ddiv_rn(num, den);
+    if (!(fabs(v) <= 1.0)) domain = true;  // math.acos raises ValueError (cbpm:134)
+    angle[k] = acos(v);
+  }
+  if (domain) {
+    status[pidx] = SSP_POLY_DOMAIN;
+    flags[pidx] = 0;
+    atomicAdd(n_domain, 1);
+    return;
+  }
+  // (4) rotate so the smallest angle (first occurrence) is element 0 (cbpm:578-591)
+  int rot = 0;
+#pragma unroll
+  for (int k = 1; k < 5; ++k)
+    if (angle[k] < angle[rot]) rot = k;
+  double max_side = 0.0, max_bright = 0.0;
+  double r_angle[5], r_side[5], r_bright[5];
+  int r_idx[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const int src = (k + rot) % 5;
+    r_idx[k] = id[ring[src]];
+    r_angle[k] = angle[src];
+    r_side[k] = side[src];
+    r_bright[k] = sv.bright[r_idx[k]];
+    max_side = fmax(max_side, r_side[k]);
+    max_bright = fmax(max_bright, r_bright[k]);
+  }
+  // (5) normalise: angles / pi, sides / max side, brightness / max brightness (cbpm:722-740)
+  const double pi = 3.141592653589793;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    o_idx[pidx * 5 + k] = r_idx[k];
+    o_angle[pidx * 5 + k] = r_angle[k];
+    o_side[pidx * 5 + k] = r_side[k];
+    o_bright[pidx * 5 + k] = r_bright[k];
+    o_feat[pidx * 15 + k] = __ddiv_rn(r_angle[k], pi);
+    o_feat[pidx * 15 + 5 + k] = __ddiv_rn(r_side[k], max_side);
+    o_feat[pidx * 15 + 10 + k] = __ddiv_rn(r_bright[k], max_bright);
+  }
+  status[pidx] = SSP_POLY_VALID;
+  flags[pidx] = 1;
+}
+
+__global__ void poly_scatter_kernel(const int* __restrict__ flags, const long long* __restrict__ pos,
+                                    long long n_cand, const int* __restrict__ t_idx,
+                                    const double* __restrict__ t_angle,
+                                    const double* __restrict__ t_side,
+                                    const double* __restrict__ t_bright,
+                                    const double* __restrict__ t_feat, int* __restrict__ o_idx,
+                                    double* __restrict__ o_angle, double* __restrict__ o_side,
+                                    double* __restrict__ o_bright, double* __restrict__ o_feat) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_cand || !flags[i]) return;
+  const long long d = pos[i];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    o_idx[d * 5 + k] = t_idx[i * 5 + k];
+    o_angle[d * 5 + k] = t_angle[i * 5 + k];
+    o_side[d * 5 + k] = t_side[i * 5 + k];
+    o_bright[d * 5 + k] = t_bright[i * 5 + k];
+  }
+#pragma unroll
+  for (int k = 0; k < 15; ++k) o_feat[d * 15 + k] = t_feat[i * 15 + k];
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 3: polygon versus polygon (cbpm:992-1067, :1145-1148)
+// ---------------------------------------------------------------------------------------------
+constexpr int PC_THREADS = 128;  // rows per CTA (one polygon of image 1 per thread)
+constexpr int PC_TILE = 128;     // columns (polygons of image 2) per shared-memory tile
+
+// Squared distance in numpy's float64 evaluation order: per property a sequential sum of the 5
+// squared differences, then (angles + sides) + brightness; no FMA contraction so every
+// intermediate rounds exactly like np.square / np.sum / the two additions of cbpm:1011-1016.
+template <int SHIFT>
+__device__ __forceinline__ double poly_dist2_f64(const double (&a)[15], const double* __restrict__ b) {
+  double tot = 0.0;
+#pragma unroll
+  for (int g = 0; g < 3; ++g) {
+    double acc = 0.0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const double d = __dsub_rn(a[g * 5 + k], b[g * 5 + (k + SHIFT) % 5]);
+      const double s = __dmul_rn(d, d);
+      acc = (k == 0) ? s : __dadd_rn(acc, s);
+    }
+    tot = (g == 0) ? acc : __dadd_rn(tot, acc);
+  }
+  return tot;
+}
+
+template <int SHIFT>
+__device__ __forceinline__ float poly_dist2_f32(const float (&a)[15], const float* __restrict__ b) {
+  float tot = 0.f;
+#pragma unroll
+  for (int g = 0; g < 3; ++g)
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const float d = a[g * 5 + k] - b[g * 5 + (k + SHIFT) % 5];
+      tot = fmaf(d, d, tot);
+    }
+  return tot;
+}
+
+// FP64 parity kernel.  Row argmin is taken on sqrt(dist2) exactly as np.argmin sees it: two
+// different dist2 values can round to the same square root, and the reference then keeps the
+// earlier column.  `thr` is the dist2 of the last examined improvement, so the sqrt is only
+// evaluated O(log P2) times per row.
+template <bool MIN_SHIFTS>
+__global__ void __launch_bounds__(PC_THREADS)
+poly_compare_f64_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ argmin,
+                        double* __restrict__ mindist) {
+  __shared__ __align__(16) double tile[PC_TILE * 15];
+  const PolyPair pp = pairs[blockIdx.x];
+  const int row0 = blockIdx.y * PC_THREADS;
+  if (row0 >= pp.p1) return;
+  const int r = row0 + threadIdx.x;
+  const bool live = r < pp.p1;
+  double a[15];
+#pragma unroll
+  for (int k = 0; k < 15; ++k) a[k] = live ? pp.f1[(long long)r * 15 + k] : 0.0;
+  double thr = INFINITY, best = INFINITY;
+  int best_c = 0;
+  for (int c0 = 0; c0 < pp.p2; c0 += PC_TILE) {
+    const int ncol = min(PC_TILE, pp.p2 - c0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < ncol * 15; i += PC_THREADS)
+      tile[i] = pp.f2[(long long)c0 * 15 + i];
+    __syncthreads();
+    if (live) {
+      for (int j = 0; j < ncol; ++j) {
+        const double* b = tile + j * 15;
+        double v = poly_dist2_f64<0>(a, b);
+        if (MIN_SHIFTS) {
+          v = fmin(v, poly_dist2_f64<1>(a, b));
+          v = fmin(v, poly_dist2_f64<2>(a, b));
+          v = fmin(v, poly_dist2_f64<3>(a, b));
+          v = fmin(v, poly_dist2_f64<4>(a, b));
+        }
+        if (v < thr) {
+          const double s = sqrt(v);
+          if (s < best) {
+            best = s;
+            best_c = c0 + j;
+          }
+          thr = v;
+        }
+      }
+    }
+  }
+  if (live) {
+    argmin[pp.out_row + r] = best_c;
+    mindist[pp.out_row + r] = best;
+  }
+}
+
+// FP32 fast mode (non-parity): features converted on the fly, FMA accumulation.
+template <bool MIN_SHIFTS>
+__global__ void __launch_bounds__(PC_THREADS)
+poly_compare_f32_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ argmin,
+                        double* __restrict__ mindist) {
+  __shared__ __align__(16) float tile[PC_TILE * 15];
+  const PolyPair pp = pairs[blockIdx.x];
+  const int row0 = blockIdx.y * PC_THREADS;
+  if (row0 >= pp.p1) return;
+  const int r = row0 + threadIdx.x;
+  const bool live = r < pp.p1;
+  float a[15];
+#pragma unroll
+  for (int k = 0; k < 15; ++k) a[k] = live ? (float)pp.f1[(long long)r * 15 + k] : 0.f;
+  float best = INFINITY;
+  int best_c = 0;
+  for (int c0 = 0; c0 < pp.p2; c0 += PC_TILE) {
+    const int ncol = min(PC_TILE, pp.p2 - c0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < ncol * 15; i += PC_THREADS)
+      tile[i] = (float)pp.f2[(long long)c0 * 15 + i];
+    __syncthreads();
+    if (live) {
+      for (int j = 0; j < ncol; ++j) {
+        const float* b = tile + j * 15;
+        float v = poly_dist2_f32<0>(a, b);
+        if (MIN_SHIFTS) {
+          v = fminf(v, poly_dist2_f32<1>(a, b));
+          v = fminf(v, poly_dist2_f32<2>(a, b));
+          v = fminf(v, poly_dist2_f32<3>(a, b));
+          v = fminf(v, poly_dist2_f32<4>(a, b));
+        }
+        if (v < best) {
+          best = v;
+          best_c = c0 + j;
+        }
+      }
+    }
+  }
+  if (live) {
+    argmin[pp.out_row + r] = best_c;
+    mindist[pp.out_row + r] = (double)sqrtf(best);
+  }
+}
+
+constexpr int PF_THREADS = 256;
+
+__global__ void __launch_bounds__(PF_THREADS)
+poly_count_kernel(const PolyPair* __restrict__ pairs, const double* __restrict__ mindist,
+                  double threshold, int* __restrict__ counts) {
+  const PolyPair pp = pairs[blockIdx.x];
+  int local = 0;
+  for (int r = threadIdx.x; r < pp.p1; r += PF_THREADS)
+    local += (pp.p2 > 0 && mindist[pp.out_row + r] < threshold) ? 1 : 0;
+  __shared__ int ws[PF_THREADS / 32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int i = 0; i < PF_THREADS / 32; ++i) t += ws[i];
+    counts[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(PF_THREADS)
+poly_compact_kernel(const PolyPair* __restrict__ pairs, const int* __restrict__ argmin,
+                    const double* __restrict__ mindist, double threshold,
+                    const long long* __restrict__ offsets, int* __restrict__ m1,
+                    int* __restrict__ m2, double* __restrict__ md) {
+  const PolyPair pp = pairs[blockIdx.x];
+  __shared__ int warp_cnt[PF_THREADS / 32];
+  __shared__ long long run;
+  if (threadIdx.x == 0) run = offsets[blockIdx.x];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int base = 0; base < pp.p1; base += PF_THREADS) {
+    const int r = base + threadIdx.x;
+    double d = 0.0;
+    bool keep = false;
+    if (r < pp.p1 && pp.p2 > 0) {
+      d = mindist[pp.out_row + r];
+      keep = d < threshold;
+    }
+    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) warp_cnt[wid] = __popc(ballot);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int i = 0; i < PF_THREADS / 32; ++i) {
+      const int c = warp_cnt[i];
+      before += (i < wid) ? c : 0;
+      total += c;
+    }
+    if (keep) {
+      const long long pos = run + before + __popc(ballot & ((1u << lane) - 1u));
+      m1[pos] = r;
+      m2[pos] = argmin[pp.out_row + r];
+      md[pos] = d;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) run += total;
+    __syncthreads();
+  }
+}
+
+}  // namespace ssp
+
+// =============================================================================================
+extern "C" {
+
+int ssp_upload_star_bank(ssp_ctx* ctx, const double* xy, const double* brightness,
+                         const int64_t* star_offsets, int n_images, int img_w, int img_h,
+                         double focal_px, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, star_offsets != nullptr && n_images >= 0 && star_offsets[0] == 0,
+              SSP_ERR_INVALID, "ssp_upload_star_bank: bad offsets");
+  for (int i = 0; i < n_images; ++i)
+    SSP_REQUIRE(ctx, star_offsets[i + 1] >= star_offsets[i] &&
+                         star_offsets[i + 1] - star_offsets[i] < (1LL << 31) - 1,
+                SSP_ERR_INVALID, "ssp_upload_star_bank: bad offsets at image %d", i);
+  SSP_REQUIRE(ctx, img_w > 0 && img_h > 0 && focal_px > 0.0, SSP_ERR_INVALID,
+              "ssp_upload_star_bank: image size and focal length must be positive");
+  const long long n = star_offsets[n_images];
+  SSP_REQUIRE(ctx, n == 0 || (xy != nullptr && brightness != nullptr), SSP_ERR_INVALID,
+              "ssp_upload_star_bank: NULL star arrays");
+  SSP_CUDA_TRY(ctx, ctx->s_xy.ensure((size_t)n * 16 + 16));
+  SSP_CUDA_TRY(ctx, ctx->s_bright.ensure((size_t)n * 8 + 8));
+  SSP_CUDA_TRY(ctx, ctx->s_rays.ensure((size_t)n * 24 + 24));
+  if (n > 0) {
+    const cudaMemcpyKind kind = to_device_kind(mem_kind);
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_xy.p, xy, (size_t)n * 16, kind, ctx->stream));
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_bright.p, brightness, (size_t)n * 8, kind, ctx->stream));
+    // half sizes exactly as the reference: int(img_shape[1] / 2), int(img_shape[0] / 2)
+    const double half_w = (double)(img_w / 2), half_h = (double)(img_h / 2);
+    star_rays_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(
+        ctx->s_xy.as<double>(), n, half_w, half_h, focal_px, ctx->s_rays.as<double>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+  }
+  ctx->star_off.assign(star_offsets, star_offsets + n_images + 1);
+  ctx->img_w = img_w;
+  ctx->img_h = img_h;
+  ctx->focal = focal_px;
+  // polygon banks measured earlier stay valid (they hold their own copies); re-measure an
+  // image after changing its stars.
+  if (ctx->poly.size() < (size_t)n_images) ctx->poly.resize((size_t)n_images);
+  return SSP_OK;
+}
+
+int ssp_fetch_star_rays(ssp_ctx* ctx, double* rays, int64_t capacity_stars, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, !ctx->star_off.empty(), SSP_ERR_STATE, "ssp_fetch_star_rays: no star bank");
+  const long long n = ctx->star_off.back();
+  SSP_REQUIRE(ctx, capacity_stars >= n, SSP_ERR_CAPACITY, "ssp_fetch_star_rays: capacity too small");
+  SSP_REQUIRE(ctx, rays != nullptr || n == 0, SSP_ERR_INVALID, "ssp_fetch_star_rays: NULL buffer");
+  if (n > 0)
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(rays, ctx->s_rays.p, (size_t)n * 24, from_device_kind(mem_kind),
+                                      ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+static int ensure_poly_image(ssp_ctx* ctx, int image, const char* who, bool need_stars) {
+  // polygon banks can also be loaded without a star bank (ssp_polygon_upload_features)
+  SSP_REQUIRE(ctx, image >= 0 && image < (1 << 20), SSP_ERR_INVALID, "%s: bad image index %d", who,
+              image);
+  if (need_stars)
+    SSP_REQUIRE(ctx, image < (int)ctx->star_off.size() - 1, SSP_ERR_INVALID,
+                "%s: image %d is not in the star bank", who, image);
+  if ((size_t)image >= ctx->poly.size()) ctx->poly.resize((size_t)image + 1);
+  return SSP_OK;
+}
+
+int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int64_t n_candidates,
+                        double min_side_px, int mem_kind, uint8_t* status, int64_t* n_valid) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, !ctx->star_off.empty(), SSP_ERR_STATE, "ssp_polygon_measure: no star bank");
+  if (int rc = ensure_poly_image(ctx, image, "ssp_polygon_measure", true)) return rc;
+  SSP_REQUIRE(ctx, n_candidates >= 0 && n_candidates < (1LL << 31) - 1024, SSP_ERR_INVALID,
+              "ssp_polygon_measure: bad candidate count");
+  SSP_REQUIRE(ctx, n_candidates == 0 || candidates != nullptr, SSP_ERR_INVALID,
+              "ssp_polygon_measure: NULL candidates");
+  PolyImage& pi = ctx->poly[(size_t)image];
+  const long long n = n_candidates;
+  ctx->p_n_matches = -1;
+  if (n == 0) {
+    pi.count = 0;
+    pi.has_raw = true;
+    if (n_valid) *n_valid = 0;
+    return SSP_OK;
+  }
+  const long long s0 = ctx->star_off[(size_t)image];
+  StarView sv;
+  sv.xy = ctx->s_xy.as<double>() + 2 * s0;
+  sv.bright = ctx->s_bright.as<double>() + s0;
+  sv.rays = ctx->s_rays.as<double>() + 3 * s0;
+  sv.n = (int)(ctx->star_off[(size_t)image + 1] - s0);
+
+  SSP_CUDA_TRY(ctx, ctx->p_cand.ensure((size_t)n * 20));
+  SSP_CUDA_TRY(ctx, ctx->p_status.ensure((size_t)n + 16));
+  SSP_CUDA_TRY(ctx, ctx->p_scan.ensure((size_t)n * 4 + (size_t)(n + 1) * 8 + 64));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_idx.ensure((size_t)n * 20));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_angle.ensure((size_t)n * 40));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_side.ensure((size_t)n * 40));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_bright.ensure((size_t)n * 40));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_feat.ensure((size_t)n * 120));
+  SSP_CUDA_TRY(ctx, pi.star_idx.ensure((size_t)n * 20));
+  SSP_CUDA_TRY(ctx, pi.angle.ensure((size_t)n * 40));
+  SSP_CUDA_TRY(ctx, pi.side.ensure((size_t)n * 40));
+  SSP_CUDA_TRY(ctx, pi.bright.ensure((size_t)n * 40));
+  SSP_CUDA_TRY(ctx, pi.feat.ensure((size_t)n * 120));
+  // p_scan layout: [n_domain int][pad][offsets (n+1) int64][flags n int]
+  int* d_ndomain = ctx->p_scan.as<int>();
+  long long* d_pos = reinterpret_cast<long long*>(ctx->p_scan.as<char>() + 16);
+  int* d_flags = reinterpret_cast<int*>(ctx->p_scan.as<char>() + 16 + (size_t)(n + 1) * 8);
+  SSP_CUDA_TRY(ctx, cudaMemsetAsync(d_ndomain, 0, 16, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_cand.p, candidates, (size_t)n * 20,
+                                    to_device_kind(mem_kind), ctx->stream));
+  const unsigned blocks = (unsigned)((n + 127) / 128);
+  poly_measure_kernel<<<blocks, 128, 0, ctx->stream>>>(
+      sv, ctx->p_cand.as<int>(), n, min_side_px, ctx->p_status.as<unsigned char>(), d_flags,
+      d_ndomain, ctx->p_tmp_idx.as<int>(), ctx->p_tmp_angle.as<double>(),
+      ctx->p_tmp_side.as<double>(), ctx->p_tmp_bright.as<double>(), ctx->p_tmp_feat.as<double>());
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(d_flags, (int)n, d_pos);
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  poly_scatter_kernel<<<blocks, 128, 0, ctx->stream>>>(
+      d_flags, d_pos, n, ctx->p_tmp_idx.as<int>(), ctx->p_tmp_angle.as<double>(),
+      ctx->p_tmp_side.as<double>(), ctx->p_tmp_bright.as<double>(), ctx->p_tmp_feat.as<double>(),
+      pi.star_idx.as<int>(), pi.angle.as<double>(), pi.side.as<double>(), pi.bright.as<double>(),
+      pi.feat.as<double>());
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  long long count = 0;
+  int n_domain = 0;
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&count, d_pos + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&n_domain, d_ndomain, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (status)
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(status, ctx->p_status.p, (size_t)n, cudaMemcpyDeviceToHost,
+                                      ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  pi.count = count;
+  pi.has_raw = true;
+  if (n_valid) *n_valid = count;
+  if (n_domain > 0)
+    return fail(ctx, SSP_ERR_DOMAIN,
+                "ssp_polygon_measure: %d candidate(s) of image %d gave |acos argument| > 1 "
+                "(the reference raises ValueError at custom_bf_polygon_matcher.py:134)",
+                n_domain, image);
+  return SSP_OK;
+}
+
+int ssp_polygon_count(ssp_ctx* ctx, int image, int64_t* n_polygons) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  SSP_REQUIRE(ctx, image >= 0 && (size_t)image < ctx->poly.size() && ctx->poly[(size_t)image].count >= 0,
+              SSP_ERR_STATE, "ssp_polygon_count: image %d has no polygon bank", image);
+  if (n_polygons) *n_polygons = ctx->poly[(size_t)image].count;
+  return SSP_OK;
+}
+
+int ssp_polygon_fetch(ssp_ctx* ctx, int image, int32_t* star_idx, double* angle, double* side,
+                      double* brightness, double* feat, int64_t capacity, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, image >= 0 && (size_t)image < ctx->poly.size() && ctx->poly[(size_t)image].count >= 0,
+              SSP_ERR_STATE, "ssp_polygon_fetch: image %d has no polygon bank", image);
+  PolyImage& pi = ctx->poly[(size_t)image];
+  const long long n = pi.count;
+  SSP_REQUIRE(ctx, capacity >= n, SSP_ERR_CAPACITY, "ssp_polygon_fetch: capacity %lld < %lld",
+              (long long)capacity, n);
+  SSP_REQUIRE(ctx, pi.has_raw || (angle == nullptr && side == nullptr && brightness == nullptr),
+              SSP_ERR_STATE,
+              "ssp_polygon_fetch: image %d was loaded with ssp_polygon_upload_features, raw "
+              "measures are not available", image);
+  if (n > 0) {
+    const cudaMemcpyKind kind = from_device_kind(mem_kind);
+    if (star_idx && pi.star_idx.p)
+      SSP_CUDA_TRY(ctx, cudaMemcpyAsync(star_idx, pi.star_idx.p, (size_t)n * 20, kind, ctx->stream));
+    if (angle) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(angle, pi.angle.p, (size_t)n * 40, kind, ctx->stream));
+    if (side) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(side, pi.side.p, (size_t)n * 40, kind, ctx->stream));
+    if (brightness)
+      SSP_CUDA_TRY(ctx, cudaMemcpyAsync(brightness, pi.bright.p, (size_t)n * 40, kind, ctx->stream));
+    if (feat) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(feat, pi.feat.p, (size_t)n * 120, kind, ctx->stream));
+  }
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+int ssp_polygon_upload_features(ssp_ctx* ctx, int image, const double* feat,
+                                const int32_t* star_idx, int64_t n_polygons, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  if (int rc = ensure_poly_image(ctx, image, "ssp_polygon_upload_features", false)) return rc;
+  SSP_REQUIRE(ctx, n_polygons >= 0 && n_polygons < (1LL << 31) - 1024, SSP_ERR_INVALID,
+              "ssp_polygon_upload_features: bad polygon count");
+  SSP_REQUIRE(ctx, n_polygons == 0 || feat != nullptr, SSP_ERR_INVALID,
+              "ssp_polygon_upload_features: NULL features");
+  PolyImage& pi = ctx->poly[(size_t)image];
+  const cudaMemcpyKind kind = to_device_kind(mem_kind);
+  SSP_CUDA_TRY(ctx, pi.feat.ensure((size_t)n_polygons * 120 + 16));
+  if (n_polygons > 0)
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(pi.feat.p, feat, (size_t)n_polygons * 120, kind, ctx->stream));
+  if (star_idx) {
+    SSP_CUDA_TRY(ctx, pi.star_idx.ensure((size_t)n_polygons * 20 + 16));
+    if (n_polygons > 0)
+      SSP_CUDA_TRY(ctx, cudaMemcpyAsync(pi.star_idx.p, star_idx, (size_t)n_polygons * 20, kind,
+                                        ctx->stream));
+  } else {
+    pi.star_idx.release();
+  }
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  pi.count = n_polygons;
+  pi.has_raw = false;
+  ctx->p_n_matches = -1;
+  return SSP_OK;
+}
+
+int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, double threshold,
+                            int shift_mode, int precision, int64_t* match_offsets) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, n_pairs >= 0 && (n_pairs == 0 || pairs != nullptr), SSP_ERR_INVALID,
+              "ssp_polygon_match_pairs: bad pair list");
+  SSP_REQUIRE(ctx, match_offsets != nullptr, SSP_ERR_INVALID,
+              "ssp_polygon_match_pairs: match_offsets is NULL");
+  SSP_REQUIRE(ctx, shift_mode == SSP_SHIFT_CANONICAL || shift_mode == SSP_SHIFT_MIN_OVER_SHIFTS,
+              SSP_ERR_INVALID, "ssp_polygon_match_pairs: unknown shift mode %d", shift_mode);
+  SSP_REQUIRE(ctx, precision == SSP_PRECISION_FP64 || precision == SSP_PRECISION_FP32,
+              SSP_ERR_INVALID, "ssp_polygon_match_pairs: unknown precision %d", precision);
+  ctx->p_n_matches = -1;
+  ctx->p_launches = 0;
+  ctx->p_main_ms = 0.f;
+  ctx->p_evaluations = 0;
+  ctx->p_match_offsets.assign((size_t)n_pairs + 1, 0);
+  if (n_pairs == 0) {
+    match_offsets[0] = 0;
+    ctx->p_n_matches = 0;
+    ctx->p_total_rows = 0;
+    return SSP_OK;
+  }
+  std::vector<PolyPair> pp((size_t)n_pairs);
+  long long rows = 0;
+  int max_p1 = 0;
+  for (int p = 0; p < n_pairs; ++p) {
+    const int i1 = pairs[2 * p], i2 = pairs[2 * p + 1];
+    SSP_REQUIRE(ctx, i1 >= 0 && (size_t)i1 < ctx->poly.size() && ctx->poly[(size_t)i1].count >= 0 &&
+                         i2 >= 0 && (size_t)i2 < ctx->poly.size() && ctx->poly[(size_t)i2].count >= 0,
+                SSP_ERR_STATE, "ssp_polygon_match_pairs: pair %d = (%d, %d) has no polygon bank", p,
+                i1, i2);
+    pp[p].f1 = ctx->poly[(size_t)i1].feat.as<double>();
+    pp[p].f2 = ctx->poly[(size_t)i2].feat.as<double>();
+    pp[p].p1 = (int)ctx->poly[(size_t)i1].count;
+    pp[p].p2 = (int)ctx->poly[(size_t)i2].count;
+    pp[p].out_row = rows;
+    rows += pp[p].p1;
+    max_p1 = pp[p].p1 > max_p1 ? pp[p].p1 : max_p1;
+    ctx->p_evaluations += (long long)pp[p].p1 * pp[p].p2;
+  }
+  ctx->p_total_rows = rows;
+  SSP_CUDA_TRY(ctx, ctx->p_pairs.ensure(pp.size() * sizeof(PolyPair)));
+  SSP_CUDA_TRY(ctx, ctx->p_argmin.ensure((size_t)(rows + 1) * 4));
+  SSP_CUDA_TRY(ctx, ctx->p_mindist.ensure((size_t)(rows + 1) * 8));
+  SSP_CUDA_TRY(ctx, ctx->p_counts.ensure((size_t)n_pairs * 4));
+  SSP_CUDA_TRY(ctx, ctx->p_offsets.ensure(((size_t)n_pairs + 1) * 8));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_pairs.p, pp.data(), pp.size() * sizeof(PolyPair),
+                                    cudaMemcpyHostToDevice, ctx->stream));
+  if (max_p1 > 0) {
+    dim3 grid((unsigned)n_pairs, (unsigned)((max_p1 + PC_THREADS - 1) / PC_THREADS));
+    SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    const PolyPair* dp = ctx->p_pairs.as<PolyPair>();
+    int* am = ctx->p_argmin.as<int>();
+    double* md = ctx->p_mindist.as<double>();
+    const bool ms = (shift_mode == SSP_SHIFT_MIN_OVER_SHIFTS);
+    if (precision == SSP_PRECISION_FP64) {
+      if (ms) poly_compare_f64_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+      else poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+    } else {
+      if (ms) poly_compare_f32_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+      else poly_compare_f32_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+    }
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->p_launches += 1;
+  }
+  poly_count_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
+      ctx->p_pairs.as<PolyPair>(), ctx->p_mindist.as<double>(), threshold, ctx->p_counts.as<int>());
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->p_counts.as<int>(), n_pairs,
+                                                  ctx->p_offsets.as<long long>());
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  ctx->p_launches += 2;
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_match_offsets.data(), ctx->p_offsets.p,
+                                    ((size_t)n_pairs + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  const long long total = ctx->p_match_offsets[(size_t)n_pairs];
+  SSP_CUDA_TRY(ctx, ctx->p_m1.ensure((size_t)(total + 1) * 4));
+  SSP_CUDA_TRY(ctx, ctx->p_m2.ensure((size_t)(total + 1) * 4));
+  SSP_CUDA_TRY(ctx, ctx->p_md.ensure((size_t)(total + 1) * 8));
+  poly_compact_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
+      ctx->p_pairs.as<PolyPair>(), ctx->p_argmin.as<int>(), ctx->p_mindist.as<double>(), threshold,
+      ctx->p_offsets.as<long long>(), ctx->p_m1.as<int>(), ctx->p_m2.as<int>(),
+      ctx->p_md.as<double>());
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  ctx->p_launches += 1;
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (max_p1 > 0) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->p_main_ms, ctx->ev0, ctx->ev1));
+  for (int p = 0; p <= n_pairs; ++p) match_offsets[p] = ctx->p_match_offsets[(size_t)p];
+  ctx->p_n_matches = total;
+  return SSP_OK;
+}
+
+int ssp_polygon_fetch_matches(ssp_ctx* ctx, int32_t* poly1, int32_t* poly2, double* dist,
+                              int64_t capacity, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, ctx->p_n_matches >= 0, SSP_ERR_STATE,
+              "ssp_polygon_fetch_matches: no completed ssp_polygon_match_pairs call");
+  const long long n = ctx->p_n_matches;
+  SSP_REQUIRE(ctx, capacity >= n, SSP_ERR_CAPACITY, "ssp_polygon_fetch_matches: capacity too small");
+  if (n == 0) return SSP_OK;
+  const cudaMemcpyKind kind = from_device_kind(mem_kind);
+  if (poly1) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(poly1, ctx->p_m1.p, (size_t)n * 4, kind, ctx->stream));
+  if (poly2) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(poly2, ctx->p_m2.p, (size_t)n * 4, kind, ctx->stream));
+  if (dist) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(dist, ctx->p_md.p, (size_t)n * 8, kind, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+int ssp_polygon_fetch_rowmin(ssp_ctx* ctx, int32_t* argmin, double* mindist, int64_t capacity_rows,
+                             int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, ctx->p_n_matches >= 0, SSP_ERR_STATE,
+              "ssp_polygon_fetch_rowmin: no completed ssp_polygon_match_pairs call");
+  const long long n = ctx->p_total_rows;
+  SSP_REQUIRE(ctx, capacity_rows >= n, SSP_ERR_CAPACITY, "ssp_polygon_fetch_rowmin: capacity too small");
+  if (n == 0) return SSP_OK;
+  const cudaMemcpyKind kind = from_device_kind(mem_kind);
+  if (argmin) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(argmin, ctx->p_argmin.p, (size_t)n * 4, kind, ctx->stream));
+  if (mindist) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(mindist, ctx->p_mindist.p, (size_t)n * 8, kind, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+int ssp_polygon_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
+                           int64_t* evaluations) {
+  if (!ctx) return SSP_ERR_INVALID;
+  if (n_launches) *n_launches = ctx->p_launches;
+  if (main_kernel_ms) *main_kernel_ms = ctx->p_main_ms;
+  if (evaluations) *evaluations = ctx->p_evaluations;
+  return SSP_OK;
+}
+
+}  // extern "C"

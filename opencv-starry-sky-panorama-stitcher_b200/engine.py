@@ -1,0 +1,333 @@
+"""Thin Python face of the C ABI: numpy in, numpy out, device work in libssp_b200.so.
+
+PyTorch is optional plumbing here (device buffers and the stream the kernels run on); every
+computation happens in the hand-written CUDA kernels behind `include/ssp_b200.h`.
+"""
+import ctypes
+from dataclasses import dataclass
+from fractions import Fraction
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _native as N
+
+
+class EngineError(RuntimeError):
+    """Any failure reported by libssp_b200.so other than the reference's own ValueError case."""
+
+
+@dataclass
+class HammingResult:
+    """Survivors of `hamming_match_pairs`: pair p owns [offsets[p], offsets[p+1])."""
+    offsets: np.ndarray      # int64 (n_pairs + 1)
+    query_idx: np.ndarray    # int32 (n_matches)  ascending inside each pair
+    train_idx: np.ndarray    # int32 (n_matches)
+    distance: np.ndarray     # int32 (n_matches)  Hamming distance (DMatch.distance as integer)
+    best2: Optional[np.ndarray] = None       # int32 (rows, 4) {idx1, d1, idx2, d2}
+    best2_offsets: Optional[np.ndarray] = None  # int64 (n_pairs + 1) row ranges into best2
+
+    def pair(self, p):
+        lo, hi = int(self.offsets[p]), int(self.offsets[p + 1])
+        return self.query_idx[lo:hi], self.train_idx[lo:hi], self.distance[lo:hi]
+
+
+@dataclass
+class PolygonMatchResult:
+    """Polygon matches of `polygon_match_pairs` (cbpm:1145-1152 `valid_polygon_matches_*`)."""
+    offsets: np.ndarray   # int64 (n_pairs + 1)
+    poly1: np.ndarray     # int32 row index in the first image's polygon bank
+    poly2: np.ndarray     # int32 argmin row in the second image's bank
+    dist: np.ndarray      # float64 polygon distance
+    argmin: Optional[np.ndarray] = None       # int32 per row of every pair (before threshold)
+    mindist: Optional[np.ndarray] = None      # float64
+    row_offsets: Optional[np.ndarray] = None  # int64 (n_pairs + 1)
+
+    def pair(self, p):
+        lo, hi = int(self.offsets[p]), int(self.offsets[p + 1])
+        return self.poly1[lo:hi], self.poly2[lo:hi], self.dist[lo:hi]
+
+
+_MODES = {"knn2_ratio": N.MODE_KNN2_RATIO, "crosscheck": N.MODE_CROSSCHECK}
+_VARIANTS = {"auto": N.HAMMING_AUTO, "popc": N.HAMMING_POPC, "popc_csa": N.HAMMING_POPC_CSA,
+             "tensor": N.HAMMING_TENSOR}
+
+
+def _ratio_terms(ratio):
+    """Lowe ratio as an exact integer fraction (0.75 -> (3, 4))."""
+    if isinstance(ratio, (tuple, list)):
+        num, den = int(ratio[0]), int(ratio[1])
+    else:
+        fr = Fraction(ratio)
+        if fr.denominator >= 1 << 20:
+            fr = Fraction(ratio).limit_denominator(4096)
+        num, den = fr.numerator, fr.denominator
+    if num <= 0 or den <= 0:
+        raise ValueError("ratio must be positive")
+    return num, den
+
+
+def _ptr(a):
+    return None if a is None else ctypes.c_void_p(a.ctypes.data)
+
+
+def _as_pairs(pairs):
+    arr = np.ascontiguousarray(np.asarray(pairs, dtype=np.int32).reshape(-1, 2))
+    return arr
+
+
+class Engine:
+    """One engine context per matcher instance and CUDA device."""
+
+    def __init__(self, device: int = 0, stream: Optional[int] = None):
+        self._lib = N.lib()
+        self._ctx = ctypes.c_void_p()
+        rc = self._lib.ssp_create(ctypes.byref(self._ctx), int(device))
+        if rc != N.OK:
+            msg = self._lib.ssp_last_error(None).decode()
+            self._ctx = None
+            raise EngineError(f"ssp_create failed ({rc}): {msg}")
+        self.device = int(device)
+        self._desc_offsets = None
+        self._star_offsets = None
+        self._bound = None  # keeps a bound torch tensor alive
+        if stream is not None:
+            self.set_stream(stream)
+
+    # -- lifetime -------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._lib.ssp_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc):
+        if rc == N.OK:
+            return
+        msg = self._lib.ssp_last_error(self._ctx).decode()
+        if rc == N.ERR_DOMAIN:
+            # the reference's math.acos raises ValueError("math domain error") (cbpm:134)
+            raise ValueError(f"math domain error: {msg}")
+        raise EngineError(f"libssp_b200 error {rc}: {msg}")
+
+    def set_stream(self, cuda_stream_handle: Optional[int]):
+        """Run subsequent work on this cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
+        self._check(self._lib.ssp_set_stream(self._ctx, ctypes.c_void_p(cuda_stream_handle or 0)))
+
+    def synchronize(self):
+        self._check(self._lib.ssp_synchronize(self._ctx))
+
+    def device_info(self):
+        sm, khz, mem = ctypes.c_int(), ctypes.c_int(), ctypes.c_int64()
+        self._check(self._lib.ssp_device_info(self._ctx, ctypes.byref(sm), ctypes.byref(khz),
+                                              ctypes.byref(mem)))
+        return {"sm_count": sm.value, "sm_clock_khz": khz.value, "hbm_bytes": mem.value}
+
+    # -- descriptor bank ------------------------------------------------------------------
+    @staticmethod
+    def pack_descriptors(descriptors: Sequence[np.ndarray]):
+        """list of uint8 (n_i, 32) -> (uint8 (sum n_i, 32) C-contiguous, int64 offsets)."""
+        offs = np.zeros(len(descriptors) + 1, dtype=np.int64)
+        for i, d in enumerate(descriptors):
+            d = np.asarray(d)
+            if d.size and (d.dtype != np.uint8 or d.ndim != 2 or d.shape[1] != 32):
+                raise ValueError(f"descriptor set {i}: expected uint8 (n, 32), got {d.dtype} {d.shape}")
+            offs[i + 1] = offs[i] + (d.shape[0] if d.size else 0)
+        bank = np.empty((int(offs[-1]), 32), dtype=np.uint8)
+        for i, d in enumerate(descriptors):
+            if offs[i + 1] > offs[i]:
+                bank[offs[i]:offs[i + 1]] = d
+        return bank, offs
+
+    def upload_descriptor_bank(self, descriptors, row_offsets=None):
+        """`descriptors`: list of uint8 (n_i, 32) arrays, or one packed (N, 32) array together
+        with `row_offsets`.  Copies host -> device."""
+        if row_offsets is None:
+            bank, offs = self.pack_descriptors(descriptors)
+        else:
+            bank = np.ascontiguousarray(descriptors, dtype=np.uint8).reshape(-1, 32)
+            offs = np.ascontiguousarray(row_offsets, dtype=np.int64)
+            if offs[-1] != bank.shape[0]:
+                raise ValueError("row_offsets[-1] must equal the number of descriptor rows")
+        self._check(self._lib.ssp_upload_descriptor_bank(self._ctx, _ptr(bank), _ptr(offs),
+                                                         len(offs) - 1, N.MEM_HOST))
+        self.synchronize()  # `bank` may be a temporary
+        self._desc_offsets = offs.copy()
+        self._bound = None
+
+    def bind_descriptor_bank(self, device_ptr: int, row_offsets, keepalive=None):
+        """Zero-copy: the bank already lives on this device (e.g. a torch uint8 tensor);
+        `keepalive` is held so the buffer outlives the binding."""
+        offs = np.ascontiguousarray(row_offsets, dtype=np.int64)
+        self._check(self._lib.ssp_bind_descriptor_bank(self._ctx, ctypes.c_void_p(device_ptr),
+                                                       _ptr(offs), len(offs) - 1))
+        self._desc_offsets = offs.copy()
+        self._bound = keepalive
+
+    # -- kernel 1 -------------------------------------------------------------------------
+    def hamming_match_pairs(self, pairs, mode="crosscheck", ratio=0.75, variant="auto",
+                            return_best2=False, fetch=True) -> HammingResult:
+        """All-pairs Hamming matching of image pairs (query image, train image).
+
+        mode="crosscheck"  == cv.BFMatcher(cv.NORM_HAMMING, crossCheck=True).match per pair
+                              (custom_bruteforce_matcher.py:193-199)
+        mode="knn2_ratio"  == knnMatch(k=2) + `m.distance < ratio * n.distance`
+                              (custom_bruteforce_matcher.py:160-172)
+        """
+        if self._desc_offsets is None:
+            raise EngineError("no descriptor bank uploaded")
+        p = _as_pairs(pairs)
+        num, den = _ratio_terms(ratio)
+        offs = np.zeros(p.shape[0] + 1, dtype=np.int64)
+        self._check(self._lib.ssp_hamming_match_pairs(
+            self._ctx, _ptr(p), p.shape[0], _MODES[mode], num, den, _VARIANTS[variant], _ptr(offs)))
+        n = int(offs[-1])
+        q = np.empty(n, dtype=np.int32)
+        t = np.empty(n, dtype=np.int32)
+        d = np.empty(n, dtype=np.int32)
+        if fetch:
+            self._check(self._lib.ssp_hamming_fetch_matches(self._ctx, _ptr(q), _ptr(t), _ptr(d), n,
+                                                            N.MEM_HOST))
+        res = HammingResult(offs, q, t, d)
+        if return_best2:
+            nq = (self._desc_offsets[1:] - self._desc_offsets[:-1])[p[:, 0]] if p.size else \
+                np.zeros(0, dtype=np.int64)
+            b_off = np.zeros(p.shape[0] + 1, dtype=np.int64)
+            np.cumsum(nq, out=b_off[1:])
+            b2 = np.empty((int(b_off[-1]), 4), dtype=np.int32)
+            self._check(self._lib.ssp_hamming_fetch_best2(self._ctx, _ptr(b2), b2.shape[0], N.MEM_HOST))
+            res.best2, res.best2_offsets = b2, b_off
+        return res
+
+    def hamming_last_stats(self):
+        n, ms, cmp_ = ctypes.c_int(), ctypes.c_float(), ctypes.c_int64()
+        self._check(self._lib.ssp_hamming_last_stats(self._ctx, ctypes.byref(n), ctypes.byref(ms),
+                                                     ctypes.byref(cmp_)))
+        return {"launches": n.value, "main_kernel_ms": ms.value, "comparisons": cmp_.value}
+
+    # -- kernel 2 -------------------------------------------------------------------------
+    def upload_star_bank(self, xy: Sequence[np.ndarray], brightness: Sequence[np.ndarray],
+                         img_w: int, img_h: int, focal_px: float):
+        """`xy[i]`: (n_i, 2) pixel coordinates of image i's stars (keypoints[n_orb:], cbpm:710);
+        `brightness[i]`: (n_i,) get_star_brightness values.  img_w/img_h = work image size."""
+        offs = np.zeros(len(xy) + 1, dtype=np.int64)
+        for i, a in enumerate(xy):
+            offs[i + 1] = offs[i] + len(a)
+        allxy = np.zeros((int(offs[-1]), 2), dtype=np.float64)
+        allb = np.zeros(int(offs[-1]), dtype=np.float64)
+        for i, (a, b) in enumerate(zip(xy, brightness)):
+            if len(a) != len(b):
+                raise ValueError(f"image {i}: {len(a)} stars but {len(b)} brightness values")
+            if len(a):
+                allxy[offs[i]:offs[i + 1]] = np.asarray(a, dtype=np.float64).reshape(-1, 2)
+                allb[offs[i]:offs[i + 1]] = np.asarray(b, dtype=np.float64)
+        self._check(self._lib.ssp_upload_star_bank(self._ctx, _ptr(allxy), _ptr(allb), _ptr(offs),
+                                                   len(offs) - 1, int(img_w), int(img_h),
+                                                   float(focal_px), N.MEM_HOST))
+        self.synchronize()
+        self._star_offsets = offs
+
+    def star_rays(self):
+        n = int(self._star_offsets[-1])
+        rays = np.empty((n, 3), dtype=np.float64)
+        self._check(self._lib.ssp_fetch_star_rays(self._ctx, _ptr(rays), n, N.MEM_HOST))
+        return rays
+
+    def polygon_measure(self, image: int, candidates, min_side_px: float = 5.0,
+                        return_status: bool = False):
+        """Measures candidate 5-star polygons of one image (cbpm:500-600 + :722-740) into the
+        engine's polygon bank.  Returns n_valid (and the per-candidate status)."""
+        cand = np.ascontiguousarray(np.asarray(candidates, dtype=np.int32).reshape(-1, 5))
+        status = np.empty(cand.shape[0], dtype=np.uint8) if return_status else None
+        n_valid = ctypes.c_int64()
+        self._check(self._lib.ssp_polygon_measure(self._ctx, int(image), _ptr(cand), cand.shape[0],
+                                                  float(min_side_px), N.MEM_HOST, _ptr(status),
+                                                  ctypes.byref(n_valid)))
+        return (n_valid.value, status) if return_status else n_valid.value
+
+    def polygon_count(self, image: int) -> int:
+        n = ctypes.c_int64()
+        self._check(self._lib.ssp_polygon_count(self._ctx, int(image), ctypes.byref(n)))
+        return n.value
+
+    def polygon_fetch(self, image: int, raw: bool = True):
+        """Polygon bank of one image as numpy arrays in the reference's layout."""
+        n = self.polygon_count(image)
+        out = {"star_idx": np.empty((n, 5), dtype=np.int32), "feat": np.empty((n, 15), dtype=np.float64)}
+        if raw:
+            for k in ("angle", "side", "brightness"):
+                out[k] = np.empty((n, 5), dtype=np.float64)
+        self._check(self._lib.ssp_polygon_fetch(
+            self._ctx, int(image), _ptr(out["star_idx"]), _ptr(out.get("angle")), _ptr(out.get("side")),
+            _ptr(out.get("brightness")), _ptr(out["feat"]), n, N.MEM_HOST))
+        return out
+
+    def polygon_upload_features(self, image: int, feat, star_idx=None):
+        f = np.ascontiguousarray(np.asarray(feat, dtype=np.float64).reshape(-1, 15))
+        s = None
+        if star_idx is not None:
+            s = np.ascontiguousarray(np.asarray(star_idx, dtype=np.int32).reshape(-1, 5))
+            if s.shape[0] != f.shape[0]:
+                raise ValueError("star_idx and feat row counts differ")
+        self._check(self._lib.ssp_polygon_upload_features(self._ctx, int(image), _ptr(f), _ptr(s),
+                                                          f.shape[0], N.MEM_HOST))
+
+    # -- kernel 3 -------------------------------------------------------------------------
+    def polygon_match_pairs(self, pairs, threshold: float = 0.1566, min_over_shifts: bool = False,
+                            fp32: bool = False, return_rowmin: bool = False) -> PolygonMatchResult:
+        """Per polygon of the first image the nearest polygon of the second (cbpm:992-1067), kept
+        iff distance < threshold (cbpm:1145-1148).  Defaults are the reference's parity mode."""
+        p = _as_pairs(pairs)
+        offs = np.zeros(p.shape[0] + 1, dtype=np.int64)
+        self._check(self._lib.ssp_polygon_match_pairs(
+            self._ctx, _ptr(p), p.shape[0], float(threshold),
+            N.SHIFT_MIN_OVER_SHIFTS if min_over_shifts else N.SHIFT_CANONICAL,
+            N.PRECISION_FP32 if fp32 else N.PRECISION_FP64, _ptr(offs)))
+        n = int(offs[-1])
+        m1 = np.empty(n, dtype=np.int32)
+        m2 = np.empty(n, dtype=np.int32)
+        md = np.empty(n, dtype=np.float64)
+        self._check(self._lib.ssp_polygon_fetch_matches(self._ctx, _ptr(m1), _ptr(m2), _ptr(md), n,
+                                                        N.MEM_HOST))
+        res = PolygonMatchResult(offs, m1, m2, md)
+        if return_rowmin:
+            rows = np.array([self.polygon_count(int(a)) for a in p[:, 0]], dtype=np.int64)
+            r_off = np.zeros(p.shape[0] + 1, dtype=np.int64)
+            np.cumsum(rows, out=r_off[1:])
+            am = np.empty(int(r_off[-1]), dtype=np.int32)
+            mn = np.empty(int(r_off[-1]), dtype=np.float64)
+            self._check(self._lib.ssp_polygon_fetch_rowmin(self._ctx, _ptr(am), _ptr(mn), am.shape[0],
+                                                           N.MEM_HOST))
+            res.argmin, res.mindist, res.row_offsets = am, mn, r_off
+        return res
+
+    def polygon_last_stats(self):
+        n, ms, ev = ctypes.c_int(), ctypes.c_float(), ctypes.c_int64()
+        self._check(self._lib.ssp_polygon_last_stats(self._ctx, ctypes.byref(n), ctypes.byref(ms),
+                                                     ctypes.byref(ev)))
+        return {"launches": n.value, "main_kernel_ms": ms.value, "evaluations": ev.value}
+
+    # -- row N1 ---------------------------------------------------------------------------
+    def star_brightness(self, gray: np.ndarray, centers_xy, disc_dxdy, top_k: int = 10):
+        """get_star_brightness (image_processors.py:222-254) for many stars of one grey image."""
+        g = np.ascontiguousarray(gray, dtype=np.uint8)
+        if g.ndim != 2:
+            raise ValueError("gray must be (h, w) uint8")
+        c = np.ascontiguousarray(np.asarray(centers_xy, dtype=np.int32).reshape(-1, 2))
+        d = np.ascontiguousarray(np.asarray(disc_dxdy, dtype=np.int32).reshape(-1, 2))
+        out = np.empty(c.shape[0], dtype=np.int32)
+        self._check(self._lib.ssp_star_brightness(self._ctx, _ptr(g), g.shape[0], g.shape[1], _ptr(c),
+                                                  c.shape[0], _ptr(d), d.shape[0], int(top_k),
+                                                  _ptr(out), N.MEM_HOST))
+        return out

@@ -1,0 +1,140 @@
+"""Parity of CUDA kernel 1 (through the C ABI) with the oracle and with cv2.BFMatcher: bit-exact
+distances, tie-broken indices and survivor sets."""
+import cv2
+import numpy as np
+import pytest
+
+from oracle import hamming_oracle as ho
+import ssp_b200
+from ssp_b200 import synthetic as synth
+
+pytestmark = pytest.mark.gpu
+VARIANTS = ["popc", "popc_csa"]
+
+
+def oracle_pairs(sets, pairs, mode):
+    out = []
+    for a, b in pairs:
+        if mode == "crosscheck":
+            out.append(ho.crosscheck(sets[a], sets[b]))
+        else:
+            out.append(ho.ratio_survivors(ho.knn2(sets[a], sets[b])))
+    return out
+
+
+def assert_result_equals(res, expected):
+    for p, (mq, mt, md) in enumerate(expected):
+        q, t, d = res.pair(p)
+        np.testing.assert_array_equal(q, mq, err_msg=f"pair {p} queryIdx")
+        np.testing.assert_array_equal(t, mt, err_msg=f"pair {p} trainIdx")
+        np.testing.assert_array_equal(d, md, err_msg=f"pair {p} distance")
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_golden_vectors_from_cv2(engine, golden, variant):
+    g = golden("hamming_golden.npz")
+    for name in g["case_names"]:
+        q, t = g[f"{name}_q"], g[f"{name}_t"]
+        engine.upload_descriptor_bank([q, t])
+        res = engine.hamming_match_pairs([(0, 1)], mode="knn2_ratio", variant=variant, return_best2=True)
+        np.testing.assert_array_equal(res.best2, g[f"{name}_knn2"], err_msg=f"{name} knn2")
+        res = engine.hamming_match_pairs([(0, 1)], mode="crosscheck", variant=variant)
+        got = np.stack(res.pair(0), axis=1)
+        np.testing.assert_array_equal(got, g[f"{name}_cross"], err_msg=f"{name} crosscheck")
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+@pytest.mark.parametrize("mode", ["crosscheck", "knn2_ratio"])
+def test_ragged_multi_pair_batch_against_oracle(engine, variant, mode):
+    sizes = [0, 1, 2, 255, 256, 257, 1023, 1024, 1025, 1500]
+    tie = synth.tie_stress_bank(len(sizes), max(sizes), seed=7)
+    sets = [tie[i][:n] for i, n in enumerate(sizes)]
+    pairs = [(i, j) for i in range(len(sizes)) for j in range(len(sizes)) if i != j]
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs(pairs, mode=mode, variant=variant)
+    assert_result_equals(res, oracle_pairs(sets, pairs, mode))
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_best2_records_against_oracle_with_planted_matches(engine, variant):
+    sets = synth.descriptor_bank(3, 3000, seed=4, world=4000)
+    engine.upload_descriptor_bank(sets)
+    pairs = [(0, 1), (1, 2), (2, 0)]
+    res = engine.hamming_match_pairs(pairs, mode="knn2_ratio", variant=variant, return_best2=True)
+    for p, (a, b) in enumerate(pairs):
+        lo, hi = res.best2_offsets[p], res.best2_offsets[p + 1]
+        np.testing.assert_array_equal(res.best2[lo:hi], ho.knn2(sets[a], sets[b]))
+    assert res.offsets[-1] > 500  # planted matches survive the ratio test
+
+
+def test_against_installed_cv2_bfmatcher(engine):
+    sets = synth.descriptor_bank(2, 2000, seed=9, world=2500)
+    bf = ssp_b200.BFMatcher(cv2.NORM_HAMMING, crossCheck=True, engine=engine)
+    ours = bf.match(cv2.UMat(sets[0]), cv2.UMat(sets[1]))
+    theirs = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True).match(cv2.UMat(sets[0]), cv2.UMat(sets[1]))
+    assert [(m.queryIdx, m.trainIdx, m.imgIdx, m.distance) for m in ours] == \
+           [(m.queryIdx, m.trainIdx, m.imgIdx, m.distance) for m in theirs]
+    knn_ours = ssp_b200.BFMatcher(cv2.NORM_HAMMING, engine=engine).knnMatch(sets[0], sets[1], k=2)
+    knn_theirs = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(sets[0], sets[1], k=2)
+    assert [[(m.queryIdx, m.trainIdx, m.distance) for m in row] for row in knn_ours] == \
+           [[(m.queryIdx, m.trainIdx, m.distance) for m in row] for row in knn_theirs]
+
+
+def test_real_orb_fixture_all_210_pairs(engine, golden):
+    g = golden("orb_forest_c1.npz")
+    offs = g["offsets"]
+    sets = [g["descriptors"][offs[i]:offs[i + 1]] for i in range(len(offs) - 1)]
+    pairs = synth.all_pairs(len(sets))
+    assert len(pairs) == 210
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs(pairs, mode="crosscheck")
+    assert_result_equals(res, oracle_pairs(sets, pairs, "crosscheck"))
+    counts = np.diff(res.offsets)
+    assert 100 < counts.min() and counts.max() < 400  # the author's runs: 149-294 per pair
+
+
+def test_full_size_pair_50k_against_oracle_and_properties(engine):
+    """One C3-sized pair (50 000 x 50 000) against the C oracle, plus size-independent
+    properties on a second pair: mirror symmetry of cross-check and distance recomputation."""
+    sets = synth.descriptor_bank(3, 50_000, seed=0)
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs([(0, 1), (1, 0), (1, 2)], mode="crosscheck")
+    mq, mt, md = ho.crosscheck(sets[0], sets[1])
+    q, t, d = res.pair(0)
+    np.testing.assert_array_equal(q, mq)
+    np.testing.assert_array_equal(t, mt)
+    np.testing.assert_array_equal(d, md)
+    # (1,0) is the mirror of (0,1): same couples with roles swapped
+    q2, t2, d2 = res.pair(1)
+    order = np.argsort(t2, kind="stable")
+    np.testing.assert_array_equal(t2[order], q)
+    np.testing.assert_array_equal(q2[order], t)
+    np.testing.assert_array_equal(d2[order], d)
+    # reported distances are the true Hamming distances of the reported couples
+    q3, t3, d3 = res.pair(2)
+    x = np.unpackbits(sets[1][q3] ^ sets[2][t3], axis=1).sum(axis=1)
+    np.testing.assert_array_equal(x, d3)
+    assert len(q) > 10_000
+
+
+def test_full_size_knn2_ratio_sampled_rows(engine):
+    sets = synth.descriptor_bank(2, 50_000, seed=0)
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs([(0, 1)], mode="knn2_ratio", return_best2=True)
+    rows = np.random.default_rng(1).choice(50_000, size=256, replace=False)
+    np.testing.assert_array_equal(res.best2[rows], ho.knn2(sets[0][rows], sets[1]))
+    mq, mt, md = ho.ratio_survivors(res.best2)
+    np.testing.assert_array_equal(res.query_idx, mq)
+    np.testing.assert_array_equal(res.train_idx, mt)
+    np.testing.assert_array_equal(res.distance, md)
+
+
+def test_errors_are_loud(engine):
+    engine.upload_descriptor_bank([np.zeros((4, 32), np.uint8)])
+    with pytest.raises(ssp_b200.EngineError, match="out of range"):
+        engine.hamming_match_pairs([(0, 3)])
+    assert engine.hamming_match_pairs([]).offsets.tolist() == [0]
+    fresh = ssp_b200.Engine(0)
+    with pytest.raises(ssp_b200.EngineError, match="no descriptor bank"):
+        fresh.hamming_match_pairs([(0, 0)])
+    fresh.close()
