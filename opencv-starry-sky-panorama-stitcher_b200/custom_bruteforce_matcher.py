@@ -251,7 +251,11 @@ class CustomBruteForceMatcher:
         combos = list(itertools.combinations(range(n), 2))
 
         dummy = cv.detail.MatchesInfo()
-        dummy.H = None
+        # The reference assigns H = None (:603).  Under cv2 4.13 a Python-built MatchesInfo whose
+        # H was never given an array makes detail_HomographyBasedEstimator.apply segfault
+        # (cv2's own apply2() dummies do not); an empty float64 array is the same "no homography"
+        # (H.empty() in C++) and is safe.  Host glue only, outside the CUDA path.
+        dummy.H = np.zeros((0, 0), np.float64)
         dummy.confidence = 0.0
         dummy.dst_img_idx = -1
         dummy.inliers_mask = tuple()
