@@ -76,7 +76,7 @@ int ssp_destroy(ssp_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   ssp::DevBuf* bufs[] = {&ctx->desc_owned, &ctx->h_work,      &ctx->h_pairs,     &ctx->h_best2,
                          &ctx->h_counts,   &ctx->h_offsets,   &ctx->h_mq,        &ctx->h_mt,
-                         &ctx->h_md,       &ctx->h_expanded,  &ctx->s_xy,        &ctx->s_bright,
+                         &ctx->h_md,       &ctx->h_expanded,  &ctx->h_tc_work,  &ctx->h_tc_err,  &ctx->s_xy,        &ctx->s_bright,
                          &ctx->s_rays,     &ctx->p_cand,      &ctx->p_status,    &ctx->p_scan,
                          &ctx->p_tmp_idx,  &ctx->p_tmp_angle, &ctx->p_tmp_side,  &ctx->p_tmp_bright,
                          &ctx->p_tmp_feat, &ctx->p_pairs,     &ctx->p_argmin,    &ctx->p_mindist,
@@ -154,7 +154,7 @@ int ssp_upload_descriptor_bank(ssp_ctx* ctx, const uint8_t* desc, const int64_t*
   ctx->d_desc = ctx->desc_owned.as<uint8_t>();
   ctx->row_off.assign(row_offsets, row_offsets + n_images + 1);
   ctx->h_n_matches = -1;
-  ctx->h_expanded.release();
+  ctx->h_expanded_valid = false;
   return SSP_OK;
 }
 
@@ -171,7 +171,7 @@ int ssp_bind_descriptor_bank(ssp_ctx* ctx, const uint8_t* d_desc, const int64_t*
   ctx->d_desc = d_desc;
   ctx->row_off.assign(row_offsets, row_offsets + n_images + 1);
   ctx->h_n_matches = -1;
-  ctx->h_expanded.release();
+  ctx->h_expanded_valid = false;
   return SSP_OK;
 }
 

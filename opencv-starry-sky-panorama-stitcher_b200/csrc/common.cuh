@@ -53,6 +53,7 @@ struct HammingWork {
   int nq;
   int nt;
   long long out_row;  // first row of this item in the best2 scratch
+  int qi, ti;         // image indices of q and t in the bank
 };
 
 // One image pair for the finalize kernels.
@@ -100,7 +101,11 @@ struct ssp_ctx {
 
   // Hamming scratch / results
   ssp::DevBuf h_work, h_pairs, h_best2, h_counts, h_offsets, h_mq, h_mt, h_md;
-  ssp::DevBuf h_expanded;  // 0/1 int8 expansion of the bank for the tensor variant
+  ssp::DevBuf h_expanded;  // +-1 int8 expansion of the bank for the tensor variant (swizzled tiles)
+  ssp::DevBuf h_tc_work, h_tc_err;
+  bool h_expanded_valid = false;
+  std::vector<long long> exp_byte_off;  // per image byte offset into h_expanded
+  std::vector<int> exp_rows_pad;
   std::vector<long long> h_match_offsets;
   long long h_total_rows = 0;   // forward rows of the last call
   long long h_n_matches = -1;

@@ -305,6 +305,8 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
     f.nq = nq;
     f.nt = nt;
     f.out_row = rows;
+    f.qi = qi;
+    f.ti = ti;
     hp[p].fwd_row = rows;
     hp[p].rev_row = -1;
     hp[p].nq = nq;
@@ -320,6 +322,8 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
       r.nq = nt;
       r.nt = nq;
       r.out_row = rev_cursor;
+      r.qi = ti;
+      r.ti = qi;
       hp[p].rev_row = rev_cursor;
       rev_cursor += nt;
       if (nt > 0) work.push_back(r);
@@ -363,7 +367,7 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
       SSP_CUDA_TRY(ctx, e);
       ctx->h_launches += 1;
     }
-    SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    if (v != SSP_HAMMING_TENSOR) SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   }
 
   hamming_count_kernel<<<n_pairs, FIN_THREADS, 0, ctx->stream>>>(

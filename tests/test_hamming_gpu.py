@@ -9,7 +9,7 @@ import ssp_b200
 from ssp_b200 import synthetic as synth
 
 pytestmark = pytest.mark.gpu
-VARIANTS = ["popc", "popc_csa"]
+VARIANTS = ["popc", "popc_csa", "tensor"]
 
 
 def oracle_pairs(sets, pairs, mode):

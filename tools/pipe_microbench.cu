@@ -26,8 +26,12 @@ __global__ void __launch_bounds__(1024) bench(uint32_t seed, unsigned long long*
 #pragma unroll
     for (int i = 0; i < CHAINS; ++i) {
       if (OP == 0) {  // POPC (result fed back so the chain cannot be folded)
-        asm volatile("popc.b32 %0, %1;" : "=r"(w[i]) : "r"(v[i]));
-        v[i] = w[i];
+        // popc followed by an xor with a live value: the xor issues on the (4x wider) alu pipe,
+        // so the chain is paced by POPC and cannot be folded away
+        uint32_t p;
+        asm volatile("popc.b32 %0, %1;" : "=r"(p) : "r"(v[i]));
+        v[i] = p ^ w[i];
+        w[i] += seed;
       } else if (OP == 1) {  // LOP3
         asm volatile("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(v[i]) : "r"(v[i]), "r"(w[i]), "r"(seed));
       } else if (OP == 2) {  // IMAD
