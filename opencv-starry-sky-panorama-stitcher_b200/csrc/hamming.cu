@@ -239,7 +239,7 @@ static cudaError_t launch_popc(ssp_ctx* ctx, int n_work, int max_nq) {
 
 // implemented in hamming_tensor.cu
 cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& work, int k,
-                                  std::string* why_not);
+                                  bool two_cta, std::string* why_not);
 
 }  // namespace ssp
 
@@ -260,7 +260,7 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
               "ssp_hamming_match_pairs: match_offsets is NULL");
   SSP_REQUIRE(ctx, mode == SSP_MODE_KNN2_RATIO || mode == SSP_MODE_CROSSCHECK, SSP_ERR_INVALID,
               "ssp_hamming_match_pairs: unknown mode %d", mode);
-  SSP_REQUIRE(ctx, variant >= SSP_HAMMING_AUTO && variant <= SSP_HAMMING_TENSOR, SSP_ERR_INVALID,
+  SSP_REQUIRE(ctx, variant >= SSP_HAMMING_AUTO && variant <= SSP_HAMMING_TENSOR_1CTA, SSP_ERR_INVALID,
               "ssp_hamming_match_pairs: unknown variant %d", variant);
   if (mode == SSP_MODE_KNN2_RATIO)
     SSP_REQUIRE(ctx, ratio_num > 0 && ratio_den > 0, SSP_ERR_INVALID,
@@ -348,9 +348,10 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
     int v = variant;
     if (v == SSP_HAMMING_AUTO) v = SSP_HAMMING_POPC_CSA;
     SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    if (v == SSP_HAMMING_TENSOR) {
+    const bool tensor = (v == SSP_HAMMING_TENSOR || v == SSP_HAMMING_TENSOR_1CTA);
+    if (tensor) {
       std::string why;
-      cudaError_t e = launch_hamming_tensor(ctx, work, k, &why);
+      cudaError_t e = launch_hamming_tensor(ctx, work, k, v == SSP_HAMMING_TENSOR, &why);
       if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
       SSP_CUDA_TRY(ctx, e);
     } else {
@@ -367,7 +368,7 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
       SSP_CUDA_TRY(ctx, e);
       ctx->h_launches += 1;
     }
-    if (v != SSP_HAMMING_TENSOR) SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    if (!tensor) SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   }
 
   hamming_count_kernel<<<n_pairs, FIN_THREADS, 0, ctx->stream>>>(

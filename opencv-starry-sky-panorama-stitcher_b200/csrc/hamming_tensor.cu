@@ -372,6 +372,264 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
   }
 }
 
+// ================================================================================================
+// 2-CTA variant (cta_group::2): a CTA pair shares every train tile.  Each CTA keeps its own 128
+// query rows (M = 256 across the pair) and stages only HALF of the 256 train rows of a tile
+// (N split), so L2 -> SM traffic and the shared-memory reads of the B operand are halved versus
+// the 1-CTA kernel, which ncu showed L2-bound (profiles/r01_ncu_hamming_tcgen05_1cta.txt:
+// tensor pipe 63 %, 10.3 TB/s crossbar reads).  The leader CTA's MMA thread issues for both
+// SMs; each CTA's accumulator (its 128 rows x 256 columns) lands in its own TMEM and is drained
+// by its own epilogue warpgroups exactly as in the 1-CTA kernel.
+//
+// Synchronisation.  Every CTA loads into its own shared memory and completes its own tx
+// barriers; the peer's warp 9 forwards "my half has landed" to the leader with a remote
+// mbarrier arrive, tcgen05.commit multicasts "stage free" / "accumulator full" / "A free" to
+// both CTAs, and both CTAs' epilogue warps arrive (locally / remotely) on the leader's
+// "accumulator empty" barrier.
+constexpr int TC2_STAGES = 4;
+constexpr int TC2_B_BYTES = (TC_N / 2) * TC_ROW_BYTES;  // 32 KB: this CTA's half of a train tile
+constexpr uint32_t TC2_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_N >> 3) << 17) |
+                               ((uint32_t)(256 >> 4) << 24);
+constexpr size_t TC2_SMEM_BYTES = 2 * (size_t)TC_A_BYTES + (size_t)TC2_STAGES * TC2_B_BYTES + 256 +
+                                  2 * TC_M * sizeof(uint2);
+
+__device__ __forceinline__ bool tc2_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+      " selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void tc2_wait(uint64_t* bar, uint32_t parity) {
+  if (tc2_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!tc2_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) __trap();
+  }
+}
+// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void tc2_arrive_remote(uint64_t* bar, uint32_t rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(rank));
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+__device__ __forceinline__ void tc2_commit_mc(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
+          "r"(smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void tc2_mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " setp.ne.b32 p, %4, 0;\n"
+      " tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc2_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// `work[].tile_begin` holds the prefix sum of UNITS here: one unit = two consecutive query tiles
+// of one directed pair (CTA rank r of the cluster takes tile 2 * unit + r).
+template <int K>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+hamming_tcgen05_2cta_kernel(const TcWork* __restrict__ work, int n_work, int total_units,
+                            int4* __restrict__ best2, int* __restrict__ error_flag) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sA = smem;                               // [2][32 KB]
+  uint8_t* sB = smem + 2 * TC_A_BYTES;              // [TC2_STAGES][32 KB]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * TC_A_BYTES + TC2_STAGES * TC2_B_BYTES);
+  uint64_t* a_full = bars;                          // [2]
+  uint64_t* a_empty = a_full + 2;                   // [2]
+  uint64_t* peer_a_full = a_empty + 2;              // [2]  (leader's copy is used)
+  uint64_t* acc_full = peer_a_full + 2;             // [2]
+  uint64_t* acc_empty = acc_full + 2;               // [2]  (leader's copy is used, 8 arrivals)
+  uint64_t* b_full = acc_empty + 2;                 // [S]
+  uint64_t* b_empty = b_full + TC2_STAGES;          // [S]
+  uint64_t* peer_b_full = b_empty + TC2_STAGES;     // [S]  (leader's copy is used)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(peer_b_full + TC2_STAGES);
+  uint2* merge = reinterpret_cast<uint2*>(smem + 2 * TC_A_BYTES + TC2_STAGES * TC2_B_BYTES + 256);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int cluster_id = blockIdx.x >> 1;
+  const int n_clusters = gridDim.x >> 1;
+
+  if ((smem_u32(smem) & 1023u) != 0) {   // same in both CTAs of the pair
+    if (tid == 0) atomicExch(error_flag, 1);
+    return;
+  }
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&a_full[i], 1);
+      mbar_init(&a_empty[i], 1);
+      mbar_init(&peer_a_full[i], 1);
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 8);   // 4 epilogue warps x 2 CTAs
+    }
+    for (int s = 0; s < TC2_STAGES; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+      mbar_init(&peer_b_full[s], 1);
+    }
+    fence_mbar_init();
+  }
+  tc2_cluster_sync();
+  if (warp == 9) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
+                     smem_u32(tmem_slot))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  tc2_cluster_sync();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 8) {
+    // ===== TMA producer (both CTAs: own query tile, own half of every train tile) =====
+    if (lane == 0) {
+      uint32_t g = 0, item = 0;
+      for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
+        const TcWork w = work[tc_find_work(work, n_work, unit)];
+        const int q_tile = 2 * (unit - w.tile_begin) + (int)rank;
+        const uint32_t ab = item & 1u;
+        tc2_wait(&a_empty[ab], ((item >> 1) & 1u) ^ 1u);
+        mbar_arrive_expect_tx(&a_full[ab], TC_A_BYTES);
+        uint8_t* a_dst = sA + (size_t)ab * TC_A_BYTES;
+        tma_bulk_g2s(a_dst, w.q_exp + (size_t)q_tile * (TC_M * 128), TC_M * 128, &a_full[ab]);
+        tma_bulk_g2s(a_dst + TC_M * 128,
+                     w.q_exp + (size_t)w.q_rows_pad * 128 + (size_t)q_tile * (TC_M * 128), TC_M * 128,
+                     &a_full[ab]);
+        const int n_t = (w.nt + TC_N - 1) / TC_N;
+        for (int t = 0; t < n_t; ++t, ++g) {
+          const uint32_t s = g % TC2_STAGES;
+          const uint32_t ph = (g / TC2_STAGES) & 1u;
+          tc2_wait(&b_empty[s], ph ^ 1u);
+          mbar_arrive_expect_tx(&b_full[s], TC2_B_BYTES);
+          uint8_t* dst = sB + (size_t)s * TC2_B_BYTES;
+          const size_t row0 = (size_t)t * TC_N + (size_t)rank * (TC_N / 2);
+          tma_bulk_g2s(dst, w.t_exp + row0 * 128, (TC_N / 2) * 128, &b_full[s]);
+          tma_bulk_g2s(dst + (TC_N / 2) * 128, w.t_exp + (size_t)w.t_rows_pad * 128 + row0 * 128,
+                       (TC_N / 2) * 128, &b_full[s]);
+        }
+      }
+    }
+  } else if (warp == 9) {
+    if (lane == 0 && rank == 0) {
+      // ===== MMA issuer (leader CTA, for both SMs) =====
+      uint32_t g = 0, item = 0;
+      for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
+        const TcWork w = work[tc_find_work(work, n_work, unit)];
+        const int n_t = (w.nt + TC_N - 1) / TC_N;
+        const uint32_t ab = item & 1u;
+        tc2_wait(&a_full[ab], (item >> 1) & 1u);
+        tc2_wait(&peer_a_full[ab], (item >> 1) & 1u);
+        const uint32_t a_addr = smem_u32(sA + (size_t)ab * TC_A_BYTES);
+        for (int t = 0; t < n_t; ++t, ++g) {
+          const uint32_t s = g % TC2_STAGES;
+          const uint32_t ph = (g / TC2_STAGES) & 1u;
+          const uint32_t buf = g & 1u;
+          tc2_wait(&b_full[s], ph);
+          tc2_wait(&peer_b_full[s], ph);
+          tc2_wait(&acc_empty[buf], ((g >> 1) & 1u) ^ 1u);
+          tc_fence_after();
+          const uint32_t b_addr = smem_u32(sB + (size_t)s * TC2_B_BYTES);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint64_t ad = tc_smem_desc(a_addr + (k >> 2) * (TC_M * 128) + (k & 3) * 32);
+            const uint64_t bd = tc_smem_desc(b_addr + (k >> 2) * ((TC_N / 2) * 128) + (k & 3) * 32);
+            tc2_mma_i8(tmem_base + buf * TC_N, ad, bd, TC2_IDESC, k > 0 ? 1u : 0u);
+          }
+          tc2_commit_mc(&b_empty[s]);
+          tc2_commit_mc(&acc_full[buf]);
+        }
+        tc2_commit_mc(&a_empty[ab]);
+      }
+    } else if (lane == 0) {
+      // ===== forwarder (peer CTA): tells the leader when this CTA's operands have landed =====
+      uint32_t g = 0, item = 0;
+      for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
+        const TcWork w = work[tc_find_work(work, n_work, unit)];
+        const int n_t = (w.nt + TC_N - 1) / TC_N;
+        const uint32_t ab = item & 1u;
+        tc2_wait(&a_full[ab], (item >> 1) & 1u);
+        tc2_arrive_remote(&peer_a_full[ab], 0);
+        for (int t = 0; t < n_t; ++t, ++g) {
+          const uint32_t s = g % TC2_STAGES;
+          tc2_wait(&b_full[s], (g / TC2_STAGES) & 1u);
+          tc2_arrive_remote(&peer_b_full[s], 0);
+        }
+      }
+    }
+  } else {
+    // ===== epilogue warpgroups =====
+    const uint32_t wg = (uint32_t)warp >> 2;
+    const int row_in_tile = (warp & 3) * 32 + lane;
+    const uint32_t taddr = tmem_base + wg * TC_N + ((uint32_t)((warp & 3) * 32) << 16);
+    uint32_t g = 0, item = 0;
+    for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
+      const TcWork w = work[tc_find_work(work, n_work, unit)];
+      const int q_tile = 2 * (unit - w.tile_begin) + (int)rank;
+      const int n_t = (w.nt + TC_N - 1) / TC_N;
+      uint32_t m1 = TC_KEY_NONE, m2 = TC_KEY_NONE;
+      int thr = -100000;
+      for (int t = 0; t < n_t; ++t, ++g) {
+        if ((g & 1u) != wg) continue;
+        tc2_wait(&acc_full[wg], (g >> 1) & 1u);
+        tc_fence_after();
+        if (t == n_t - 1 && (w.nt % TC_N) != 0)
+          tc_tile<K, true>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, m1, m2, thr);
+        else
+          tc_tile<K, false>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, m1, m2, thr);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc2_arrive_remote(&acc_empty[wg], 0);
+      }
+      uint2* slot = merge + (item & 1u) * TC_M;
+      if (wg == 1) slot[row_in_tile] = make_uint2(m1, m2);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (wg == 0) {
+        const uint2 o = slot[row_in_tile];
+        const uint32_t lo = min(m1, o.x);
+        const uint32_t hi = min(max(m1, o.x), min(m2, o.y));
+        const int row = q_tile * TC_M + row_in_tile;
+        if (row < w.nq) {
+          int4 r;
+          r.x = (lo == TC_KEY_NONE) ? -1 : (int)(lo & TC_KEY_IDX_MASK);
+          r.y = (lo == TC_KEY_NONE) ? -1 : (int)(lo >> TC_KEY_SHIFT);
+          r.z = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi & TC_KEY_IDX_MASK);
+          r.w = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi >> TC_KEY_SHIFT);
+          best2[w.out_row + row] = r;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  tc2_cluster_sync();   // no CTA of the pair may leave while the other can still signal it
+  if (warp == 9) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+  }
+}
+
 // ---- host side --------------------------------------------------------------------------------------
 
 constexpr size_t TC_SMEM_BYTES = (size_t)TC_A_BYTES + (size_t)TC_STAGES * TC_B_BYTES + 256 + 2 * TC_M * sizeof(uint2);
@@ -406,8 +664,18 @@ static cudaError_t ensure_expanded(ssp_ctx* ctx) {
   return cudaSuccess;
 }
 
+template <typename Kern>
+static cudaError_t tc_launch(ssp_ctx* ctx, Kern kern, size_t smem, int grid, int n_work, int total) {
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  kern<<<grid, TC_THREADS, smem, ctx->stream>>>(ctx->h_tc_work.as<TcWork>(), n_work, total,
+                                                ctx->h_best2.as<int4>(), ctx->h_tc_err.as<int>());
+  return cudaGetLastError();
+}
+
+// `two_cta`: SSP_HAMMING_TENSOR (cta_group::2 pairs) versus SSP_HAMMING_TENSOR_1CTA.
 cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& work, int k,
-                                  std::string* why_not) {
+                                  bool two_cta, std::string* why_not) {
   cudaError_t e = ensure_expanded(ctx);
   if (e != cudaSuccess) return e;
   if ((reinterpret_cast<uintptr_t>(ctx->h_expanded.p) & 15) != 0) {
@@ -416,7 +684,7 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
   }
   std::vector<TcWork> tw;
   tw.reserve(work.size());
-  int tiles = 0;
+  int total = 0;  // query tiles (1-CTA) or units of two query tiles (2-CTA)
   for (const HammingWork& w : work) {
     if (w.nq <= 0 || w.nt <= 0) continue;  // rows of such items keep the "no neighbour" memset
     TcWork t;
@@ -427,9 +695,10 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
     t.q_rows_pad = ctx->exp_rows_pad[w.qi];
     t.t_rows_pad = ctx->exp_rows_pad[w.ti];
     t.out_row = w.out_row;
-    t.tile_begin = tiles;
+    t.tile_begin = total;
     t.pad_ = 0;
-    tiles += (w.nq + TC_M - 1) / TC_M;
+    const int q_tiles = (w.nq + TC_M - 1) / TC_M;
+    total += two_cta ? (q_tiles + 1) / 2 : q_tiles;
     tw.push_back(t);
   }
   if (tw.empty()) {
@@ -442,28 +711,20 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
                            cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
     return e;
   if ((e = cudaMemsetAsync(ctx->h_tc_err.p, 0, sizeof(int), ctx->stream)) != cudaSuccess) return e;
-  const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
   // the caller's ev0 marks the whole variant; re-record it here so that main_kernel_ms times the
   // tcgen05 kernel alone (bank expansion happens once per upload, outside)
   if ((e = cudaEventRecord(ctx->ev0, ctx->stream)) != cudaSuccess) return e;
-  if (k == 2) {
-    auto kern = hamming_tcgen05_kernel<2>;
-    if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)TC_SMEM_BYTES)) != cudaSuccess)
-      return e;
-    kern<<<grid, TC_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->h_tc_work.as<TcWork>(), (int)tw.size(),
-                                                           tiles, ctx->h_best2.as<int4>(),
-                                                           ctx->h_tc_err.as<int>());
+  const int n_work = (int)tw.size();
+  if (two_cta) {
+    const int clusters = total < ctx->sm_count / 2 ? total : ctx->sm_count / 2;
+    e = (k == 2) ? tc_launch(ctx, hamming_tcgen05_2cta_kernel<2>, TC2_SMEM_BYTES, 2 * clusters, n_work, total)
+                 : tc_launch(ctx, hamming_tcgen05_2cta_kernel<1>, TC2_SMEM_BYTES, 2 * clusters, n_work, total);
   } else {
-    auto kern = hamming_tcgen05_kernel<1>;
-    if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)TC_SMEM_BYTES)) != cudaSuccess)
-      return e;
-    kern<<<grid, TC_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->h_tc_work.as<TcWork>(), (int)tw.size(),
-                                                           tiles, ctx->h_best2.as<int4>(),
-                                                           ctx->h_tc_err.as<int>());
+    const int grid = total < ctx->sm_count ? total : ctx->sm_count;
+    e = (k == 2) ? tc_launch(ctx, hamming_tcgen05_kernel<2>, TC_SMEM_BYTES, grid, n_work, total)
+                 : tc_launch(ctx, hamming_tcgen05_kernel<1>, TC_SMEM_BYTES, grid, n_work, total);
   }
-  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  if (e != cudaSuccess) return e;
   if ((e = cudaEventRecord(ctx->ev1, ctx->stream)) != cudaSuccess) return e;
   ctx->h_launches += 1;
   int flag = 0;

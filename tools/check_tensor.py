@@ -7,6 +7,7 @@ import ssp_b200
 from ssp_b200 import synthetic as synth
 from oracle import hamming_oracle as ho
 
+VARIANT = sys.argv[1] if len(sys.argv) > 1 else "tensor"
 eng = ssp_b200.Engine(0)
 ok = True
 for n_img, n_desc, world in ((2, 300, 400), (3, 1500, 2000), (3, 5000, 8000)):
@@ -17,7 +18,7 @@ for n_img, n_desc, world in ((2, 300, 400), (3, 1500, 2000), (3, 5000, 8000)):
     for mode in ("knn2_ratio", "crosscheck"):
         ref = eng.hamming_match_pairs(pairs, mode=mode, variant="popc", return_best2=True)
         t0 = time.time()
-        got = eng.hamming_match_pairs(pairs, mode=mode, variant="tensor", return_best2=True)
+        got = eng.hamming_match_pairs(pairs, mode=mode, variant=VARIANT, return_best2=True)
         same = np.array_equal(ref.best2, got.best2) and np.array_equal(ref.offsets, got.offsets) and \
             np.array_equal(ref.query_idx, got.query_idx) and np.array_equal(ref.train_idx, got.train_idx) and \
             np.array_equal(ref.distance, got.distance)
@@ -32,7 +33,7 @@ tie = synth.tie_stress_bank(3, 700, seed=5)
 eng.upload_descriptor_bank(tie)
 for mode in ("knn2_ratio", "crosscheck"):
     ref = eng.hamming_match_pairs(synth.all_pairs(3), mode=mode, variant="popc", return_best2=True)
-    got = eng.hamming_match_pairs(synth.all_pairs(3), mode=mode, variant="tensor", return_best2=True)
+    got = eng.hamming_match_pairs(synth.all_pairs(3), mode=mode, variant=VARIANT, return_best2=True)
     same = np.array_equal(ref.best2, got.best2) and np.array_equal(ref.query_idx, got.query_idx)
     print("tie-stress", mode, "same" if same else "DIFFERENT", flush=True)
     ok &= same
