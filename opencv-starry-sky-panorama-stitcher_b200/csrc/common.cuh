@@ -101,7 +101,8 @@ struct ssp_ctx {
 
   // Hamming scratch / results
   ssp::DevBuf h_work, h_pairs, h_best2, h_counts, h_offsets, h_mq, h_mt, h_md;
-  ssp::DevBuf h_expanded;  // +-1 int8 expansion of the bank for the tensor variant (swizzled tiles)
+  ssp::DevBuf h_expanded;  // int8 expansion of the bank for the tensor variant (swizzled tiles)
+  ssp::DevBuf h_popc;      // popcount of every bank row (int32), tensor variant
   ssp::DevBuf h_tc_work, h_tc_err;
   bool h_expanded_valid = false;
   std::vector<long long> exp_byte_off;  // per image byte offset into h_expanded

@@ -1,21 +1,28 @@
-// Kernel 1, tensor-core variant: all-pairs Hamming nearest neighbours as a dense +-1 int8
-// contraction on the 5th-generation tensor cores (tcgen05.mma kind::i8, accumulators in TMEM).
+// Kernel 1, tensor-core variant: all-pairs Hamming nearest neighbours as a dense int8 contraction
+// on the 5th-generation tensor cores (tcgen05.mma kind::i8, accumulators in TMEM).
 //
 // Replaces the same reference calls as hamming.cu (custom_bruteforce_matcher.py:160-172 and
-// :193-199).  For rows a, b in {+1,-1}^256 (bit 1 -> -1, bit 0 -> +1):
-//     dot(a, b) = 256 - 2 * hamming(a, b)          (exact in int32)
-// so the nearest neighbour is the LARGEST dot product and `hamming = (256 - dot) / 2`.
+// :193-199).  Encoding: a QUERY row q is expanded to {-1,+1}^256 (bit 0 -> -1, bit 1 -> +1), a
+// TRAIN row t to {0,1}^256.  Then
+//     D(q, t) = sum_k q'_k t_k = popc(q & t) - popc(~q & t) = 2 popc(q & t) - popc(t)
+//     hamming(q, t) = popc(q) + popc(t) - 2 popc(q & t) = popc(q) - D(q, t)      (exact in int32)
+// so for a fixed query row the nearest neighbour is the LARGEST D, and popc(q) is one constant per
+// epilogue thread.  (The symmetric +-1 x +-1 encoding gives the same ordering but toggles every
+// operand bit: the probes in profiles/ show it pulls the SM clock to ~1.54 GHz under the power cap,
+// while 0/1 train operands hold a higher clock.)
 // on sm_100a the b1 `mma.sync ... and.popc` path is emulated by IMMA + unpack
 // code, the native route is tcgen05 kind::i8 on pre-expanded operands; this file is that route.
 //
 // Data layout.  At bank upload every image is expanded once (expand_bank_kernel) from 32 B/row
-// packed bits to 256 B/row int8 and stored in HBM *already in the shared-memory image* the
-// tensor core wants: K-major, 128-byte swizzle.  Per image: two K-half slabs (K bytes 0..127 and
+// packed bits to 256 B/row int8, in BOTH encodings (an image is the query of some pairs and the
+// train set of others), stored in HBM *already in the shared-memory image* the tensor core
+// wants: K-major, 128-byte swizzle.  Per image and encoding: two K-half slabs (K bytes 0..127 and
 // 128..255), each [rows_pad/8][8 rows][128 B] with the 16-byte chunk c of row r stored at chunk
 // position c ^ (r & 7).  rows_pad = rows rounded up to 256, pad rows are all-zero.  A tile of R
 // rows (R % 8 == 0) of one K-half is therefore one contiguous R*128-byte block, and plain 1-D
 // TMA bulk copies (cp.async.bulk, no tensor map) drop it into shared memory ready for the UMMA
-// shared-memory descriptor (SWIZZLE_128B, SBO = 1024 B).
+// shared-memory descriptor (SWIZZLE_128B, SBO = 1024 B).  The popcount of every row is stored
+// next to the bank.
 //
 // Kernel.  Persistent, one CTA per SM, warp-specialised:
 //   warp 8  : TMA producer  — query tile (128 rows, 32 KB) once per work item, then streams the
@@ -24,18 +31,24 @@
 //             stage into one of two 256-column TMEM accumulators, tcgen05.commit signals
 //             "stage free" and "accumulator full" mbarriers
 //   warps 0-7: two epilogue warpgroups, one per accumulator buffer.  Each thread owns one TMEM
-//             lane = one query row: tcgen05.ld 32 columns at a time, a VIMNMX3 max-tree over the
-//             32 dots and ONE compare against the row's current k-th best; only if some lane of
-//             the warp beats its threshold the chunk is re-scanned with the exact packed-key
-//             update min(key) on (distance << 22 | train index), which is OpenCV's (distance,
-//             lowest index) order.  The running best-2 stays in registers for the whole train
-//             image; the two warpgroups merge through shared memory at the end of a work item.
+//             lane = one query row: tcgen05.ld 16 columns at a time, a VIMNMX3 max-tree over the
+//             16 values and ONE compare against the row's current k-th best; only if some lane of
+//             the warp beats its threshold the chunk's exact top-2 is extracted by a log-depth
+//             tournament over packed keys and merged into the running best-2 as
+//             (distance << 22 | train index), which is OpenCV's (distance, lowest index) order.
+//             The running best-2 stays in registers for the whole train image; the two
+//             warpgroups publish their thresholds to each other through shared memory (each sees
+//             only every other train tile) and merge at the end of a work item.
 #include "common.cuh"
 
 namespace ssp {
 
+#ifndef TC_EXPERIMENT
+#define TC_EXPERIMENT 0   // 1..3: bottleneck probes (tools/tc_bottleneck.sh), results are wrong
+#endif
 constexpr int TC_M = 128;                    // query rows per tile = TMEM lanes
 constexpr int TC_N = 256;                    // train rows per stage = TMEM columns per accumulator
+constexpr int TC_CHUNK = 16;                 // columns per epilogue step
 constexpr int TC_STAGES = 3;
 constexpr int TC_ROW_BYTES = 256;            // expanded row
 constexpr int TC_A_BYTES = TC_M * TC_ROW_BYTES;      // 32 KB
@@ -46,11 +59,15 @@ constexpr int TC_PAD = 256;                  // rows of every expanded image are
 constexpr uint32_t TC_KEY_SHIFT = 22;
 constexpr uint32_t TC_KEY_IDX_MASK = (1u << TC_KEY_SHIFT) - 1u;
 constexpr uint32_t TC_KEY_NONE = 0xFFFFFFFFu;
-constexpr int TC_DOT_MASKED = -30000;        // stands for "no such column"
+constexpr int TC_D_MASKED = -30000;          // stands for "no such column"
+constexpr int TC_THR_NONE = -100000;         // "no k-th neighbour yet"
+// bytes after the operand stages: mbarriers + TMEM slot (256), best-2 merge slots, thresholds
+constexpr int TC_TAIL_BYTES = 256 + 2 * TC_M * (int)sizeof(uint2) + 2 * TC_M * (int)sizeof(uint16_t);
 
 struct TcWork {              // one directed image pair
-  const uint8_t* q_exp;      // expanded query image
-  const uint8_t* t_exp;      // expanded train image
+  const uint8_t* q_exp;      // query image, +-1 encoding
+  const uint8_t* t_exp;      // train image, 0/1 encoding
+  const int* q_popc;         // popcount of every query row
   int nq, nt;
   int q_rows_pad, t_rows_pad;
   long long out_row;         // first best2 row of this item
@@ -59,41 +76,66 @@ struct TcWork {              // one directed image pair
 };
 
 // ---- bank expansion ---------------------------------------------------------------------------
-// one thread per (padded row, 16-byte output chunk)
+// one thread per (padded row, 16-byte output chunk); `out` = query encoding, `out + enc_stride`
+// = train encoding of the same image
 __global__ void __launch_bounds__(256)
 expand_bank_kernel(const uint8_t* __restrict__ packed, int n_rows, int rows_pad,
-                   uint8_t* __restrict__ out) {
+                   uint8_t* __restrict__ out, size_t enc_stride, int* __restrict__ popc) {
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int row = (int)(gid >> 4);
   const int c = (int)(gid & 15);
   if (row >= rows_pad) return;
-  uint4 v = make_uint4(0, 0, 0, 0);
+  uint4 vq = make_uint4(0, 0, 0, 0), vt = make_uint4(0, 0, 0, 0);
   if (row < n_rows) {
     const uint32_t bits = (uint32_t)packed[(size_t)row * 32 + c * 2] |
                           ((uint32_t)packed[(size_t)row * 32 + c * 2 + 1] << 8);
-    uint32_t w[4];
+    uint32_t wq[4], wt[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const uint32_t nib = (bits >> (4 * i)) & 0xFu;
-      // bit j of the nibble -> lsb of byte j (disjoint partial products), then 0 -> 0x01 (+1),
-      // 1 -> 0xFF (-1)
+      // bit j of the nibble -> lsb of byte j (disjoint partial products)
       const uint32_t t = (nib * 0x00204081u) & 0x01010101u;
-      w[i] = 0x01010101u ^ (t * 0xFEu);
+      wt[i] = t;                               // train: 0 / 1
+      wq[i] = 0xFFFFFFFFu ^ (t * 0xFEu);       // query: 0 -> 0xFF (-1), 1 -> 0x01 (+1)
     }
-    v = make_uint4(w[0], w[1], w[2], w[3]);
+    vq = make_uint4(wq[0], wq[1], wq[2], wq[3]);
+    vt = make_uint4(wt[0], wt[1], wt[2], wt[3]);
+    if (c == 0) {
+      const uint4* r4 = reinterpret_cast<const uint4*>(packed + (size_t)row * 32);
+      const uint4 a = r4[0], b = r4[1];
+      popc[row] = __popc(a.x) + __popc(a.y) + __popc(a.z) + __popc(a.w) + __popc(b.x) + __popc(b.y) +
+                  __popc(b.z) + __popc(b.w);
+    }
   }
   const int kh = c >> 3, c8 = c & 7;
   const size_t off = (size_t)kh * rows_pad * 128 + (size_t)(row >> 3) * 1024 + (size_t)(row & 7) * 128 +
                      (size_t)((c8 ^ (row & 7)) * 16);
-  *reinterpret_cast<uint4*>(out + off) = v;
+  *reinterpret_cast<uint4*>(out + off) = vq;
+  *reinterpret_cast<uint4*>(out + enc_stride + off) = vt;
 }
 
-// mbarrier wait with a watchdog: a protocol bug must surface as a CUDA error, not as a hung GPU
+// mbarrier wait.  try_wait carries a suspend-time hint so the polling warp sleeps in hardware
+// instead of burning issue slots of the SM sub-partition it shares with two epilogue warps (ncu:
+// the clock64-per-iteration loop this replaces was 22 % of all issued instructions).  Watchdog by
+// spin count: a protocol bug must surface as a CUDA error, not as a hung GPU.
+constexpr uint32_t TC_WAIT_HINT_NS = 20000;
+__device__ __forceinline__ bool tc_try_wait_hint(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
+      " selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(TC_WAIT_HINT_NS)
+      : "memory");
+  return ok != 0;
+}
 __device__ __forceinline__ void tc_wait(uint64_t* bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) __trap();  // ~2 s at 1.9 GHz
+  uint32_t spins = 0;
+  while (!tc_try_wait_hint(bar, parity)) {
+    if (++spins > 100000000u) __trap();
   }
 }
 
@@ -138,71 +180,163 @@ __device__ __forceinline__ uint64_t tc_smem_desc(uint32_t smem_addr) {
 constexpr uint32_t TC_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_N >> 3) << 17) |
                               ((uint32_t)(TC_M >> 4) << 24);
 
-// 32 consecutive TMEM columns of this thread's lane
-__device__ __forceinline__ void tc_ld32(uint32_t taddr, int (&v)[32]) {
+// 16 consecutive TMEM columns of this thread's lane
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, int (&v)[16]) {
   asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
         "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
-        "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
-        "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
-        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        "=r"(v[14]), "=r"(v[15])
       : "r"(taddr)
       : "memory");
 }
 // The registers of the preceding tcgen05.ld are valid only after this wait; they are passed as
 // in/out operands so the compiler cannot schedule their consumers above it.
-__device__ __forceinline__ void tc_wait_ld(int (&v)[32]) {
+__device__ __forceinline__ void tc_wait_ld(int (&v)[16]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]),
+                 "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]),
+                 "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
                :
                : "memory");
 }
 
-// ---- epilogue: one 32-column chunk of one query row ------------------------------------------------
-// v[j] = dot(query row, train row col0 + j).  Fast path: VIMNMX3 max-tree + one compare against the
-// dot of the row's current k-th best.  Slow path (warp-uniform): exact packed-key top-2 update of
-// all 32 columns; min/max on keys is order independent, so no per-element predication is needed.
+// ---- 2-CTA (cluster) PTX wrappers ------------------------------------------------------------------
+__device__ __forceinline__ bool tc2_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n"
+      " selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(TC_WAIT_HINT_NS)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void tc2_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!tc2_try_wait(bar, parity)) {
+    if (++spins > 100000000u) __trap();
+  }
+}
+// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void tc2_arrive_remote(uint64_t* bar, uint32_t rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(rank));
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+__device__ __forceinline__ void tc2_commit_mc(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
+          "r"(smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void tc2_mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " setp.ne.b32 p, %4, 0;\n"
+      " tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc2_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// ---- epilogue ------------------------------------------------------------------------------------
+// Per-thread state of one query row while a train image streams by.
+struct TcRow {
+  uint32_t m1, m2;     // running best-2 as packed keys (hamming << 22 | train index)
+  int thr;             // skip a chunk unless some D in it is > thr
+  int pq;              // popcount of the query row: hamming = pq - D
+  uint16_t* my_slot;   // where this thread publishes the D of its own k-th best
+  uint32_t tag;        // (item & 63) << 10, marks published values of the current work item
+};
+
+// One 16-column chunk of one query row; v[j] = D(query row, train row col0 + j).
+// Fast path: VIMNMX3 max-tree + one compare against the threshold.  Slow path (warp-uniform):
+// exact top-2 of the chunk by a tournament over local keys D * 16 + (15 - j) -- larger is better
+// and among equal D the lowest column wins, OpenCV's (distance, lowest index) order.  The key
+// IMADs run on the FMA pipe, the tournament on the ALU pipe.
 template <int K, bool MASKED>
-__device__ __forceinline__ void tc_chunk(int (&v)[32], uint32_t col0, uint32_t nt, uint32_t& m1,
-                                         uint32_t& m2, int& thr) {
+__device__ __forceinline__ void tc_chunk(int (&v)[16], uint32_t col0, uint32_t nt, TcRow& r) {
   if (MASKED) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = (col0 + j < nt) ? v[j] : TC_DOT_MASKED;
+    for (int j = 0; j < 16; ++j) v[j] = (col0 + j < nt) ? v[j] : TC_D_MASKED;
   }
-  int mx[8];
+#if TC_EXPERIMENT == 2
+  if (v[0] == 0x7fffffff) r.m1 = 0;  // keeps the loads alive, never true
+  return;
+#endif
+  const int m = max(__vimax3_s32(__vimax3_s32(v[0], v[1], v[2]), __vimax3_s32(v[3], v[4], v[5]),
+                                 __vimax3_s32(v[6], v[7], v[8])),
+                    __vimax3_s32(__vimax3_s32(v[9], v[10], v[11]), __vimax3_s32(v[12], v[13], v[14]),
+                                 v[15]));
+#if TC_EXPERIMENT == 3
+  if (m == 0x7fffffff) r.m1 = 0;
+  return;
+#endif
+  if (__any_sync(0xffffffffu, m > r.thr)) {
+    int hi[8], lo[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) mx[j] = max(max(v[4 * j], v[4 * j + 1]), max(v[4 * j + 2], v[4 * j + 3]));
-  const int m = max(max(max(mx[0], mx[1]), max(mx[2], mx[3])), max(max(mx[4], mx[5]), max(mx[6], mx[7])));
-  if (__any_sync(0xffffffffu, m > thr)) {
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      // hamming = (256 - dot) / 2  ->  key = hamming << 22 | index
-      uint32_t key = ((uint32_t)(256 - v[j]) << (TC_KEY_SHIFT - 1)) + (col0 + j);
-      if (MASKED) key = (col0 + j < nt) ? key : TC_KEY_NONE;
-      if (K == 2) m2 = min(m2, max(m1, key));
-      m1 = min(m1, key);
+    for (int i = 0; i < 8; ++i) {
+      const int a = v[2 * i] * 16 + (15 - 2 * i);
+      const int b = v[2 * i + 1] * 16 + (14 - 2 * i);
+      hi[i] = max(a, b);
+      if (K == 2) lo[i] = min(a, b);
     }
-    const uint32_t kth = (K == 2) ? m2 : m1;
-    thr = (kth == TC_KEY_NONE) ? -100000 : 256 - 2 * (int)(kth >> TC_KEY_SHIFT);
+#pragma unroll
+    for (int n = 4; n >= 1; n >>= 1) {
+#pragma unroll
+      for (int i = 0; i < n; ++i) {
+        if (K == 2) lo[i] = __vimax3_s32(min(hi[2 * i], hi[2 * i + 1]), lo[2 * i], lo[2 * i + 1]);
+        hi[i] = max(hi[2 * i], hi[2 * i + 1]);
+      }
+    }
+    // local key -> global packed key
+    const uint32_t j1 = 15u - ((uint32_t)hi[0] & 15u);
+    uint32_t k1 = ((uint32_t)(r.pq - (hi[0] >> 4)) << TC_KEY_SHIFT) + (col0 + j1);
+    if (MASKED) k1 = (col0 + j1 < nt) ? k1 : TC_KEY_NONE;
+    if (K == 2) {
+      const uint32_t j2 = 15u - ((uint32_t)lo[0] & 15u);
+      uint32_t k2 = ((uint32_t)(r.pq - (lo[0] >> 4)) << TC_KEY_SHIFT) + (col0 + j2);
+      if (MASKED) k2 = (col0 + j2 < nt) ? k2 : TC_KEY_NONE;
+      r.m2 = min(min(r.m2, k2), max(r.m1, k1));   // k1 <= k2 and m1 <= m2
+    }
+    r.m1 = min(r.m1, k1);
+    const uint32_t kth = (K == 2) ? r.m2 : r.m1;
+    if (kth != TC_KEY_NONE) {
+      const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
+      *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
+      r.thr = max(r.thr, d_own);
+    }
   }
 }
 
+// one 256-column accumulator of this thread's lane
 template <int K, bool MASKED>
-__device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint32_t nt, uint32_t& m1,
-                                        uint32_t& m2, int& thr) {
-  int va[32], vb[32];
-  tc_ld32(taddr, va);
+__device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint32_t nt, TcRow& r) {
+#if TC_EXPERIMENT == 1
+  return;
+#endif
+  int va[16], vb[16];
+  tc_ld16(taddr, va);
 #pragma unroll
-  for (int c = 0; c < TC_N / 32; c += 2) {
+  for (int c = 0; c < TC_N / TC_CHUNK; c += 2) {
     tc_wait_ld(va);
-    tc_ld32(taddr + (c + 1) * 32, vb);
-    tc_chunk<K, MASKED>(va, col_base + c * 32, nt, m1, m2, thr);
+    tc_ld16(taddr + (c + 1) * TC_CHUNK, vb);
+    tc_chunk<K, MASKED>(va, col_base + c * TC_CHUNK, nt, r);
     tc_wait_ld(vb);
-    if (c + 2 < TC_N / 32) tc_ld32(taddr + (c + 2) * 32, va);
-    tc_chunk<K, MASKED>(vb, col_base + (c + 1) * 32, nt, m1, m2, thr);
+    if (c + 2 < TC_N / TC_CHUNK) tc_ld16(taddr + (c + 2) * TC_CHUNK, va);
+    tc_chunk<K, MASKED>(vb, col_base + (c + 1) * TC_CHUNK, nt, r);
   }
 }
 
@@ -216,6 +350,66 @@ __device__ __forceinline__ int tc_find_work(const TcWork* __restrict__ work, int
   return lo;
 }
 
+// Epilogue of one work item (query tile `q_tile` of `w` against the whole train image) for one
+// thread of the two epilogue warpgroups; `g` counts train tiles across work items.  wg 0 drains
+// accumulator 0 (even tiles), wg 1 accumulator 1.  TWO_CTA: barriers live in the leader CTA.
+template <int K, bool TWO_CTA>
+__device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, uint32_t item, uint32_t& g,
+                                                 int warp, int lane, uint32_t tmem_base,
+                                                 uint64_t* acc_full, uint64_t* acc_empty, uint2* merge,
+                                                 uint16_t* share, int4* __restrict__ best2) {
+  const uint32_t wg = (uint32_t)warp >> 2;
+  const int row_in_tile = (warp & 3) * 32 + lane;
+  const uint32_t taddr = tmem_base + wg * TC_N + ((uint32_t)((warp & 3) * 32) << 16);
+  const int n_t = (w.nt + TC_N - 1) / TC_N;
+  const int row = q_tile * TC_M + row_in_tile;
+  TcRow r;
+  r.m1 = TC_KEY_NONE;
+  r.m2 = TC_KEY_NONE;
+  r.thr = TC_THR_NONE;
+  r.pq = (row < w.nq) ? w.q_popc[row] : 0;
+  r.my_slot = share + wg * TC_M + row_in_tile;
+  r.tag = (item & 63u) << 10;
+  const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
+  *r.my_slot = 0;
+  for (int t = 0; t < n_t; ++t, ++g) {
+    if ((g & 1u) != wg) continue;
+    // the other warpgroup's k-th best D bounds this row too; an equal D with a lower train index
+    // still has to be seen, hence the -1
+    const uint32_t pv = *reinterpret_cast<const volatile uint16_t*>(peer_slot);
+    if ((pv & 0xFC00u) == r.tag) r.thr = max(r.thr, (int)(pv & 1023u) - 513);
+    if (TWO_CTA) tc2_wait(&acc_full[wg], (g >> 1) & 1u); else tc_wait(&acc_full[wg], (g >> 1) & 1u);
+    tc_fence_after();
+    if (t == n_t - 1 && (w.nt % TC_N) != 0)
+      tc_tile<K, true>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, r);
+    else
+      tc_tile<K, false>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, r);
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) {
+      if (TWO_CTA) tc2_arrive_remote(&acc_empty[wg], 0); else mbar_arrive(&acc_empty[wg]);
+    }
+  }
+  // merge the two warpgroups' top-2 (disjoint train subsets) and write the row record
+  uint2* slot = merge + (item & 1u) * TC_M;
+  if (wg == 1) slot[row_in_tile] = make_uint2(r.m1, r.m2);
+  asm volatile("bar.sync 1, 256;" ::: "memory");
+  if (wg == 0) {
+    const uint2 o = slot[row_in_tile];
+    const uint32_t lo = min(r.m1, o.x);
+    const uint32_t hi = min(max(r.m1, o.x), min(r.m2, o.y));
+    if (row < w.nq) {
+      int4 out;
+      out.x = (lo == TC_KEY_NONE) ? -1 : (int)(lo & TC_KEY_IDX_MASK);
+      out.y = (lo == TC_KEY_NONE) ? -1 : (int)(lo >> TC_KEY_SHIFT);
+      out.z = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi & TC_KEY_IDX_MASK);
+      out.w = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi >> TC_KEY_SHIFT);
+      best2[w.out_row + row] = out;
+    }
+  }
+}
+
+// ---- 1-CTA kernel ----------------------------------------------------------------------------------
 template <int K>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_tiles,
@@ -223,7 +417,8 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + TC_A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TC_A_BYTES + TC_STAGES * TC_B_BYTES);
+  uint8_t* tail = smem + TC_A_BYTES + TC_STAGES * TC_B_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
   uint64_t* a_full = bars + 0;
   uint64_t* a_empty = bars + 1;
   uint64_t* b_full = bars + 2;
@@ -231,7 +426,8 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
   uint64_t* acc_full = b_empty + TC_STAGES;   // [2]
   uint64_t* acc_empty = acc_full + 2;          // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-  uint2* merge = reinterpret_cast<uint2*>(smem + TC_A_BYTES + TC_STAGES * TC_B_BYTES + 256);  // [2][128]
+  uint2* merge = reinterpret_cast<uint2*>(tail + 256);                                        // [2][128]
+  uint16_t* share = reinterpret_cast<uint16_t*>(tail + 256 + 2 * TC_M * sizeof(uint2));       // [2][128]
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -254,6 +450,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
     }
     fence_mbar_init();
   }
+  if (tid < 2 * TC_M) share[tid] = 0;
   if (warp == 9) {  // TMEM: all 512 columns (two 256-column int32 accumulators)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
                      smem_u32(tmem_slot))
@@ -320,47 +517,12 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
       }
     }
   } else {
-    // ===== epilogue warpgroups: wg 0 owns accumulator 0 (even tiles), wg 1 accumulator 1 =====
-    const uint32_t wg = (uint32_t)warp >> 2;
-    const int row_in_tile = (warp & 3) * 32 + lane;
-    const uint32_t taddr = tmem_base + wg * TC_N + ((uint32_t)((warp & 3) * 32) << 16);
+    // ===== epilogue warpgroups =====
     uint32_t g = 0, item = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
       const TcWork w = work[tc_find_work(work, n_work, tile)];
-      const int q_tile = tile - w.tile_begin;
-      const int n_t = (w.nt + TC_N - 1) / TC_N;
-      uint32_t m1 = TC_KEY_NONE, m2 = TC_KEY_NONE;
-      int thr = -100000;
-      for (int t = 0; t < n_t; ++t, ++g) {
-        if ((g & 1u) != wg) continue;
-        tc_wait(&acc_full[wg], (g >> 1) & 1u);
-        tc_fence_after();
-        if (t == n_t - 1 && (w.nt % TC_N) != 0)
-          tc_tile<K, true>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, m1, m2, thr);
-        else
-          tc_tile<K, false>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, m1, m2, thr);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&acc_empty[wg]);
-      }
-      // merge the two warpgroups' top-2 (disjoint train subsets) and write the row record
-      uint2* slot = merge + (item & 1u) * TC_M;
-      if (wg == 1) slot[row_in_tile] = make_uint2(m1, m2);
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (wg == 0) {
-        const uint2 o = slot[row_in_tile];
-        const uint32_t lo = min(m1, o.x);
-        const uint32_t hi = min(max(m1, o.x), min(m2, o.y));
-        const int row = q_tile * TC_M + row_in_tile;
-        if (row < w.nq) {
-          int4 r;
-          r.x = (lo == TC_KEY_NONE) ? -1 : (int)(lo & TC_KEY_IDX_MASK);
-          r.y = (lo == TC_KEY_NONE) ? -1 : (int)(lo >> TC_KEY_SHIFT);
-          r.z = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi & TC_KEY_IDX_MASK);
-          r.w = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi >> TC_KEY_SHIFT);
-          best2[w.out_row + row] = r;
-        }
-      }
+      tc_epilogue_item<K, false>(w, tile - w.tile_begin, item, g, warp, lane, tmem_base, acc_full,
+                                 acc_empty, merge, share, best2);
     }
   }
 
@@ -371,13 +533,11 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
   }
 }
-
 // ================================================================================================
 // 2-CTA variant (cta_group::2): a CTA pair shares every train tile.  Each CTA keeps its own 128
 // query rows (M = 256 across the pair) and stages only HALF of the 256 train rows of a tile
 // (N split), so L2 -> SM traffic and the shared-memory reads of the B operand are halved versus
-// the 1-CTA kernel, which ncu showed L2-bound (profiles/r01_ncu_hamming_tcgen05_1cta.txt:
-// tensor pipe 63 %, 10.3 TB/s crossbar reads).  The leader CTA's MMA thread issues for both
+// the 1-CTA kernel (profiles/r01_ncu_hamming_tcgen05_1cta.txt: 10.3 TB/s crossbar reads).  The leader CTA's MMA thread issues for both
 // SMs; each CTA's accumulator (its 128 rows x 256 columns) lands in its own TMEM and is drained
 // by its own epilogue warpgroups exactly as in the 1-CTA kernel.
 //
@@ -390,57 +550,7 @@ constexpr int TC2_STAGES = 4;
 constexpr int TC2_B_BYTES = (TC_N / 2) * TC_ROW_BYTES;  // 32 KB: this CTA's half of a train tile
 constexpr uint32_t TC2_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_N >> 3) << 17) |
                                ((uint32_t)(256 >> 4) << 24);
-constexpr size_t TC2_SMEM_BYTES = 2 * (size_t)TC_A_BYTES + (size_t)TC2_STAGES * TC2_B_BYTES + 256 +
-                                  2 * TC_M * sizeof(uint2);
-
-__device__ __forceinline__ bool tc2_try_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n"
-      " .reg .pred p;\n"
-      " mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
-      " selp.u32 %0, 1, 0, p;\n"
-      "}\n"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void tc2_wait(uint64_t* bar, uint32_t parity) {
-  if (tc2_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!tc2_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) __trap();
-  }
-}
-// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster
-__device__ __forceinline__ void tc2_arrive_remote(uint64_t* bar, uint32_t rank) {
-  uint32_t remote;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(rank));
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
-}
-__device__ __forceinline__ void tc2_commit_mc(uint64_t* bar) {
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
-          "r"(smem_u32(bar)),
-      "h"((uint16_t)3)
-      : "memory");
-}
-__device__ __forceinline__ void tc2_mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
-                                           uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n"
-      " .reg .pred p;\n"
-      " setp.ne.b32 p, %4, 0;\n"
-      " tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n"
-      "}\n" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void tc2_cluster_sync() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
+constexpr size_t TC2_SMEM_BYTES = 2 * (size_t)TC_A_BYTES + (size_t)TC2_STAGES * TC2_B_BYTES + TC_TAIL_BYTES;
 
 // `work[].tile_begin` holds the prefix sum of UNITS here: one unit = two consecutive query tiles
 // of one directed pair (CTA rank r of the cluster takes tile 2 * unit + r).
@@ -462,6 +572,8 @@ hamming_tcgen05_2cta_kernel(const TcWork* __restrict__ work, int n_work, int tot
   uint64_t* peer_b_full = b_empty + TC2_STAGES;     // [S]  (leader's copy is used)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(peer_b_full + TC2_STAGES);
   uint2* merge = reinterpret_cast<uint2*>(smem + 2 * TC_A_BYTES + TC2_STAGES * TC2_B_BYTES + 256);
+  uint16_t* share = reinterpret_cast<uint16_t*>(smem + 2 * TC_A_BYTES + TC2_STAGES * TC2_B_BYTES + 256 +
+                                                2 * TC_M * sizeof(uint2));
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -490,6 +602,7 @@ hamming_tcgen05_2cta_kernel(const TcWork* __restrict__ work, int n_work, int tot
     }
     fence_mbar_init();
   }
+  if (tid < 2 * TC_M) share[tid] = 0;
   tc2_cluster_sync();
   if (warp == 9) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
@@ -580,45 +693,11 @@ hamming_tcgen05_2cta_kernel(const TcWork* __restrict__ work, int n_work, int tot
     }
   } else {
     // ===== epilogue warpgroups =====
-    const uint32_t wg = (uint32_t)warp >> 2;
-    const int row_in_tile = (warp & 3) * 32 + lane;
-    const uint32_t taddr = tmem_base + wg * TC_N + ((uint32_t)((warp & 3) * 32) << 16);
     uint32_t g = 0, item = 0;
     for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
       const TcWork w = work[tc_find_work(work, n_work, unit)];
-      const int q_tile = 2 * (unit - w.tile_begin) + (int)rank;
-      const int n_t = (w.nt + TC_N - 1) / TC_N;
-      uint32_t m1 = TC_KEY_NONE, m2 = TC_KEY_NONE;
-      int thr = -100000;
-      for (int t = 0; t < n_t; ++t, ++g) {
-        if ((g & 1u) != wg) continue;
-        tc2_wait(&acc_full[wg], (g >> 1) & 1u);
-        tc_fence_after();
-        if (t == n_t - 1 && (w.nt % TC_N) != 0)
-          tc_tile<K, true>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, m1, m2, thr);
-        else
-          tc_tile<K, false>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, m1, m2, thr);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) tc2_arrive_remote(&acc_empty[wg], 0);
-      }
-      uint2* slot = merge + (item & 1u) * TC_M;
-      if (wg == 1) slot[row_in_tile] = make_uint2(m1, m2);
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (wg == 0) {
-        const uint2 o = slot[row_in_tile];
-        const uint32_t lo = min(m1, o.x);
-        const uint32_t hi = min(max(m1, o.x), min(m2, o.y));
-        const int row = q_tile * TC_M + row_in_tile;
-        if (row < w.nq) {
-          int4 r;
-          r.x = (lo == TC_KEY_NONE) ? -1 : (int)(lo & TC_KEY_IDX_MASK);
-          r.y = (lo == TC_KEY_NONE) ? -1 : (int)(lo >> TC_KEY_SHIFT);
-          r.z = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi & TC_KEY_IDX_MASK);
-          r.w = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi >> TC_KEY_SHIFT);
-          best2[w.out_row + row] = r;
-        }
-      }
+      tc_epilogue_item<K, true>(w, 2 * (unit - w.tile_begin) + (int)rank, item, g, warp, lane, tmem_base,
+                                acc_full, acc_empty, merge, share, best2);
     }
   }
 
@@ -632,7 +711,7 @@ hamming_tcgen05_2cta_kernel(const TcWork* __restrict__ work, int n_work, int tot
 
 // ---- host side --------------------------------------------------------------------------------------
 
-constexpr size_t TC_SMEM_BYTES = (size_t)TC_A_BYTES + (size_t)TC_STAGES * TC_B_BYTES + 256 + 2 * TC_M * sizeof(uint2);
+constexpr size_t TC_SMEM_BYTES = (size_t)TC_A_BYTES + (size_t)TC_STAGES * TC_B_BYTES + TC_TAIL_BYTES;
 
 // (re)builds the expanded bank if the packed bank changed since the last call
 static cudaError_t ensure_expanded(ssp_ctx* ctx) {
@@ -644,10 +723,11 @@ static cudaError_t ensure_expanded(ssp_ctx* ctx) {
     const long long n = ctx->row_off[i + 1] - ctx->row_off[i];
     const long long pad = (n + TC_PAD - 1) / TC_PAD * TC_PAD;
     ctx->exp_rows_pad[i] = (int)pad;
-    ctx->exp_byte_off[i + 1] = ctx->exp_byte_off[i] + pad * TC_ROW_BYTES;
+    ctx->exp_byte_off[i + 1] = ctx->exp_byte_off[i] + 2 * pad * TC_ROW_BYTES;  // query + train encoding
   }
   cudaError_t e = ctx->h_expanded.ensure((size_t)ctx->exp_byte_off[n_images] + 1024);
   if (e != cudaSuccess) return e;
+  if ((e = ctx->h_popc.ensure(((size_t)ctx->row_off[n_images] + 1) * sizeof(int))) != cudaSuccess) return e;
   for (int i = 0; i < n_images; ++i) {
     const int n = (int)(ctx->row_off[i + 1] - ctx->row_off[i]);
     const int pad = ctx->exp_rows_pad[i];
@@ -655,7 +735,8 @@ static cudaError_t ensure_expanded(ssp_ctx* ctx) {
     const long long threads = (long long)pad * 16;
     expand_bank_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(
         ctx->d_desc + (size_t)ctx->row_off[i] * 32, n, pad,
-        ctx->h_expanded.as<uint8_t>() + ctx->exp_byte_off[i]);
+        ctx->h_expanded.as<uint8_t>() + ctx->exp_byte_off[i], (size_t)pad * TC_ROW_BYTES,
+        ctx->h_popc.as<int>() + ctx->row_off[i]);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     ctx->h_launches += 1;
@@ -689,7 +770,9 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
     if (w.nq <= 0 || w.nt <= 0) continue;  // rows of such items keep the "no neighbour" memset
     TcWork t;
     t.q_exp = ctx->h_expanded.as<uint8_t>() + ctx->exp_byte_off[w.qi];
-    t.t_exp = ctx->h_expanded.as<uint8_t>() + ctx->exp_byte_off[w.ti];
+    t.t_exp = ctx->h_expanded.as<uint8_t>() + ctx->exp_byte_off[w.ti] +
+              (size_t)ctx->exp_rows_pad[w.ti] * TC_ROW_BYTES;
+    t.q_popc = ctx->h_popc.as<int>() + ctx->row_off[w.qi];
     t.nq = w.nq;
     t.nt = w.nt;
     t.q_rows_pad = ctx->exp_rows_pad[w.qi];
