@@ -31,10 +31,11 @@
 //             stage into one of two 256-column TMEM accumulators, tcgen05.commit signals
 //             "stage free" and "accumulator full" mbarriers
 //   warps 0-7: two epilogue warpgroups, one per accumulator buffer.  Each thread owns one TMEM
-//             lane = one query row: tcgen05.ld 16 columns at a time, a VIMNMX3 max-tree over the
-//             16 values and ONE compare against the row's current k-th best; only if some lane of
-//             the warp beats its threshold the chunk's exact top-2 is extracted by a log-depth
-//             tournament over packed keys and merged into the running best-2 as
+//             lane = one query row.  Pass 1 streams the accumulator as packed s16 pairs
+//             (tcgen05.ld .pack::16b) through a VIMNMX3.S16x2 max-tree and compares each
+//             16-column chunk with the row's current k-th best; pass 2 re-reads only the chunks
+//             in which some lane of the warp beat its threshold and extracts their exact top-2
+//             by a log-depth tournament over packed keys, merged into the running best-2 as
 //             (distance << 22 | train index), which is OpenCV's (distance, lowest index) order.
 //             The running best-2 stays in registers for the whole train image; the two
 //             warpgroups publish their thresholds to each other through shared memory (each sees
@@ -261,82 +262,121 @@ struct TcRow {
   uint32_t tag;        // (item & 63) << 10, marks published values of the current work item
 };
 
-// One 16-column chunk of one query row; v[j] = D(query row, train row col0 + j).
-// Fast path: VIMNMX3 max-tree + one compare against the threshold.  Slow path (warp-uniform):
-// exact top-2 of the chunk by a tournament over local keys D * 16 + (15 - j) -- larger is better
-// and among equal D the lowest column wins, OpenCV's (distance, lowest index) order.  The key
-// IMADs run on the FMA pipe, the tournament on the ALU pipe.
+// 32 consecutive TMEM columns of this thread's lane as 16 registers of two packed s16 values
+// (.pack::16b keeps the low 16 bits of each column: D is in [-256, 256]); register i holds columns
+// 2i (low half) and 2i + 1 (high half).
+__device__ __forceinline__ void tc_ld32_packed(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]),
+                 "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]),
+                 "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+               :
+               : "memory");
+}
+
+// Pass 1 (filter): does any of the 16 columns held by p[0..7] beat the packed threshold?
+// 4 VIMNMX(3).S16x2 for the max of 16 values, one more against the threshold, one compare.
+__device__ __forceinline__ bool tc_beats(const uint32_t* p, uint32_t thrp) {
+  const uint32_t t0 = __vimax3_s16x2(p[0], p[1], p[2]);
+  const uint32_t t1 = __vimax3_s16x2(p[3], p[4], p[5]);
+  const uint32_t t2 = __vimax3_s16x2(p[6], p[7], t0);
+  return __vimax3_s16x2(t1, t2, thrp) != thrp;   // some half is > its threshold half
+}
+
+// Pass 2 (exact): top-2 of one flagged 16-column chunk, v[j] = D(query row, train row col0 + j),
+// by a tournament over local keys D * 16 + (15 - j) -- larger is better and among equal D the
+// lowest column wins, OpenCV's (distance, lowest index) order -- merged into the running best-2.
+// The key IMADs run on the FMA pipe, the tournament on the ALU pipe.  Every lane of the warp runs
+// it (the merge is exact, so lanes that did not need it are unaffected).
 template <int K, bool MASKED>
-__device__ __forceinline__ void tc_chunk(int (&v)[16], uint32_t col0, uint32_t nt, TcRow& r) {
+__device__ __forceinline__ void tc_chunk_exact(int (&v)[16], uint32_t col0, uint32_t nt, TcRow& r) {
   if (MASKED) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) v[j] = (col0 + j < nt) ? v[j] : TC_D_MASKED;
   }
-#if TC_EXPERIMENT == 2
-  if (v[0] == 0x7fffffff) r.m1 = 0;  // keeps the loads alive, never true
-  return;
-#endif
-  const int m = max(__vimax3_s32(__vimax3_s32(v[0], v[1], v[2]), __vimax3_s32(v[3], v[4], v[5]),
-                                 __vimax3_s32(v[6], v[7], v[8])),
-                    __vimax3_s32(__vimax3_s32(v[9], v[10], v[11]), __vimax3_s32(v[12], v[13], v[14]),
-                                 v[15]));
-#if TC_EXPERIMENT == 3
-  if (m == 0x7fffffff) r.m1 = 0;
-  return;
-#endif
-  if (__any_sync(0xffffffffu, m > r.thr)) {
-    int hi[8], lo[8];
+  int hi[8], lo[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int a = v[2 * i] * 16 + (15 - 2 * i);
-      const int b = v[2 * i + 1] * 16 + (14 - 2 * i);
-      hi[i] = max(a, b);
-      if (K == 2) lo[i] = min(a, b);
-    }
+  for (int i = 0; i < 8; ++i) {
+    const int a = v[2 * i] * 16 + (15 - 2 * i);
+    const int b = v[2 * i + 1] * 16 + (14 - 2 * i);
+    hi[i] = max(a, b);
+    if (K == 2) lo[i] = min(a, b);
+  }
 #pragma unroll
-    for (int n = 4; n >= 1; n >>= 1) {
+  for (int n = 4; n >= 1; n >>= 1) {
 #pragma unroll
-      for (int i = 0; i < n; ++i) {
-        if (K == 2) lo[i] = __vimax3_s32(min(hi[2 * i], hi[2 * i + 1]), lo[2 * i], lo[2 * i + 1]);
-        hi[i] = max(hi[2 * i], hi[2 * i + 1]);
-      }
+    for (int i = 0; i < n; ++i) {
+      if (K == 2) lo[i] = __vimax3_s32(min(hi[2 * i], hi[2 * i + 1]), lo[2 * i], lo[2 * i + 1]);
+      hi[i] = max(hi[2 * i], hi[2 * i + 1]);
     }
-    // local key -> global packed key
-    const uint32_t j1 = 15u - ((uint32_t)hi[0] & 15u);
-    uint32_t k1 = ((uint32_t)(r.pq - (hi[0] >> 4)) << TC_KEY_SHIFT) + (col0 + j1);
-    if (MASKED) k1 = (col0 + j1 < nt) ? k1 : TC_KEY_NONE;
-    if (K == 2) {
-      const uint32_t j2 = 15u - ((uint32_t)lo[0] & 15u);
-      uint32_t k2 = ((uint32_t)(r.pq - (lo[0] >> 4)) << TC_KEY_SHIFT) + (col0 + j2);
-      if (MASKED) k2 = (col0 + j2 < nt) ? k2 : TC_KEY_NONE;
-      r.m2 = min(min(r.m2, k2), max(r.m1, k1));   // k1 <= k2 and m1 <= m2
-    }
-    r.m1 = min(r.m1, k1);
-    const uint32_t kth = (K == 2) ? r.m2 : r.m1;
-    if (kth != TC_KEY_NONE) {
-      const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
-      *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
-      r.thr = max(r.thr, d_own);
-    }
+  }
+  // local key -> global packed key
+  const uint32_t j1 = 15u - ((uint32_t)hi[0] & 15u);
+  uint32_t k1 = ((uint32_t)(r.pq - (hi[0] >> 4)) << TC_KEY_SHIFT) + (col0 + j1);
+  if (MASKED) k1 = (col0 + j1 < nt) ? k1 : TC_KEY_NONE;
+  if (K == 2) {
+    const uint32_t j2 = 15u - ((uint32_t)lo[0] & 15u);
+    uint32_t k2 = ((uint32_t)(r.pq - (lo[0] >> 4)) << TC_KEY_SHIFT) + (col0 + j2);
+    if (MASKED) k2 = (col0 + j2 < nt) ? k2 : TC_KEY_NONE;
+    r.m2 = min(min(r.m2, k2), max(r.m1, k1));   // k1 <= k2 and m1 <= m2
+  }
+  r.m1 = min(r.m1, k1);
+  const uint32_t kth = (K == 2) ? r.m2 : r.m1;
+  if (kth != TC_KEY_NONE) {
+    const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
+    *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
+    r.thr = max(r.thr, d_own);
   }
 }
 
-// one 256-column accumulator of this thread's lane
+// One 256-column accumulator of this thread's lane, in two passes.
+//   Pass 1 streams the accumulator as packed s16 pairs and records, per 16-column chunk, whether
+//   any lane of the warp sees a value above its row's threshold: branch-free, 7 instructions per
+//   chunk and lane.  Pad columns of the last tile read as D = 0 and may raise a flag needlessly.
+//   Pass 2 re-reads only the flagged chunks (typically one or two of 16 once the thresholds have
+//   settled) as int32 and updates the best-2 exactly.
 template <int K, bool MASKED>
 __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint32_t nt, TcRow& r) {
 #if TC_EXPERIMENT == 1
   return;
 #endif
-  int va[16], vb[16];
-  tc_ld16(taddr, va);
+  const uint32_t thrp = (uint32_t)(max(r.thr, -32768) & 0xFFFF) * 0x10001u;
+  uint32_t flags = 0;
+  uint32_t pa[16], pb[16];
+  tc_ld32_packed(taddr, pa);
 #pragma unroll
-  for (int c = 0; c < TC_N / TC_CHUNK; c += 2) {
-    tc_wait_ld(va);
-    tc_ld16(taddr + (c + 1) * TC_CHUNK, vb);
-    tc_chunk<K, MASKED>(va, col_base + c * TC_CHUNK, nt, r);
-    tc_wait_ld(vb);
-    if (c + 2 < TC_N / TC_CHUNK) tc_ld16(taddr + (c + 2) * TC_CHUNK, va);
-    tc_chunk<K, MASKED>(vb, col_base + (c + 1) * TC_CHUNK, nt, r);
+  for (int c = 0; c < TC_N / 32; c += 2) {
+    tc_wait_ld(pa);
+    tc_ld32_packed(taddr + (c + 1) * 32, pb);
+    flags |= tc_beats(pa, thrp) ? (1u << (2 * c)) : 0u;
+    flags |= tc_beats(pa + 8, thrp) ? (1u << (2 * c + 1)) : 0u;
+    tc_wait_ld(pb);
+    if (c + 2 < TC_N / 32) tc_ld32_packed(taddr + (c + 2) * 32, pa);
+    flags |= tc_beats(pb, thrp) ? (1u << (2 * c + 2)) : 0u;
+    flags |= tc_beats(pb + 8, thrp) ? (1u << (2 * c + 3)) : 0u;
+  }
+#if TC_EXPERIMENT == 2 || TC_EXPERIMENT == 3
+  if (flags == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
+  return;
+#endif
+  flags = __reduce_or_sync(0xffffffffu, flags);
+  while (flags) {
+    const uint32_t c = (uint32_t)__ffs((int)flags) - 1u;
+    flags &= flags - 1u;
+    int v[16];
+    tc_ld16(taddr + c * TC_CHUNK, v);
+    tc_wait_ld(v);
+    tc_chunk_exact<K, MASKED>(v, col_base + c * TC_CHUNK, nt, r);
   }
 }
 

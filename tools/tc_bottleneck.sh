@@ -3,8 +3,7 @@
 # Rebuilds libssp_b200.so with -DTC_EXPERIMENT=n (results are WRONG for n > 0; only the time of the
 # dominant kernel is of interest), prints kernel ms per launch, then restores the product build.
 #   1: accumulators are never read      -> TMA feed + MMA issue rate alone
-#   2: tcgen05.ld only, no ALU work      -> TMEM read rate
-#   3: max-tree fast path only           -> ALU cost of the filter without exact updates
+#   2, 3: pass 1 only (packed filter), no exact updates
 #   4: like 1 with 0/1 instead of +-1 operands -> operand-toggling share of the power cap
 set -e
 cd "$(dirname "$0")/../opencv-starry-sky-panorama-stitcher_b200/csrc"
