@@ -30,8 +30,9 @@
 //   warp 9  : MMA issuer    — one elected thread issues 8 x tcgen05.mma (M128 N256 K32) per
 //             stage into one of two 256-column TMEM accumulators, tcgen05.commit signals
 //             "stage free" and "accumulator full" mbarriers
-//   warps 0-7: two epilogue warpgroups, one per accumulator buffer.  Each thread owns one TMEM
-//             lane = one query row.  Pass 1 streams the accumulator as packed s16 pairs
+//   warps 0-7: two epilogue warpgroups, each draining one 128-column half of every accumulator
+//             (halves the drain latency of a buffer).  Each thread owns one TMEM lane = one
+//             query row.  Pass 1 streams the accumulator as packed s16 pairs
 //             (tcgen05.ld .pack::16b) through a VIMNMX3.S16x2 max-tree and compares each
 //             16-column chunk with the row's current k-th best; pass 2 re-reads only the chunks
 //             in which some lane of the warp beat its threshold and extracts their exact top-2
@@ -39,7 +40,7 @@
 //             (distance << 22 | train index), which is OpenCV's (distance, lowest index) order.
 //             The running best-2 stays in registers for the whole train image; the two
 //             warpgroups publish their thresholds to each other through shared memory (each sees
-//             only every other train tile) and merge at the end of a work item.
+//             only half of the train rows) and merge at the end of a work item.
 #include "common.cuh"
 
 namespace ssp {
@@ -50,6 +51,7 @@ namespace ssp {
 constexpr int TC_M = 128;                    // query rows per tile = TMEM lanes
 constexpr int TC_N = 256;                    // train rows per stage = TMEM columns per accumulator
 constexpr int TC_CHUNK = 16;                 // columns per epilogue step
+constexpr int TC_HALF = TC_N / 2;            // columns of an accumulator drained by one warpgroup
 constexpr int TC_STAGES = 3;
 constexpr int TC_ROW_BYTES = 256;            // expanded row
 constexpr int TC_A_BYTES = TC_M * TC_ROW_BYTES;      // 32 KB
@@ -339,7 +341,7 @@ __device__ __forceinline__ void tc_chunk_exact(int (&v)[16], uint32_t col0, uint
   }
 }
 
-// One 256-column accumulator of this thread's lane, in two passes.
+// This warpgroup's 128-column half of one accumulator, for this thread's lane, in two passes.
 //   Pass 1 streams the accumulator as packed s16 pairs and records, per 16-column chunk, whether
 //   any lane of the warp sees a value above its row's threshold: branch-free, 7 instructions per
 //   chunk and lane.  Pad columns of the last tile read as D = 0 and may raise a flag needlessly.
@@ -355,13 +357,13 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
   uint32_t pa[16], pb[16];
   tc_ld32_packed(taddr, pa);
 #pragma unroll
-  for (int c = 0; c < TC_N / 32; c += 2) {
+  for (int c = 0; c < TC_HALF / 32; c += 2) {
     tc_wait_ld(pa);
     tc_ld32_packed(taddr + (c + 1) * 32, pb);
     flags |= tc_beats(pa, thrp) ? (1u << (2 * c)) : 0u;
     flags |= tc_beats(pa + 8, thrp) ? (1u << (2 * c + 1)) : 0u;
     tc_wait_ld(pb);
-    if (c + 2 < TC_N / 32) tc_ld32_packed(taddr + (c + 2) * 32, pa);
+    if (c + 2 < TC_HALF / 32) tc_ld32_packed(taddr + (c + 2) * 32, pa);
     flags |= tc_beats(pb, thrp) ? (1u << (2 * c + 2)) : 0u;
     flags |= tc_beats(pb + 8, thrp) ? (1u << (2 * c + 3)) : 0u;
   }
@@ -391,8 +393,11 @@ __device__ __forceinline__ int tc_find_work(const TcWork* __restrict__ work, int
 }
 
 // Epilogue of one work item (query tile `q_tile` of `w` against the whole train image) for one
-// thread of the two epilogue warpgroups; `g` counts train tiles across work items.  wg 0 drains
-// accumulator 0 (even tiles), wg 1 accumulator 1.  TWO_CTA: barriers live in the leader CTA.
+// thread of the two epilogue warpgroups; `g` counts train tiles across work items.  BOTH
+// warpgroups drain every accumulator, wg 0 its columns [0, 128) and wg 1 [128, 256): the MMA of
+// tile g + 2 needs the buffer of tile g back within ONE stage time (tile g + 1 runs meanwhile), so
+// what matters is the drain latency of a buffer, and splitting it halves that.
+// TWO_CTA: barriers live in the leader CTA.
 template <int K, bool TWO_CTA>
 __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, uint32_t item, uint32_t& g,
                                                  int warp, int lane, uint32_t tmem_base,
@@ -400,7 +405,7 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
                                                  uint16_t* share, int4* __restrict__ best2) {
   const uint32_t wg = (uint32_t)warp >> 2;
   const int row_in_tile = (warp & 3) * 32 + lane;
-  const uint32_t taddr = tmem_base + wg * TC_N + ((uint32_t)((warp & 3) * 32) << 16);
+  const uint32_t taddr0 = tmem_base + wg * TC_HALF + ((uint32_t)((warp & 3) * 32) << 16);
   const int n_t = (w.nt + TC_N - 1) / TC_N;
   const int row = q_tile * TC_M + row_in_tile;
   TcRow r;
@@ -413,21 +418,23 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
   *r.my_slot = 0;
   for (int t = 0; t < n_t; ++t, ++g) {
-    if ((g & 1u) != wg) continue;
+    const uint32_t buf = g & 1u;
     // the other warpgroup's k-th best D bounds this row too; an equal D with a lower train index
     // still has to be seen, hence the -1
     const uint32_t pv = *reinterpret_cast<const volatile uint16_t*>(peer_slot);
     if ((pv & 0xFC00u) == r.tag) r.thr = max(r.thr, (int)(pv & 1023u) - 513);
-    if (TWO_CTA) tc2_wait(&acc_full[wg], (g >> 1) & 1u); else tc_wait(&acc_full[wg], (g >> 1) & 1u);
+    if (TWO_CTA) tc2_wait(&acc_full[buf], (g >> 1) & 1u); else tc_wait(&acc_full[buf], (g >> 1) & 1u);
     tc_fence_after();
+    const uint32_t taddr = taddr0 + buf * TC_N;
+    const uint32_t col_base = (uint32_t)t * TC_N + wg * TC_HALF;
     if (t == n_t - 1 && (w.nt % TC_N) != 0)
-      tc_tile<K, true>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, r);
+      tc_tile<K, true>(taddr, col_base, (uint32_t)w.nt, r);
     else
-      tc_tile<K, false>(taddr, (uint32_t)t * TC_N, (uint32_t)w.nt, r);
+      tc_tile<K, false>(taddr, col_base, (uint32_t)w.nt, r);
     tc_fence_before();
     __syncwarp();
     if (lane == 0) {
-      if (TWO_CTA) tc2_arrive_remote(&acc_empty[wg], 0); else mbar_arrive(&acc_empty[wg]);
+      if (TWO_CTA) tc2_arrive_remote(&acc_empty[buf], 0); else mbar_arrive(&acc_empty[buf]);
     }
   }
   // merge the two warpgroups' top-2 (disjoint train subsets) and write the row record
@@ -486,7 +493,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&acc_full[b], 1);
-      mbar_init(&acc_empty[b], 4);  // one arrive per epilogue warp of the owning warpgroup
+      mbar_init(&acc_empty[b], 8);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -633,7 +640,7 @@ hamming_tcgen05_2cta_kernel(const TcWork* __restrict__ work, int n_work, int tot
       mbar_init(&a_empty[i], 1);
       mbar_init(&peer_a_full[i], 1);
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 8);   // 4 epilogue warps x 2 CTAs
+      mbar_init(&acc_empty[i], 16);  // 8 epilogue warps x 2 CTAs
     }
     for (int s = 0; s < TC2_STAGES; ++s) {
       mbar_init(&b_full[s], 1);
