@@ -239,7 +239,7 @@ static cudaError_t launch_popc(ssp_ctx* ctx, int n_work, int max_nq) {
 
 // implemented in hamming_tensor.cu
 cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& work, int k,
-                                  bool two_cta, std::string* why_not);
+                                  std::string* why_not);
 
 }  // namespace ssp
 
@@ -351,7 +351,7 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
     const bool tensor = (v == SSP_HAMMING_TENSOR || v == SSP_HAMMING_TENSOR_1CTA);
     if (tensor) {
       std::string why;
-      cudaError_t e = launch_hamming_tensor(ctx, work, k, v == SSP_HAMMING_TENSOR, &why);
+      cudaError_t e = launch_hamming_tensor(ctx, work, k, &why);
       if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
       SSP_CUDA_TRY(ctx, e);
     } else {

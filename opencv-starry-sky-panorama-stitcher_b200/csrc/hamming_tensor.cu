@@ -26,15 +26,15 @@
 //
 // Kernel.  Persistent, one CTA per SM, warp-specialised:
 //   warp 8  : TMA producer  — query tile (128 rows, 32 KB) once per work item, then streams the
-//             train image through a ring of 64 KB stages (256 train rows each)
+//             train image through a ring of three 64 KB stages (256 train rows each)
 //   warp 9  : MMA issuer    — one elected thread issues 8 x tcgen05.mma (M128 N256 K32) per
 //             stage into one of two 256-column TMEM accumulators, tcgen05.commit signals
 //             "stage free" and "accumulator full" mbarriers
 //   warps 0-7: two epilogue warpgroups, each draining one 128-column half of every accumulator
-//             (halves the drain latency of a buffer).  Each thread owns one TMEM lane = one
-//             query row.  Pass 1 streams the accumulator as packed s16 pairs
+//             and handing it back as soon as the values it still needs are in registers.  Each
+//             thread owns one TMEM lane = one query row.  Pass 1 streams the accumulator as packed s16 pairs
 //             (tcgen05.ld .pack::16b) through a VIMNMX3.S16x2 max-tree and compares each
-//             16-column chunk with the row's current k-th best; pass 2 re-reads only the chunks
+//             8-column chunk with the row's current k-th best; pass 2 re-reads only the chunks
 //             in which some lane of the warp beat its threshold and extracts their exact top-2
 //             by a log-depth tournament over packed keys, merged into the running best-2 as
 //             (distance << 22 | train index), which is OpenCV's (distance, lowest index) order.
@@ -48,9 +48,21 @@ namespace ssp {
 #ifndef TC_EXPERIMENT
 #define TC_EXPERIMENT 0   // 1..3: bottleneck probes (tools/tc_bottleneck.sh), results are wrong
 #endif
+#ifndef TC_PROFILE
+#define TC_PROFILE 0      // 1: block 0 prints where its MMA thread and one epilogue warp spend cycles
+#endif
+#if TC_PROFILE
+#define TC_PROF(x) x
+#else
+#define TC_PROF(x)
+#endif
 constexpr int TC_M = 128;                    // query rows per tile = TMEM lanes
+// N = 256 is the only full-rate shape here: with N = 128 (four smaller accumulators, tried for a
+// deeper epilogue pipeline) the MMA-only probe drops from 60 ms to 95 ms -- both operands come
+// from shared memory and the A tile is re-read for half as much work.
 constexpr int TC_N = 256;                    // train rows per stage = TMEM columns per accumulator
-constexpr int TC_CHUNK = 16;                 // columns per epilogue step
+constexpr int TC_ACC = 2;                    // accumulators in flight (2 x 256 = all 512 TMEM columns)
+constexpr int TC_CHUNK = 8;                  // columns per epilogue step
 constexpr int TC_HALF = TC_N / 2;            // columns of an accumulator drained by one warpgroup
 constexpr int TC_STAGES = 3;
 constexpr int TC_ROW_BYTES = 256;            // expanded row
@@ -183,75 +195,22 @@ __device__ __forceinline__ uint64_t tc_smem_desc(uint32_t smem_addr) {
 constexpr uint32_t TC_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_N >> 3) << 17) |
                               ((uint32_t)(TC_M >> 4) << 24);
 
-// 16 consecutive TMEM columns of this thread's lane
-__device__ __forceinline__ void tc_ld16(uint32_t taddr, int (&v)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
-        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
-        "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr)
-      : "memory");
+// 8 consecutive TMEM columns of this thread's lane
+__device__ __forceinline__ void tc_ld8(uint32_t taddr, int (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+                 "=r"(v[7])
+               : "r"(taddr)
+               : "memory");
 }
 // The registers of the preceding tcgen05.ld are valid only after this wait; they are passed as
 // in/out operands so the compiler cannot schedule their consumers above it.
-__device__ __forceinline__ void tc_wait_ld(int (&v)[16]) {
+__device__ __forceinline__ void tc_wait_ld(int (&v)[8]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;"
                : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]),
-                 "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]),
-                 "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+                 "+r"(v[7])
                :
                : "memory");
-}
-
-// ---- 2-CTA (cluster) PTX wrappers ------------------------------------------------------------------
-__device__ __forceinline__ bool tc2_try_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n"
-      " .reg .pred p;\n"
-      " mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n"
-      " selp.u32 %0, 1, 0, p;\n"
-      "}\n"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity), "r"(TC_WAIT_HINT_NS)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void tc2_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!tc2_try_wait(bar, parity)) {
-    if (++spins > 100000000u) __trap();
-  }
-}
-// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster
-__device__ __forceinline__ void tc2_arrive_remote(uint64_t* bar, uint32_t rank) {
-  uint32_t remote;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(rank));
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
-}
-__device__ __forceinline__ void tc2_commit_mc(uint64_t* bar) {
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
-          "r"(smem_u32(bar)),
-      "h"((uint16_t)3)
-      : "memory");
-}
-__device__ __forceinline__ void tc2_mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
-                                           uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n"
-      " .reg .pred p;\n"
-      " setp.ne.b32 p, %4, 0;\n"
-      " tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n"
-      "}\n" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void tc2_cluster_sync() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 // ---- epilogue ------------------------------------------------------------------------------------
@@ -262,60 +221,62 @@ struct TcRow {
   int pq;              // popcount of the query row: hamming = pq - D
   uint16_t* my_slot;   // where this thread publishes the D of its own k-th best
   uint32_t tag;        // (item & 63) << 10, marks published values of the current work item
+  TC_PROF(long long p_wait; long long p_pass1; long long p_pass2; long long p_nflag;)
 };
 
-// 32 consecutive TMEM columns of this thread's lane as 16 registers of two packed s16 values
+// 128 consecutive TMEM columns of this thread's lane as 64 registers of two packed s16 values
 // (.pack::16b keeps the low 16 bits of each column: D is in [-256, 256]); register i holds columns
 // 2i (low half) and 2i + 1 (high half).
-__device__ __forceinline__ void tc_ld32_packed(uint32_t taddr, uint32_t (&v)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
-        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
-        "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr)
-      : "memory");
+__device__ __forceinline__ void tc_ld128_packed(uint32_t taddr, uint32_t (&v)[64]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x64.pack::16b.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, %48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]), "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]), "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]), "=r"(v[49]), "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]), "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63])
+               : "r"(taddr)
+               : "memory");
 }
-__device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[16]) {
+__device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[64]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]),
-                 "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]),
-                 "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31]), "+r"(v[32]), "+r"(v[33]), "+r"(v[34]), "+r"(v[35]), "+r"(v[36]), "+r"(v[37]), "+r"(v[38]), "+r"(v[39]), "+r"(v[40]), "+r"(v[41]), "+r"(v[42]), "+r"(v[43]), "+r"(v[44]), "+r"(v[45]), "+r"(v[46]), "+r"(v[47]), "+r"(v[48]), "+r"(v[49]), "+r"(v[50]), "+r"(v[51]), "+r"(v[52]), "+r"(v[53]), "+r"(v[54]), "+r"(v[55]), "+r"(v[56]), "+r"(v[57]), "+r"(v[58]), "+r"(v[59]), "+r"(v[60]), "+r"(v[61]), "+r"(v[62]), "+r"(v[63])
+               :
+               : "memory");
+}
+// waits for up to four 8-column chunks fetched for pass 2
+__device__ __forceinline__ void tc_wait_ld(int (&a)[8], int (&b)[8], int (&c)[8], int (&d)[8]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
+                 "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7]),
+                 "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]), "+r"(c[4]), "+r"(c[5]), "+r"(c[6]), "+r"(c[7]),
+                 "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]), "+r"(d[4]), "+r"(d[5]), "+r"(d[6]), "+r"(d[7])
                :
                : "memory");
 }
 
-// Pass 1 (filter): does any of the 16 columns held by p[0..7] beat the packed threshold?
-// 4 VIMNMX(3).S16x2 for the max of 16 values, one more against the threshold, one compare.
+// Pass 1 (filter): does any of the 8 columns held by p[0..3] beat the packed threshold?
 __device__ __forceinline__ bool tc_beats(const uint32_t* p, uint32_t thrp) {
   const uint32_t t0 = __vimax3_s16x2(p[0], p[1], p[2]);
-  const uint32_t t1 = __vimax3_s16x2(p[3], p[4], p[5]);
-  const uint32_t t2 = __vimax3_s16x2(p[6], p[7], t0);
-  return __vimax3_s16x2(t1, t2, thrp) != thrp;   // some half is > its threshold half
+  return __vimax3_s16x2(t0, p[3], thrp) != thrp;   // some half is > its threshold half
 }
 
-// Pass 2 (exact): top-2 of one flagged 16-column chunk, v[j] = D(query row, train row col0 + j),
-// by a tournament over local keys D * 16 + (15 - j) -- larger is better and among equal D the
+// Pass 2 (exact): top-2 of one flagged 8-column chunk, v[j] = D(query row, train row col0 + j),
+// by a tournament over local keys D * 8 + (7 - j) -- larger is better and among equal D the
 // lowest column wins, OpenCV's (distance, lowest index) order -- merged into the running best-2.
 // The key IMADs run on the FMA pipe, the tournament on the ALU pipe.  Every lane of the warp runs
 // it (the merge is exact, so lanes that did not need it are unaffected).
 template <int K, bool MASKED>
-__device__ __forceinline__ void tc_chunk_exact(int (&v)[16], uint32_t col0, uint32_t nt, TcRow& r) {
+__device__ __forceinline__ void tc_chunk_exact(int (&v)[8], uint32_t col0, uint32_t nt, TcRow& r) {
   if (MASKED) {
 #pragma unroll
-    for (int j = 0; j < 16; ++j) v[j] = (col0 + j < nt) ? v[j] : TC_D_MASKED;
+    for (int j = 0; j < 8; ++j) v[j] = (col0 + j < nt) ? v[j] : TC_D_MASKED;
   }
-  int hi[8], lo[8];
+  int hi[4], lo[4];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int a = v[2 * i] * 16 + (15 - 2 * i);
-    const int b = v[2 * i + 1] * 16 + (14 - 2 * i);
+  for (int i = 0; i < 4; ++i) {
+    const int a = v[2 * i] * 8 + (7 - 2 * i);
+    const int b = v[2 * i + 1] * 8 + (6 - 2 * i);
     hi[i] = max(a, b);
     if (K == 2) lo[i] = min(a, b);
   }
 #pragma unroll
-  for (int n = 4; n >= 1; n >>= 1) {
+  for (int n = 2; n >= 1; n >>= 1) {
 #pragma unroll
     for (int i = 0; i < n; ++i) {
       if (K == 2) lo[i] = __vimax3_s32(min(hi[2 * i], hi[2 * i + 1]), lo[2 * i], lo[2 * i + 1]);
@@ -323,12 +284,12 @@ __device__ __forceinline__ void tc_chunk_exact(int (&v)[16], uint32_t col0, uint
     }
   }
   // local key -> global packed key
-  const uint32_t j1 = 15u - ((uint32_t)hi[0] & 15u);
-  uint32_t k1 = ((uint32_t)(r.pq - (hi[0] >> 4)) << TC_KEY_SHIFT) + (col0 + j1);
+  const uint32_t j1 = 7u - ((uint32_t)hi[0] & 7u);
+  uint32_t k1 = ((uint32_t)(r.pq - (hi[0] >> 3)) << TC_KEY_SHIFT) + (col0 + j1);
   if (MASKED) k1 = (col0 + j1 < nt) ? k1 : TC_KEY_NONE;
   if (K == 2) {
-    const uint32_t j2 = 15u - ((uint32_t)lo[0] & 15u);
-    uint32_t k2 = ((uint32_t)(r.pq - (lo[0] >> 4)) << TC_KEY_SHIFT) + (col0 + j2);
+    const uint32_t j2 = 7u - ((uint32_t)lo[0] & 7u);
+    uint32_t k2 = ((uint32_t)(r.pq - (lo[0] >> 3)) << TC_KEY_SHIFT) + (col0 + j2);
     if (MASKED) k2 = (col0 + j2 < nt) ? k2 : TC_KEY_NONE;
     r.m2 = min(min(r.m2, k2), max(r.m1, k1));   // k1 <= k2 and m1 <= m2
   }
@@ -342,44 +303,70 @@ __device__ __forceinline__ void tc_chunk_exact(int (&v)[16], uint32_t col0, uint
 }
 
 // This warpgroup's 128-column half of one accumulator, for this thread's lane, in two passes.
-//   Pass 1 streams the accumulator as packed s16 pairs and records, per 16-column chunk, whether
-//   any lane of the warp sees a value above its row's threshold: branch-free, 7 instructions per
-//   chunk and lane.  Pad columns of the last tile read as D = 0 and may raise a flag needlessly.
-//   Pass 2 re-reads only the flagged chunks (typically one or two of 16 once the thresholds have
-//   settled) as int32 and updates the best-2 exactly.
+//   Pass 1 reads the 128 columns as packed s16 pairs with ONE tcgen05.ld and records, per
+//   8-column chunk, whether any lane of the warp sees a value above its row's threshold:
+//   branch-free, 4 instructions per chunk and lane.  Pad columns of the last tile read as D = 0
+//   and may raise a flag needlessly.
+//   Pass 2 re-reads only the flagged chunks (typically one of 16 once the thresholds have
+//   settled) as int32, four at a time, and updates the best-2 exactly.
+// The accumulator is handed back to the MMA issuer (`acc_empty`) as soon as the LAST flagged chunk
+// is in registers, before its tournament runs: the tensor pipe needs the buffer of tile g back
+// within one stage time (tile g + 1 runs meanwhile), so what counts is how long the buffer is
+// held, not how long the tile takes.
+__device__ __forceinline__ uint32_t tc_pop(uint32_t& flags) {
+  const uint32_t c = (uint32_t)__ffs((int)flags) - 1u;
+  flags &= flags - 1u;
+  return c;
+}
+__device__ __forceinline__ void tc_release(uint64_t* acc_empty, int lane) {
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(acc_empty);
+}
 template <int K, bool MASKED>
-__device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint32_t nt, TcRow& r) {
+__device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint32_t nt, TcRow& r,
+                                        uint64_t* acc_empty, int lane) {
 #if TC_EXPERIMENT == 1
+  tc_release(acc_empty, lane);
   return;
 #endif
   const uint32_t thrp = (uint32_t)(max(r.thr, -32768) & 0xFFFF) * 0x10001u;
   uint32_t flags = 0;
-  uint32_t pa[16], pb[16];
-  tc_ld32_packed(taddr, pa);
+  {
+    uint32_t p[TC_HALF / 2];
+    tc_ld128_packed(taddr, p);
+    tc_wait_ld(p);
 #pragma unroll
-  for (int c = 0; c < TC_HALF / 32; c += 2) {
-    tc_wait_ld(pa);
-    tc_ld32_packed(taddr + (c + 1) * 32, pb);
-    flags |= tc_beats(pa, thrp) ? (1u << (2 * c)) : 0u;
-    flags |= tc_beats(pa + 8, thrp) ? (1u << (2 * c + 1)) : 0u;
-    tc_wait_ld(pb);
-    if (c + 2 < TC_HALF / 32) tc_ld32_packed(taddr + (c + 2) * 32, pa);
-    flags |= tc_beats(pb, thrp) ? (1u << (2 * c + 2)) : 0u;
-    flags |= tc_beats(pb + 8, thrp) ? (1u << (2 * c + 3)) : 0u;
+    for (int c = 0; c < TC_HALF / TC_CHUNK; ++c) flags |= tc_beats(p + 4 * c, thrp) ? (1u << c) : 0u;
   }
 #if TC_EXPERIMENT == 2 || TC_EXPERIMENT == 3
   if (flags == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
+  tc_release(acc_empty, lane);
   return;
 #endif
   flags = __reduce_or_sync(0xffffffffu, flags);
-  while (flags) {
-    const uint32_t c = (uint32_t)__ffs((int)flags) - 1u;
-    flags &= flags - 1u;
-    int v[16];
-    tc_ld16(taddr + c * TC_CHUNK, v);
-    tc_wait_ld(v);
-    tc_chunk_exact<K, MASKED>(v, col_base + c * TC_CHUNK, nt, r);
+  TC_PROF(r.p_nflag += __popc(flags);)
+  if (flags == 0) {
+    tc_release(acc_empty, lane);
+    return;
   }
+  TC_PROF(const long long c_p1 = clock64();)
+  do {   // warp-uniform: `flags` is the same in every lane
+    int v0[8], v1[8], v2[8], v3[8];
+    uint32_t c0 = tc_pop(flags), c1 = 0, c2 = 0, c3 = 0;
+    int n = 1;
+    tc_ld8(taddr + c0 * TC_CHUNK, v0);
+    if (flags) { c1 = tc_pop(flags); tc_ld8(taddr + c1 * TC_CHUNK, v1); n = 2; }
+    if (flags) { c2 = tc_pop(flags); tc_ld8(taddr + c2 * TC_CHUNK, v2); n = 3; }
+    if (flags) { c3 = tc_pop(flags); tc_ld8(taddr + c3 * TC_CHUNK, v3); n = 4; }
+    tc_wait_ld(v0, v1, v2, v3);
+    if (flags == 0) tc_release(acc_empty, lane);
+    tc_chunk_exact<K, MASKED>(v0, col_base + c0 * TC_CHUNK, nt, r);
+    if (n > 1) tc_chunk_exact<K, MASKED>(v1, col_base + c1 * TC_CHUNK, nt, r);
+    if (n > 2) tc_chunk_exact<K, MASKED>(v2, col_base + c2 * TC_CHUNK, nt, r);
+    if (n > 3) tc_chunk_exact<K, MASKED>(v3, col_base + c3 * TC_CHUNK, nt, r);
+  } while (flags);
+  TC_PROF(r.p_pass2 += clock64() - c_p1;)
 }
 
 // finds the work item that owns query tile `tile` (tile_begin is ascending; n_work >= 1)
@@ -394,11 +381,10 @@ __device__ __forceinline__ int tc_find_work(const TcWork* __restrict__ work, int
 
 // Epilogue of one work item (query tile `q_tile` of `w` against the whole train image) for one
 // thread of the two epilogue warpgroups; `g` counts train tiles across work items.  BOTH
-// warpgroups drain every accumulator, wg 0 its columns [0, 128) and wg 1 [128, 256): the MMA of
-// tile g + 2 needs the buffer of tile g back within ONE stage time (tile g + 1 runs meanwhile), so
-// what matters is the drain latency of a buffer, and splitting it halves that.
-// TWO_CTA: barriers live in the leader CTA.
-template <int K, bool TWO_CTA>
+// warpgroups drain every accumulator, wg 0 its columns [0, 128) and wg 1 [128, 256): what stalls
+// the tensor pipe is the LATENCY of getting a buffer back (the MMA of tile g + 2 needs the
+// buffer of tile g while tile g + 1 runs), so each buffer is drained by all eight warps.
+template <int K>
 __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, uint32_t item, uint32_t& g,
                                                  int warp, int lane, uint32_t tmem_base,
                                                  uint64_t* acc_full, uint64_t* acc_empty, uint2* merge,
@@ -417,26 +403,28 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   r.tag = (item & 63u) << 10;
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
   *r.my_slot = 0;
+  TC_PROF(r.p_wait = 0; r.p_pass1 = 0; r.p_pass2 = 0; r.p_nflag = 0; const long long p_t0 = clock64();)
   for (int t = 0; t < n_t; ++t, ++g) {
-    const uint32_t buf = g & 1u;
+    const uint32_t buf = g % TC_ACC;
+    TC_PROF(const long long c_w = clock64();)
     // the other warpgroup's k-th best D bounds this row too; an equal D with a lower train index
     // still has to be seen, hence the -1
     const uint32_t pv = *reinterpret_cast<const volatile uint16_t*>(peer_slot);
     if ((pv & 0xFC00u) == r.tag) r.thr = max(r.thr, (int)(pv & 1023u) - 513);
-    if (TWO_CTA) tc2_wait(&acc_full[buf], (g >> 1) & 1u); else tc_wait(&acc_full[buf], (g >> 1) & 1u);
+    tc_wait(&acc_full[buf], (g / TC_ACC) & 1u);
     tc_fence_after();
+    TC_PROF(const long long c_s = clock64(); r.p_wait += c_s - c_w;)
     const uint32_t taddr = taddr0 + buf * TC_N;
     const uint32_t col_base = (uint32_t)t * TC_N + wg * TC_HALF;
     if (t == n_t - 1 && (w.nt % TC_N) != 0)
-      tc_tile<K, true>(taddr, col_base, (uint32_t)w.nt, r);
+      tc_tile<K, true>(taddr, col_base, (uint32_t)w.nt, r, &acc_empty[buf], lane);
     else
-      tc_tile<K, false>(taddr, col_base, (uint32_t)w.nt, r);
-    tc_fence_before();
-    __syncwarp();
-    if (lane == 0) {
-      if (TWO_CTA) tc2_arrive_remote(&acc_empty[buf], 0); else mbar_arrive(&acc_empty[buf]);
-    }
+      tc_tile<K, false>(taddr, col_base, (uint32_t)w.nt, r, &acc_empty[buf], lane);
+    TC_PROF(r.p_pass1 += clock64() - c_s;)
   }
+  TC_PROF(if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 5) && item < 3)
+            printf("epi warp %d item %u: total %lld  wait acc_full %lld  tile work %lld (pass 2 %lld)  flagged %lld of %d chunks\n",
+                   warp, item, clock64() - p_t0, r.p_wait, r.p_pass1, r.p_pass2, r.p_nflag, n_t * (TC_HALF / TC_CHUNK));)
   // merge the two warpgroups' top-2 (disjoint train subsets) and write the row record
   uint2* slot = merge + (item & 1u) * TC_M;
   if (wg == 1) slot[row_in_tile] = make_uint2(r.m1, r.m2);
@@ -470,9 +458,10 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
   uint64_t* a_empty = bars + 1;
   uint64_t* b_full = bars + 2;
   uint64_t* b_empty = b_full + TC_STAGES;
-  uint64_t* acc_full = b_empty + TC_STAGES;   // [2]
-  uint64_t* acc_empty = acc_full + 2;          // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint64_t* acc_full = b_empty + TC_STAGES;        // [TC_ACC]
+  uint64_t* acc_empty = acc_full + TC_ACC;          // [TC_ACC]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + TC_ACC);
+  static_assert((2 + 2 * TC_STAGES + 2 * TC_ACC) * 8 + 4 <= 256, "barrier block overflows its 256 bytes");
   uint2* merge = reinterpret_cast<uint2*>(tail + 256);                                        // [2][128]
   uint16_t* share = reinterpret_cast<uint16_t*>(tail + 256 + 2 * TC_M * sizeof(uint2));       // [2][128]
 
@@ -491,14 +480,14 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 1);
     }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < TC_ACC; ++b) {
       mbar_init(&acc_full[b], 1);
       mbar_init(&acc_empty[b], 8);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
   if (tid < 2 * TC_M) share[tid] = 0;
-  if (warp == 9) {  // TMEM: all 512 columns (two 256-column int32 accumulators)
+  if (warp == 9) {  // TMEM: all 512 columns (TC_ACC accumulators of TC_N int32 columns)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
                      smem_u32(tmem_slot))
                  : "memory");
@@ -539,16 +528,22 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
     if (lane == 0) {
       uint32_t g = 0, item = 0;
       const uint32_t a_addr = smem_u32(sA);
+      TC_PROF(long long p_b = 0; long long p_acc = 0; long long p_a = 0; const long long p_t0 = clock64();)
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
         const TcWork w = work[tc_find_work(work, n_work, tile)];
         const int n_t = (w.nt + TC_N - 1) / TC_N;
+        TC_PROF(long long c0 = clock64();)
         tc_wait(a_full, item & 1u);
+        TC_PROF(p_a += clock64() - c0;)
         for (int t = 0; t < n_t; ++t, ++g) {
           const uint32_t s = g % TC_STAGES;
           const uint32_t ph = (g / TC_STAGES) & 1u;
-          const uint32_t buf = g & 1u;
+          const uint32_t buf = g % TC_ACC;
+          TC_PROF(long long c1 = clock64();)
           tc_wait(&b_full[s], ph);
-          tc_wait(&acc_empty[buf], ((g >> 1) & 1u) ^ 1u);
+          TC_PROF(long long c2 = clock64(); p_b += c2 - c1;)
+          tc_wait(&acc_empty[buf], ((g / TC_ACC) & 1u) ^ 1u);
+          TC_PROF(p_acc += clock64() - c2;)
           tc_fence_after();
           const uint32_t b_addr = smem_u32(sB + (size_t)s * TC_B_BYTES);
 #pragma unroll
@@ -562,13 +557,15 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
         }
         tc_commit(a_empty);
       }
+      TC_PROF(if (blockIdx.x == 0) printf("mma thread: total %lld  wait a_full %lld  b_full %lld  acc_empty %lld  stages %u\n",
+                                          clock64() - p_t0, p_a, p_b, p_acc, g);)
     }
   } else {
     // ===== epilogue warpgroups =====
     uint32_t g = 0, item = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
       const TcWork w = work[tc_find_work(work, n_work, tile)];
-      tc_epilogue_item<K, false>(w, tile - w.tile_begin, item, g, warp, lane, tmem_base, acc_full,
+      tc_epilogue_item<K>(w, tile - w.tile_begin, item, g, warp, lane, tmem_base, acc_full,
                                  acc_empty, merge, share, best2);
     }
   }
@@ -580,182 +577,6 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
   }
 }
-// ================================================================================================
-// 2-CTA variant (cta_group::2): a CTA pair shares every train tile.  Each CTA keeps its own 128
-// query rows (M = 256 across the pair) and stages only HALF of the 256 train rows of a tile
-// (N split), so L2 -> SM traffic and the shared-memory reads of the B operand are halved versus
-// the 1-CTA kernel (profiles/r01_ncu_hamming_tcgen05_1cta.txt: 10.3 TB/s crossbar reads).  The leader CTA's MMA thread issues for both
-// SMs; each CTA's accumulator (its 128 rows x 256 columns) lands in its own TMEM and is drained
-// by its own epilogue warpgroups exactly as in the 1-CTA kernel.
-//
-// Synchronisation.  Every CTA loads into its own shared memory and completes its own tx
-// barriers; the peer's warp 9 forwards "my half has landed" to the leader with a remote
-// mbarrier arrive, tcgen05.commit multicasts "stage free" / "accumulator full" / "A free" to
-// both CTAs, and both CTAs' epilogue warps arrive (locally / remotely) on the leader's
-// "accumulator empty" barrier.
-constexpr int TC2_STAGES = 4;
-constexpr int TC2_B_BYTES = (TC_N / 2) * TC_ROW_BYTES;  // 32 KB: this CTA's half of a train tile
-constexpr uint32_t TC2_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_N >> 3) << 17) |
-                               ((uint32_t)(256 >> 4) << 24);
-constexpr size_t TC2_SMEM_BYTES = 2 * (size_t)TC_A_BYTES + (size_t)TC2_STAGES * TC2_B_BYTES + TC_TAIL_BYTES;
-
-// `work[].tile_begin` holds the prefix sum of UNITS here: one unit = two consecutive query tiles
-// of one directed pair (CTA rank r of the cluster takes tile 2 * unit + r).
-template <int K>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
-hamming_tcgen05_2cta_kernel(const TcWork* __restrict__ work, int n_work, int total_units,
-                            int4* __restrict__ best2, int* __restrict__ error_flag) {
-  extern __shared__ __align__(1024) uint8_t smem[];
-  uint8_t* sA = smem;                               // [2][32 KB]
-  uint8_t* sB = smem + 2 * TC_A_BYTES;              // [TC2_STAGES][32 KB]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * TC_A_BYTES + TC2_STAGES * TC2_B_BYTES);
-  uint64_t* a_full = bars;                          // [2]
-  uint64_t* a_empty = a_full + 2;                   // [2]
-  uint64_t* peer_a_full = a_empty + 2;              // [2]  (leader's copy is used)
-  uint64_t* acc_full = peer_a_full + 2;             // [2]
-  uint64_t* acc_empty = acc_full + 2;               // [2]  (leader's copy is used, 8 arrivals)
-  uint64_t* b_full = acc_empty + 2;                 // [S]
-  uint64_t* b_empty = b_full + TC2_STAGES;          // [S]
-  uint64_t* peer_b_full = b_empty + TC2_STAGES;     // [S]  (leader's copy is used)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(peer_b_full + TC2_STAGES);
-  uint2* merge = reinterpret_cast<uint2*>(smem + 2 * TC_A_BYTES + TC2_STAGES * TC2_B_BYTES + 256);
-  uint16_t* share = reinterpret_cast<uint16_t*>(smem + 2 * TC_A_BYTES + TC2_STAGES * TC2_B_BYTES + 256 +
-                                                2 * TC_M * sizeof(uint2));
-
-  const int tid = threadIdx.x;
-  const int warp = tid >> 5;
-  const int lane = tid & 31;
-  uint32_t rank;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
-  const int cluster_id = blockIdx.x >> 1;
-  const int n_clusters = gridDim.x >> 1;
-
-  if ((smem_u32(smem) & 1023u) != 0) {   // same in both CTAs of the pair
-    if (tid == 0) atomicExch(error_flag, 1);
-    return;
-  }
-  if (tid == 0) {
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&a_full[i], 1);
-      mbar_init(&a_empty[i], 1);
-      mbar_init(&peer_a_full[i], 1);
-      mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 16);  // 8 epilogue warps x 2 CTAs
-    }
-    for (int s = 0; s < TC2_STAGES; ++s) {
-      mbar_init(&b_full[s], 1);
-      mbar_init(&b_empty[s], 1);
-      mbar_init(&peer_b_full[s], 1);
-    }
-    fence_mbar_init();
-  }
-  if (tid < 2 * TC_M) share[tid] = 0;
-  tc2_cluster_sync();
-  if (warp == 9) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
-                     smem_u32(tmem_slot))
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-  }
-  tc_fence_before();
-  tc2_cluster_sync();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 8) {
-    // ===== TMA producer (both CTAs: own query tile, own half of every train tile) =====
-    if (lane == 0) {
-      uint32_t g = 0, item = 0;
-      for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
-        const TcWork w = work[tc_find_work(work, n_work, unit)];
-        const int q_tile = 2 * (unit - w.tile_begin) + (int)rank;
-        const uint32_t ab = item & 1u;
-        tc2_wait(&a_empty[ab], ((item >> 1) & 1u) ^ 1u);
-        mbar_arrive_expect_tx(&a_full[ab], TC_A_BYTES);
-        uint8_t* a_dst = sA + (size_t)ab * TC_A_BYTES;
-        tma_bulk_g2s(a_dst, w.q_exp + (size_t)q_tile * (TC_M * 128), TC_M * 128, &a_full[ab]);
-        tma_bulk_g2s(a_dst + TC_M * 128,
-                     w.q_exp + (size_t)w.q_rows_pad * 128 + (size_t)q_tile * (TC_M * 128), TC_M * 128,
-                     &a_full[ab]);
-        const int n_t = (w.nt + TC_N - 1) / TC_N;
-        for (int t = 0; t < n_t; ++t, ++g) {
-          const uint32_t s = g % TC2_STAGES;
-          const uint32_t ph = (g / TC2_STAGES) & 1u;
-          tc2_wait(&b_empty[s], ph ^ 1u);
-          mbar_arrive_expect_tx(&b_full[s], TC2_B_BYTES);
-          uint8_t* dst = sB + (size_t)s * TC2_B_BYTES;
-          const size_t row0 = (size_t)t * TC_N + (size_t)rank * (TC_N / 2);
-          tma_bulk_g2s(dst, w.t_exp + row0 * 128, (TC_N / 2) * 128, &b_full[s]);
-          tma_bulk_g2s(dst + (TC_N / 2) * 128, w.t_exp + (size_t)w.t_rows_pad * 128 + row0 * 128,
-                       (TC_N / 2) * 128, &b_full[s]);
-        }
-      }
-    }
-  } else if (warp == 9) {
-    if (lane == 0 && rank == 0) {
-      // ===== MMA issuer (leader CTA, for both SMs) =====
-      uint32_t g = 0, item = 0;
-      for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
-        const TcWork w = work[tc_find_work(work, n_work, unit)];
-        const int n_t = (w.nt + TC_N - 1) / TC_N;
-        const uint32_t ab = item & 1u;
-        tc2_wait(&a_full[ab], (item >> 1) & 1u);
-        tc2_wait(&peer_a_full[ab], (item >> 1) & 1u);
-        const uint32_t a_addr = smem_u32(sA + (size_t)ab * TC_A_BYTES);
-        for (int t = 0; t < n_t; ++t, ++g) {
-          const uint32_t s = g % TC2_STAGES;
-          const uint32_t ph = (g / TC2_STAGES) & 1u;
-          const uint32_t buf = g & 1u;
-          tc2_wait(&b_full[s], ph);
-          tc2_wait(&peer_b_full[s], ph);
-          tc2_wait(&acc_empty[buf], ((g >> 1) & 1u) ^ 1u);
-          tc_fence_after();
-          const uint32_t b_addr = smem_u32(sB + (size_t)s * TC2_B_BYTES);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const uint64_t ad = tc_smem_desc(a_addr + (k >> 2) * (TC_M * 128) + (k & 3) * 32);
-            const uint64_t bd = tc_smem_desc(b_addr + (k >> 2) * ((TC_N / 2) * 128) + (k & 3) * 32);
-            tc2_mma_i8(tmem_base + buf * TC_N, ad, bd, TC2_IDESC, k > 0 ? 1u : 0u);
-          }
-          tc2_commit_mc(&b_empty[s]);
-          tc2_commit_mc(&acc_full[buf]);
-        }
-        tc2_commit_mc(&a_empty[ab]);
-      }
-    } else if (lane == 0) {
-      // ===== forwarder (peer CTA): tells the leader when this CTA's operands have landed =====
-      uint32_t g = 0, item = 0;
-      for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
-        const TcWork w = work[tc_find_work(work, n_work, unit)];
-        const int n_t = (w.nt + TC_N - 1) / TC_N;
-        const uint32_t ab = item & 1u;
-        tc2_wait(&a_full[ab], (item >> 1) & 1u);
-        tc2_arrive_remote(&peer_a_full[ab], 0);
-        for (int t = 0; t < n_t; ++t, ++g) {
-          const uint32_t s = g % TC2_STAGES;
-          tc2_wait(&b_full[s], (g / TC2_STAGES) & 1u);
-          tc2_arrive_remote(&peer_b_full[s], 0);
-        }
-      }
-    }
-  } else {
-    // ===== epilogue warpgroups =====
-    uint32_t g = 0, item = 0;
-    for (int unit = cluster_id; unit < total_units; unit += n_clusters, ++item) {
-      const TcWork w = work[tc_find_work(work, n_work, unit)];
-      tc_epilogue_item<K, true>(w, 2 * (unit - w.tile_begin) + (int)rank, item, g, warp, lane, tmem_base,
-                                acc_full, acc_empty, merge, share, best2);
-    }
-  }
-
-  tc_fence_before();
-  tc2_cluster_sync();   // no CTA of the pair may leave while the other can still signal it
-  if (warp == 9) {
-    tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
-  }
-}
-
 // ---- host side --------------------------------------------------------------------------------------
 
 constexpr size_t TC_SMEM_BYTES = (size_t)TC_A_BYTES + (size_t)TC_STAGES * TC_B_BYTES + TC_TAIL_BYTES;
@@ -801,9 +622,8 @@ static cudaError_t tc_launch(ssp_ctx* ctx, Kern kern, size_t smem, int grid, int
   return cudaGetLastError();
 }
 
-// `two_cta`: SSP_HAMMING_TENSOR (cta_group::2 pairs) versus SSP_HAMMING_TENSOR_1CTA.
 cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& work, int k,
-                                  bool two_cta, std::string* why_not) {
+                                  std::string* why_not) {
   cudaError_t e = ensure_expanded(ctx);
   if (e != cudaSuccess) return e;
   if ((reinterpret_cast<uintptr_t>(ctx->h_expanded.p) & 15) != 0) {
@@ -812,7 +632,7 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
   }
   std::vector<TcWork> tw;
   tw.reserve(work.size());
-  int total = 0;  // query tiles (1-CTA) or units of two query tiles (2-CTA)
+  int total = 0;  // query tiles
   for (const HammingWork& w : work) {
     if (w.nq <= 0 || w.nt <= 0) continue;  // rows of such items keep the "no neighbour" memset
     TcWork t;
@@ -827,8 +647,7 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
     t.out_row = w.out_row;
     t.tile_begin = total;
     t.pad_ = 0;
-    const int q_tiles = (w.nq + TC_M - 1) / TC_M;
-    total += two_cta ? (q_tiles + 1) / 2 : q_tiles;
+    total += (w.nq + TC_M - 1) / TC_M;
     tw.push_back(t);
   }
   if (tw.empty()) {
@@ -845,15 +664,9 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
   // tcgen05 kernel alone (bank expansion happens once per upload, outside)
   if ((e = cudaEventRecord(ctx->ev0, ctx->stream)) != cudaSuccess) return e;
   const int n_work = (int)tw.size();
-  if (two_cta) {
-    const int clusters = total < ctx->sm_count / 2 ? total : ctx->sm_count / 2;
-    e = (k == 2) ? tc_launch(ctx, hamming_tcgen05_2cta_kernel<2>, TC2_SMEM_BYTES, 2 * clusters, n_work, total)
-                 : tc_launch(ctx, hamming_tcgen05_2cta_kernel<1>, TC2_SMEM_BYTES, 2 * clusters, n_work, total);
-  } else {
-    const int grid = total < ctx->sm_count ? total : ctx->sm_count;
-    e = (k == 2) ? tc_launch(ctx, hamming_tcgen05_kernel<2>, TC_SMEM_BYTES, grid, n_work, total)
-                 : tc_launch(ctx, hamming_tcgen05_kernel<1>, TC_SMEM_BYTES, grid, n_work, total);
-  }
+  const int grid = total < ctx->sm_count ? total : ctx->sm_count;
+  e = (k == 2) ? tc_launch(ctx, hamming_tcgen05_kernel<2>, TC_SMEM_BYTES, grid, n_work, total)
+               : tc_launch(ctx, hamming_tcgen05_kernel<1>, TC_SMEM_BYTES, grid, n_work, total);
   if (e != cudaSuccess) return e;
   if ((e = cudaEventRecord(ctx->ev1, ctx->stream)) != cudaSuccess) return e;
   ctx->h_launches += 1;
