@@ -39,6 +39,8 @@ WORKLOADS = {
                name="synthetic stand-in for example_01b: 21 images x 1000 descriptors, 210 pairs"),
 }
 POPC_PER_COMPARISON = 8          # algorithmic: 8 x (32-bit XOR + POPC) per 256-bit distance
+OPS_PER_COMPARISON = 512         # tensor variant: 256 int8 multiply-adds = 512 ops per distance
+I8_OPS_PER_CLK_PER_SM = 16384    # tcgen05 kind::i8: 8192 MAC/clk/SM (M128 N256 K32 issues every 128 clk)
 BYTES_PER_ROW = 32
 
 
@@ -167,7 +169,7 @@ def run_reference(args, wl, sets, pairs):
     return {
         "impl": "reference", "metric": "image_pairs_matched_per_sec", "value": value, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 popcount", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 (256-bit Hamming, OpenCV SIMD popcount)", "data": "synthetic",
         "config": {"workload": wl["name"], "mode": args.mode, "pairs": len(pairs)},
         "gcmp_per_s": cmps / dt / 1e9,
         "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": cv.getNumThreads(), "kind": "reference",
@@ -186,6 +188,29 @@ def popc_peak_per_clk_per_sm():
             return float(json.load(f)["popc"]), "measured (profiles/pipe_microbench_r01.json)"
     except Exception:
         return 16.0, "planning figure (CUDA programming guide, 16 POPC/clk/SM)"
+
+
+def measured_tensor_peak():
+    """Dense int8 peak in TOP/s.  MEASURED_PEAKS.json holds the cuBLAS bf16 figure of this pool's
+    B200s; kind::i8 runs at twice the bf16 rate per SM and clock on sm_100, so the int8 peak is
+    2 x that (burst figure: the kernel is timed alone)."""
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            bf16 = float(json.load(f)["bf16_tflops"])
+        return 2.0 * bf16, f"2 x measured cuBLAS bf16 burst ({bf16:g} TF/s, MEASURED_PEAKS.json): int8 runs at twice the bf16 rate"
+    except Exception:
+        return 4500.0, "nominal dense int8 (B200_PROFILING.md fallback: 2 x 2250 bf16)"
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel on this
+    workload, from the committed `ncu --set full` capture (profiles/traffic_r01.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
+            t = json.load(f)[kernel]
+        return float(t["dram_bytes"]), t["source"]
+    except Exception:
+        return None, None
 
 
 def measured_hbm_peak():
@@ -302,33 +327,59 @@ def run_ours(args, wl, sets, pairs):
     info = eng.device_info()
     clk = clocks.summary()
     main_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
-    achieved = comparisons_local / (main_ms / 1e3) / 1e9 if main_ms > 0 else 0.0   # Gcmp/s, this rank
-    popc_rate, popc_src = popc_peak_per_clk_per_sm()
+    gcmp = comparisons_local / (main_ms / 1e3) / 1e9 if main_ms > 0 else 0.0   # Gcmp/s, this rank
     sm_max_mhz = clk.get("sm_max_mhz") or info["sm_clock_khz"] / 1e3
-    peak = info["sm_count"] * popc_rate * sm_max_mhz * 1e6 / POPC_PER_COMPARISON / 1e9
+    held = (clk["sm_mhz"] / sm_max_mhz) if clk.get("sm_mhz") else None
     hbm_peak, hbm_src = measured_hbm_peak()
     rows_q = sum(sets[a].shape[0] for a, _ in local_pairs)
     rows_t = sum(sets[b].shape[0] for _, b in local_pairs)
-    algo_bytes = (rows_q + rows_t) * BYTES_PER_ROW + rows_q * 16    # each operand once + best-2 records
-    roofline = {
-        "bound": "int-pipe (POPC)", "kernel": "hamming_popc_kernel" if args.variant != "tensor" else "hamming_tensor_kernel",
-        "achieved": achieved, "peak": peak, "unit": "Gcmp/s", "frac": achieved / peak if peak else None,
-        "peak_definition": f"{info['sm_count']} SMs x {popc_rate:g} POPC/clk/SM [{popc_src}] x {sm_max_mhz:g} MHz / "
-                           f"{POPC_PER_COMPARISON} POPC per 256-bit comparison",
-        "frac_at_held_clock": (achieved / (peak * clk["sm_mhz"] / sm_max_mhz)) if clk.get("sm_mhz") else None,
+    tensor = args.variant in ("auto", "tensor")
+    if tensor:
+        # algorithmic work: one 256-term int8 dot product per comparison = 512 integer ops
+        achieved = gcmp * OPS_PER_COMPARISON / 1e3                      # TOP/s
+        peak, peak_src = measured_tensor_peak()
+        pipe_peak = info["sm_count"] * I8_OPS_PER_CLK_PER_SM * sm_max_mhz * 1e6 / 1e12
+        algo_bytes = (rows_q + rows_t) * 256 + rows_q * 16              # expanded operands once + best-2 records
+        roofline = {
+            "bound": "tensor", "kernel": "hamming_tcgen05_kernel", "achieved": achieved, "peak": peak,
+            "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+            "ops": "int8 multiply-add counted as 2 ops; s8 x s8 -> s32, exact",
+            "peak_definition": peak_src,
+            "pipe_peak_at_max_clock": pipe_peak,
+            "pipe_peak_definition": f"{info['sm_count']} SMs x {I8_OPS_PER_CLK_PER_SM} int8 ops/clk/SM (tcgen05 kind::i8 "
+                                    f"M128 N256 K32 = 128 clk, measured by the MMA-only probe) x {sm_max_mhz:g} MHz",
+            "frac_of_pipe_at_max_clock": achieved / pipe_peak,
+            "frac_of_pipe_at_held_clock": achieved / (pipe_peak * held) if held else None,
+            "gcmp_per_s": gcmp,
+        }
+    else:
+        popc_rate, popc_src = popc_peak_per_clk_per_sm()
+        popc_per_cmp = 4 if args.variant == "popc_csa" else POPC_PER_COMPARISON
+        peak = info["sm_count"] * popc_rate * sm_max_mhz * 1e6 / POPC_PER_COMPARISON / 1e9
+        algo_bytes = (rows_q + rows_t) * BYTES_PER_ROW + rows_q * 16    # each operand once + best-2 records
+        roofline = {
+            "bound": "int-pipe (POPC)", "kernel": "hamming_popc_kernel", "achieved": gcmp, "peak": peak,
+            "unit": "Gcmp/s", "frac": gcmp / peak if peak else None,
+            "peak_definition": f"{info['sm_count']} SMs x {popc_rate:g} POPC/clk/SM [{popc_src}] x {sm_max_mhz:g} MHz / "
+                               f"{POPC_PER_COMPARISON} POPC per 256-bit comparison (the CSA variant issues {popc_per_cmp})",
+            "frac_at_held_clock": gcmp / (peak * held) if held else None,
+        }
+    traffic, traffic_src = ncu_traffic(roofline["kernel"])
+    roofline.update({
         "kernel_ms_per_launch": main_ms, "comparisons_per_launch": comparisons_local,
-        "traffic": None,
+        "traffic": traffic, "traffic_source": traffic_src,
         "hbm": {"achieved": algo_bytes / (main_ms / 1e3) / 1e9 if main_ms > 0 else None, "peak": hbm_peak,
                 "unit": "GB/s", "algorithmic_bytes_per_launch": algo_bytes, "peak_source": hbm_src,
                 "frac": (algo_bytes / (main_ms / 1e3) / 1e9) / hbm_peak if main_ms > 0 else None},
-    }
+    })
 
     line = None
     if rank == 0:
         line = {
             "metric": "image_pairs_matched_per_sec", "value": value, "unit": "pairs/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u32 popcount",
+            "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+            "dtype": "s8 x s8 -> s32 (exact)" if tensor else "u32 popcount",
             "data": "synthetic",
             "config": {"workload": wl["name"], "mode": args.mode, "variant": args.variant, "pairs": len(pairs),
                        "descriptors_per_image": wl["n_desc"], "sharding": f"pairs round-robin over {world} rank(s)",

@@ -50,10 +50,8 @@ extern "C" {
 #define SSP_HAMMING_AUTO 0
 #define SSP_HAMMING_POPC 1     /* LOP3 + POPC CUDA-core kernel, TMA-bulk staged train tiles         */
 #define SSP_HAMMING_POPC_CSA 2 /* same, carry-save-adder compression before POPC (4 POPC/compare)   */
-#define SSP_HAMMING_TENSOR 3   /* tcgen05 kind::i8 contraction on +-1-expanded descriptors, CTA pairs
-                                  (cta_group::2), accumulators in TMEM                             */
-#define SSP_HAMMING_TENSOR_1CTA 4 /* same contraction with one CTA per tile (cta_group::1); kept for
-                                     the ncu comparison that motivated the pair variant            */
+#define SSP_HAMMING_TENSOR 3   /* tcgen05 kind::i8 contraction on int8-expanded descriptors (+-1 query x
+                                  0/1 train), accumulators in TMEM; what SSP_HAMMING_AUTO selects   */
 
 /* polygon compare options */
 #define SSP_SHIFT_CANONICAL 0       /* parity mode: reference compares shift 0 only (cbpm:992-1016) */

@@ -15,7 +15,7 @@ OK = 0
 ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_CAPACITY, ERR_DOMAIN = -1, -2, -3, -4, -5
 MEM_HOST, MEM_DEVICE = 0, 1
 MODE_KNN2_RATIO, MODE_CROSSCHECK = 0, 1
-HAMMING_AUTO, HAMMING_POPC, HAMMING_POPC_CSA, HAMMING_TENSOR, HAMMING_TENSOR_1CTA = 0, 1, 2, 3, 4
+HAMMING_AUTO, HAMMING_POPC, HAMMING_POPC_CSA, HAMMING_TENSOR = 0, 1, 2, 3
 SHIFT_CANONICAL, SHIFT_MIN_OVER_SHIFTS = 0, 1
 PRECISION_FP64, PRECISION_FP32 = 0, 1
 POLY_VALID, POLY_SHORT_SIDE, POLY_NOT_CONVEX, POLY_DOMAIN, POLY_BAD_INDEX = 0, 1, 2, 3, 4

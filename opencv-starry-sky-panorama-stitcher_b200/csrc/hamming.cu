@@ -260,7 +260,7 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
               "ssp_hamming_match_pairs: match_offsets is NULL");
   SSP_REQUIRE(ctx, mode == SSP_MODE_KNN2_RATIO || mode == SSP_MODE_CROSSCHECK, SSP_ERR_INVALID,
               "ssp_hamming_match_pairs: unknown mode %d", mode);
-  SSP_REQUIRE(ctx, variant >= SSP_HAMMING_AUTO && variant <= SSP_HAMMING_TENSOR_1CTA, SSP_ERR_INVALID,
+  SSP_REQUIRE(ctx, variant >= SSP_HAMMING_AUTO && variant <= SSP_HAMMING_TENSOR, SSP_ERR_INVALID,
               "ssp_hamming_match_pairs: unknown variant %d", variant);
   if (mode == SSP_MODE_KNN2_RATIO)
     SSP_REQUIRE(ctx, ratio_num > 0 && ratio_den > 0, SSP_ERR_INVALID,
@@ -346,9 +346,9 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
   const int k = cross ? 1 : 2;
   if (!work.empty()) {
     int v = variant;
-    if (v == SSP_HAMMING_AUTO) v = SSP_HAMMING_POPC_CSA;
+    if (v == SSP_HAMMING_AUTO) v = SSP_HAMMING_TENSOR;   // fastest at every size measured
     SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    const bool tensor = (v == SSP_HAMMING_TENSOR || v == SSP_HAMMING_TENSOR_1CTA);
+    const bool tensor = (v == SSP_HAMMING_TENSOR);
     if (tensor) {
       std::string why;
       cudaError_t e = launch_hamming_tensor(ctx, work, k, &why);

@@ -50,7 +50,7 @@ class PolygonMatchResult:
 
 _MODES = {"knn2_ratio": N.MODE_KNN2_RATIO, "crosscheck": N.MODE_CROSSCHECK}
 _VARIANTS = {"auto": N.HAMMING_AUTO, "popc": N.HAMMING_POPC, "popc_csa": N.HAMMING_POPC_CSA,
-             "tensor": N.HAMMING_TENSOR, "tensor_1cta": N.HAMMING_TENSOR_1CTA}
+             "tensor": N.HAMMING_TENSOR}
 
 
 def _ratio_terms(ratio):

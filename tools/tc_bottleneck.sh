@@ -12,7 +12,7 @@ OUT=${1:-../../gpurun_out/tc_bottleneck.txt}
 for n in ${EXPERIMENTS:-1 2 3 0}; do
   rm -f build/hamming_tensor.o
   make EXTRA=-DTC_EXPERIMENT=$n -j8 > /dev/null
-  for v in ${VARIANTS:-tensor_1cta tensor}; do
+  for v in ${VARIANTS:-tensor}; do
     (cd ../.. && python bench.py --steps 3 --warmup 2 --variant $v --no-cpu-baseline 2>/dev/null |
       python -c "
 import json,sys

@@ -6,6 +6,6 @@ set -e
 cd "$(dirname "$0")/../opencv-starry-sky-panorama-stitcher_b200/csrc"
 rm -f build/hamming_tensor.o
 make EXTRA=-DTC_PROFILE=1 -j8 > /dev/null
-(cd ../.. && python bench.py --steps 1 --warmup 0 --variant ${1:-tensor_1cta} --no-cpu-baseline 2>&1 | grep -E "mma thread|epi warp" | head -${2:-16})
+(cd ../.. && python bench.py --steps 1 --warmup 0 --variant ${1:-tensor} --no-cpu-baseline 2>&1 | grep -E "mma thread|epi warp" | head -${2:-16})
 rm -f build/hamming_tensor.o
 make -j8 > /dev/null
