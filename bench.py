@@ -37,7 +37,14 @@ WORKLOADS = {
                name="synthetic 200-image sweep x 20k descriptors, 19900 pairs"),
     "c1": dict(n_images=21, n_desc=1_000, seed=0,
                name="synthetic stand-in for example_01b: 21 images x 1000 descriptors, 210 pairs"),
+    # star-polygon path (kernels 2 + 3); see run_polygon_*
+    "c4": dict(n_images=21, n_stars=2_000, seed=2, polygon=True,
+               name="synthetic star fields 21 images x 2k stars, f=1135 px, 894x1342, 5-gon polygon matching, all 210 pairs"),
+    "c4cap": dict(n_images=21, n_polygons=15_000, seed=3, polygon=True,
+                  name="polygon banks at the reference's cap: 21 images x 15000 polygons, all 210 pairs (kernel 3 only)"),
 }
+FLOP_PER_EVALUATION = 45         # 15 sub + 15 mul + 15 add per polygon-pair evaluation
+IMG_W, IMG_H, FOCAL = 1342, 894, 1135.0
 POPC_PER_COMPARISON = 8          # algorithmic: 8 x (32-bit XOR + POPC) per 256-bit distance
 OPS_PER_COMPARISON = 512         # tensor variant: 256 int8 multiply-adds = 512 ops per distance
 I8_OPS_PER_CLK_PER_SM = 16384    # tcgen05 kind::i8: 8192 MAC/clk/SM (M128 N256 K32 issues every 128 clk)
@@ -55,6 +62,7 @@ def parse():
     ap.add_argument("--variant", default="auto")
     ap.add_argument("--cpu-sample-pairs", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fp32", action="store_true", help="polygon workloads: non-parity fp32 compare")
     return ap.parse_args()
 
 
@@ -400,6 +408,247 @@ def run_ours(args, wl, sets, pairs):
     return line
 
 
+# ---- star-polygon path (kernels 2 + 3) ------------------------------------------------------------
+def polygon_inputs(wl):
+    """Host-side inputs of the polygon workloads.  c4: star fields + the reference's own candidate
+    reduction (cbpm:261-443, Ward clustering on the host exactly as the reference does it; brightness
+    supplied directly).  c4cap: ready-made normalised 15-dim polygon rows at the cap."""
+    from ssp_b200 import synthetic as synth
+    if "n_polygons" in wl:
+        return {"feat": synth.polygon_feature_bank(wl["n_images"], wl["n_polygons"], seed=wl["seed"])}
+    import cv2
+    import ssp_b200
+    xy, br, _ = synth.star_fields(wl["n_images"], wl["n_stars"], seed=wl["seed"], img_w=IMG_W, img_h=IMG_H, focal=FOCAL)
+    frame = np.zeros((IMG_H, IMG_W, 3), dtype=np.uint8)       # only .shape is read
+    bf = ssp_b200.BFPolygonMatcher("/tmp", "a", "b", 0, 1, frame.shape, FOCAL, write_debug_images=False)
+    cands = []
+    for i in range(wl["n_images"]):
+        kps = tuple(cv2.KeyPoint(float(p[0]), float(p[1]), 4.0) for p in xy[i].astype(np.float32))
+        c = bf.reduce_amount_of_keypoints_and_create_polygon_spanning_tuples_of_keypoints(
+            kps, f"img{i}", frame, 5, 15000, _brightness=br[i])
+        cands.append(np.array(sorted(c), dtype=np.int32).reshape(-1, 5))
+    return {"xy": xy, "br": br, "cands": cands}
+
+
+def polygon_cpu_pair(inp, oracle, k, pairs, state):
+    """CPU port of ONE pair's share of the path, as the reference amortises it: every image is
+    measured once for all its pairs (polygon_data_store cache, cbpm:744-748), i.e. n_images/n_pairs
+    of an image per pair, then the (P1, P2) numpy compare + row argmin + threshold of that pair."""
+    a, b = pairs[k % len(pairs)]
+    evals = 0
+    if "cands" in inp:
+        share = len(inp["xy"]) / len(pairs)
+        c = inp["cands"][a]
+        n = max(1, int(round(len(c) * share)))
+        lo = (k * n) % max(1, len(c) - n)
+        oracle.characteristics(inp["xy"][a], inp["br"][a], c[lo:lo + n])
+        f1, f2 = state["feat"][a], state["feat"][b]
+    else:
+        f1, f2 = inp["feat"][a][:state["rows"]], inp["feat"][b]
+    m = oracle.compare(f1, f2)
+    oracle.select(m)
+    evals += f1.shape[0] * f2.shape[0]
+    return evals
+
+
+def polygon_cpu_state(inp, oracle, pairs, steps):
+    """Untimed preparation of the CPU leg: the polygon rows the sampled pairs compare."""
+    if "cands" not in inp:
+        return {"rows": 1500}     # 1500 x 15000 rows per step: numpy needs ~1.6 GB of temporaries
+    need = sorted({i for k in range(steps) for i in pairs[k % len(pairs)]})
+    feat = {}
+    for i in need:
+        feat[i] = np.ascontiguousarray(oracle.characteristics(inp["xy"][i], inp["br"][i], inp["cands"][i])["feat"])
+    return {"feat": feat}
+
+
+def run_polygon_reference(args, wl, inp, pairs):
+    from oracle.polygon_oracle import PolygonOracle
+    oracle = PolygonOracle((IMG_H, IMG_W, 3), FOCAL)
+    sample_pairs = [pairs[0], pairs[len(pairs) // 2]]
+    state = polygon_cpu_state(inp, oracle, sample_pairs, args.steps + args.warmup)
+    k = 0
+    for _ in range(args.warmup):
+        polygon_cpu_pair(inp, oracle, k, sample_pairs, state)
+        k += 1
+    t0 = time.perf_counter()
+    evals = 0
+    for _ in range(args.steps):
+        evals += polygon_cpu_pair(inp, oracle, k, sample_pairs, state)
+        k += 1
+    dt = time.perf_counter() - t0
+    scale = 1.0
+    if "cands" not in inp:      # a step compared only state["rows"] of the first image's rows
+        scale = state["rows"] / inp["feat"][0].shape[0]
+    value = args.steps * scale / dt
+    sample = ("CPU port (oracle/polygon_oracle.py: Python measure loop + numpy (P1,P2) compare, the reference's "
+              "algorithm, 1 thread) on one pair per step incl. its 1/10-image share of polygon measuring"
+              if "cands" in inp else
+              f"CPU port numpy compare of {state['rows']} x {inp['feat'][1].shape[0]} polygon rows per step, scaled to a full pair, 1 thread")
+    return {
+        "impl": "reference", "metric": "image_pairs_matched_per_sec", "value": value, "unit": "pairs/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl["name"], "pairs": len(pairs)},
+        "polygon_evals_per_s": evals / dt,
+        "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": 1, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+def fp_pipe_peaks():
+    """FP64 / FP32 issue rates measured on this pool's B200 by tools/pipe_microbench (committed
+    summary, thread-ops per clock per SM); None when the summary has no such entry."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "pipe_microbench_r01.json")) as f:
+            j = json.load(f)
+        return {k: float(j[k]) for k in ("dfma", "dsub_dmul_dadd_total", "ffma") if k in j}
+    except Exception:
+        return {}
+
+
+def run_polygon_ours(args, wl, inp, pairs):
+    import torch
+    import ssp_b200
+    from ssp_b200.distributed import shard_pairs
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    eng = ssp_b200.Engine(local_rank)
+    stream = torch.cuda.current_stream(dev)
+    eng.set_stream(stream.cuda_stream)
+    n_img = wl["n_images"]
+    local_pairs, _ = shard_pairs(pairs, rank, world)
+    measured = "cands" in inp
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # every rank holds the full star / polygon bank (KBs..MBs) and measures all images itself:
+    # kernel 2 is microseconds per image, cheaper than any exchange (SURVEY §8(e))
+    if measured:
+        eng.upload_star_bank(inp["xy"], inp["br"], IMG_W, IMG_H, FOCAL)
+        cand_dev = [torch.from_numpy(c).to(dev) for c in inp["cands"]]
+        h2d = sum(a.nbytes for a in inp["xy"]) + sum(b.nbytes for b in inp["br"]) + sum(c.nbytes for c in inp["cands"])
+    else:
+        for i in range(n_img):
+            eng.polygon_upload_features(i, inp["feat"][i])
+        h2d = sum(f.nbytes for f in inp["feat"])
+    h2d += len(local_pairs) * 8
+
+    def step_resident():
+        n = 0
+        if measured:
+            for i in range(n_img):
+                eng.polygon_measure_resident(i, cand_dev[i].data_ptr(), cand_dev[i].shape[0])
+                n += 3
+        res = eng.polygon_match_pairs(local_pairs, fp32=args.fp32, fetch=False)
+        return res, n + eng.polygon_last_stats()["launches"]
+
+    def step_e2e():
+        if measured:
+            eng.upload_star_bank(inp["xy"], inp["br"], IMG_W, IMG_H, FOCAL)
+            for i in range(n_img):
+                eng.polygon_measure(i, inp["cands"][i])
+        else:
+            for i in range(n_img):
+                eng.polygon_upload_features(i, inp["feat"][i])
+        return eng.polygon_match_pairs(local_pairs, fp32=args.fp32)
+
+    kernel_ms, launches = [], 0
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    with ClockSampler(local_rank) as clocks:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(args.steps):
+            res, n = step_resident()
+            launches += n
+            kernel_ms.append(eng.polygon_last_stats()["main_kernel_ms"])
+        ev1.record(stream)
+        barrier()
+    elapsed_ms = ev0.elapsed_time(ev1)
+    evals_local = eng.polygon_last_stats()["evaluations"]
+    n_matches_local = int(res.offsets[-1])
+    n_polys = [eng.polygon_count(i) for i in range(n_img)]
+    if dist is not None:
+        t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+        c = torch.tensor([evals_local, n_matches_local, launches], dtype=torch.int64, device=dev)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        evals, n_matches, launches = int(c[0]), int(c[1]), int(c[2])
+    else:
+        evals, n_matches = evals_local, n_matches_local
+    ms_per_step = elapsed_ms / args.steps
+
+    e2e_steps = max(1, min(args.steps, 3))
+    step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        out = step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    d2h = int(out.offsets[-1]) * 16 + (len(local_pairs) + 1) * 8
+
+    info = eng.device_info()
+    clk = clocks.summary()
+    sm_max_mhz = clk.get("sm_max_mhz") or info["sm_clock_khz"] / 1e3
+    main_ms = float(np.mean(kernel_ms))
+    rates = fp_pipe_peaks()
+    key, what = ("ffma", "FFMA") if args.fp32 else ("dsub_dmul_dadd_total", "unfused DSUB+DMUL+DADD (numpy's rounding)")
+    flop_per_clk_sm = rates.get(key)
+    if flop_per_clk_sm is not None and args.fp32:
+        flop_per_clk_sm *= 2.0          # an FFMA is 2 flop; the fp32 mode needs 15 FSUB + 15 FFMA = 45 flop in 30 issues
+        flop_per_clk_sm *= 45.0 / 60.0  # 30 issue slots carry 45 flop, not 60
+    peak = info["sm_count"] * flop_per_clk_sm * sm_max_mhz * 1e6 / 1e12 if flop_per_clk_sm else None
+    achieved = evals_local * FLOP_PER_EVALUATION / (main_ms / 1e3) / 1e12 if main_ms > 0 else None
+    roofline = {
+        "bound": "fp32-pipe" if args.fp32 else "fp64-pipe", "kernel": "poly_compare_f32_kernel" if args.fp32 else "poly_compare_f64_kernel",
+        "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak and achieved else None,
+        "peak_definition": (f"{info['sm_count']} SMs x {flop_per_clk_sm:.1f} flop/clk/SM ({what}, measured: "
+                            f"profiles/pipe_microbench_r01.json) x {sm_max_mhz:g} MHz") if peak else "not measured",
+        "flop_per_evaluation": FLOP_PER_EVALUATION, "kernel_ms_per_launch": main_ms,
+        "evaluations_per_launch": evals_local, "traffic": None,
+    }
+    line = None
+    if rank == 0:
+        line = {
+            "metric": "image_pairs_matched_per_sec", "value": len(pairs) / (ms_per_step / 1e3), "unit": "pairs/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+            "dtype": "f32" if args.fp32 else "f64", "data": "synthetic",
+            "config": {"workload": wl["name"], "pairs": len(pairs), "polygons_per_image": [min(n_polys), max(n_polys)],
+                       "candidates_per_image": [min(map(len, inp["cands"])), max(map(len, inp["cands"]))] if measured else None,
+                       "threshold": 0.1566, "sharding": f"pairs round-robin over {world} rank(s)",
+                       "l2": "inputs are far below L2 size by nature of the path (<= 38 MB polygon bank); no flush"},
+            "polygon_evals_per_s": evals / (ms_per_step / 1e3), "matches_per_step": n_matches,
+            "e2e": {"value": len(pairs) * e2e_steps / e2e_s, "unit": "pairs/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+            "gpu_launches": launches, "clocks": clk, "roofline": roofline,
+        }
+    eng.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return line
+
+
 def main():
     args = parse()
     wl = WORKLOADS[args.workload]
@@ -407,6 +656,19 @@ def main():
     if args.impl == "reference" and rank != 0:
         return 0  # rank 0 alone runs the CPU arm
     from ssp_b200 import synthetic as synth
+    if wl.get("polygon"):
+        inp = polygon_inputs(wl)
+        pairs = synth.all_pairs(wl["n_images"])
+        if args.impl == "reference":
+            print(json.dumps(run_polygon_reference(args, wl, inp, pairs)), flush=True)
+            return 0
+        line = run_polygon_ours(args, wl, inp, pairs)
+        if rank == 0:
+            if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not args.no_cpu_baseline:
+                ref_args = argparse.Namespace(**{**vars(args), "steps": 2, "warmup": 0})
+                line["cpu_baseline"] = run_polygon_reference(ref_args, wl, inp, pairs)["cpu_baseline"]
+            print(json.dumps(line), flush=True)
+        return 0
     # every rank generates the same seeded input (cheap next to shipping it); rank 0's copy is
     # the "host input" of the e2e leg
     sets = synth.descriptor_bank(wl["n_images"], wl["n_desc"], seed=wl["seed"])

@@ -183,10 +183,12 @@ class BFPolygonMatcher:
 
     def reduce_amount_of_keypoints_and_create_polygon_spanning_tuples_of_keypoints(
             self, keypoints, img_filename, workscale_img, n_polygon_sides,
-            maximum_number_of_polygons_per_image_region=15000):
+            maximum_number_of_polygons_per_image_region=15000, _brightness=None):
         """Candidate 5-tuples (cbpm:261-443): per region keep at most k stars (k = 15, 14, ...)
-        until the union of all C(region, 5) has between 1 and the maximum number of tuples."""
-        vals = self.star_brightnesses(keypoints, workscale_img)
+        until the union of all C(region, 5) has between 1 and the maximum number of tuples.
+        `_brightness` (not in the reference) supplies get_star_brightness values already known,
+        as the synthetic C4 workload does."""
+        vals = self.star_brightnesses(keypoints, workscale_img) if _brightness is None else _brightness
         brightness = {i: float(vals[i]) for i in range(len(keypoints))}
         regions = self._regions(keypoints, workscale_img.shape[1], workscale_img.shape[0])
         polygons = []

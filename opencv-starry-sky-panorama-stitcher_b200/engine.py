@@ -256,6 +256,15 @@ class Engine:
                                                   ctypes.byref(n_valid)))
         return (n_valid.value, status) if return_status else n_valid.value
 
+    def polygon_measure_resident(self, image: int, device_ptr: int, n_candidates: int,
+                                 min_side_px: float = 5.0) -> int:
+        """Same as `polygon_measure` for an int32 (n, 5) candidate table already on this device."""
+        n_valid = ctypes.c_int64()
+        self._check(self._lib.ssp_polygon_measure(self._ctx, int(image), ctypes.c_void_p(device_ptr),
+                                                  int(n_candidates), float(min_side_px), N.MEM_DEVICE,
+                                                  None, ctypes.byref(n_valid)))
+        return n_valid.value
+
     def polygon_count(self, image: int) -> int:
         n = ctypes.c_int64()
         self._check(self._lib.ssp_polygon_count(self._ctx, int(image), ctypes.byref(n)))
@@ -285,7 +294,8 @@ class Engine:
 
     # -- kernel 3 -------------------------------------------------------------------------
     def polygon_match_pairs(self, pairs, threshold: float = 0.1566, min_over_shifts: bool = False,
-                            fp32: bool = False, return_rowmin: bool = False) -> PolygonMatchResult:
+                            fp32: bool = False, return_rowmin: bool = False,
+                            fetch: bool = True) -> PolygonMatchResult:
         """Per polygon of the first image the nearest polygon of the second (cbpm:992-1067), kept
         iff distance < threshold (cbpm:1145-1148).  Defaults are the reference's parity mode."""
         p = _as_pairs(pairs)
@@ -298,8 +308,9 @@ class Engine:
         m1 = np.empty(n, dtype=np.int32)
         m2 = np.empty(n, dtype=np.int32)
         md = np.empty(n, dtype=np.float64)
-        self._check(self._lib.ssp_polygon_fetch_matches(self._ctx, _ptr(m1), _ptr(m2), _ptr(md), n,
-                                                        N.MEM_HOST))
+        if fetch:
+            self._check(self._lib.ssp_polygon_fetch_matches(self._ctx, _ptr(m1), _ptr(m2), _ptr(md), n,
+                                                            N.MEM_HOST))
         res = PolygonMatchResult(offs, m1, m2, md)
         if return_rowmin:
             rows = np.array([self.polygon_count(int(a)) for a in p[:, 0]], dtype=np.int64)

@@ -65,6 +65,68 @@ __global__ void __launch_bounds__(1024) bench(uint32_t seed, unsigned long long*
   if (threadIdx.x == 0) cycles[blockIdx.x] = (unsigned long long)(t1 - t0);
 }
 
+// Floating-point pipes that bound kernel 3: DFMA, the unfused DMUL+DADD pair the parity mode
+// issues (numpy rounds the square and the sum separately), and FFMA for the fp32 mode.
+template <int OP>
+__global__ void __launch_bounds__(1024) benchf(double seed, unsigned long long* cycles, double* sink) {
+  double v[CHAINS], w[CHAINS];
+  float fv[CHAINS], fw[CHAINS];
+#pragma unroll
+  for (int i = 0; i < CHAINS; ++i) {
+    v[i] = seed * (threadIdx.x + 1) + i * 0.37;
+    w[i] = v[i] * 0.99991;
+    fv[i] = (float)v[i];
+    fw[i] = (float)w[i];
+  }
+  __syncthreads();
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+    for (int i = 0; i < CHAINS; ++i) {
+      if (OP == 0) {
+        asm volatile("fma.rn.f64 %0, %1, %2, %3;" : "=d"(v[i]) : "d"(v[i]), "d"(w[i]), "d"(seed));
+      } else if (OP == 1) {
+        double d;
+        asm volatile("sub.rn.f64 %0, %1, %2;" : "=d"(d) : "d"(v[i]), "d"(w[i]));
+        asm volatile("mul.rn.f64 %0, %1, %1;" : "=d"(d) : "d"(d));
+        asm volatile("add.rn.f64 %0, %1, %2;" : "=d"(v[i]) : "d"(v[i]), "d"(d));
+      } else {
+        asm volatile("fma.rn.f32 %0, %1, %2, %3;" : "=f"(fv[i]) : "f"(fv[i]), "f"(fw[i]), "f"((float)seed));
+      }
+    }
+  }
+  const long long t1 = clock64();
+  double acc = 0;
+#pragma unroll
+  for (int i = 0; i < CHAINS; ++i) acc += v[i] + w[i] + fv[i] + fw[i];
+  if (acc == 0.123456789) sink[0] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) cycles[blockIdx.x] = (unsigned long long)(t1 - t0);
+}
+
+template <int OP>
+double runf(int sms, int ops_per_chain_step, const char* name) {
+  unsigned long long* d_cycles;
+  double* d_sink;
+  cudaMalloc(&d_cycles, sms * sizeof(unsigned long long));
+  cudaMalloc(&d_sink, 8);
+  benchf<OP><<<sms, 1024>>>(1.000001, d_cycles, d_sink);
+  benchf<OP><<<sms, 1024>>>(1.000001, d_cycles, d_sink);
+  cudaDeviceSynchronize();
+  unsigned long long* h = new unsigned long long[sms];
+  cudaMemcpy(h, d_cycles, sms * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+  double mean = 0;
+  for (int i = 0; i < sms; ++i) mean += (double)h[i];
+  mean /= sms;
+  const double rate = 1024.0 * ITERS * CHAINS * ops_per_chain_step / mean;
+  printf("  \"%s\": %.2f,\n", name, rate);
+  delete[] h;
+  cudaFree(d_cycles);
+  cudaFree(d_sink);
+  return rate;
+}
+
 template <int OP>
 double run(int sms, int ops_per_chain_step, const char* name) {
   unsigned long long* d_cycles;
@@ -106,6 +168,9 @@ int main() {
   run<3>(s, 2, "vimnmx");
   run<4>(s, 3, "mix_1popc_2lop3_total");
   run<5>(s, 7, "mix_kernel1_csa_total");
+  runf<0>(s, 1, "dfma");
+  runf<1>(s, 3, "dsub_dmul_dadd_total");
+  runf<2>(s, 1, "ffma");
   printf("  \"note\": \"mix_* count every instruction of the mix\"\n}\n");
   return 0;
 }
