@@ -232,7 +232,7 @@ def measured_hbm_peak():
 def run_ours(args, wl, sets, pairs):
     import torch
     import ssp_b200
-    from ssp_b200.distributed import shard_pairs, broadcast_descriptor_bank, gather_matches
+    from ssp_b200.distributed import shard_pairs, broadcast_descriptor_bank, gather_matches_resident
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -309,10 +309,11 @@ def run_ours(args, wl, sets, pairs):
         if world > 1:
             b_t, o_all = broadcast_descriptor_bank(bank, offs, 0)       # H2D on rank 0 + NCCL broadcast
             eng.bind_descriptor_bank(b_t.data_ptr(), o_all, keepalive=b_t)
-            local = eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant)  # D2H of survivors
-            return gather_matches(local, local_pos, len(pairs), dst=0)   # NCCL gather + D2H on rank 0
+            local = eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant, fetch=False)
+            # survivors: device -> NCCL gather -> global pair order -> pinned host memory of rank 0
+            return gather_matches_resident(eng, local.offsets, local_pos, len(pairs), dst=0)
         eng.upload_descriptor_bank(bank, offs)                           # pinned host -> device
-        return eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant)
+        return eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant, pinned=True)  # D2H of survivors
 
     e2e_steps = max(1, min(args.steps, 3))
     step_e2e()
@@ -649,7 +650,25 @@ def run_polygon_ours(args, wl, inp, pairs):
     return line
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else a library prints
+    there (NCCL's version banner at N > 1) was re-routed to stderr in main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     args = parse()
     wl = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
@@ -660,21 +679,21 @@ def main():
         inp = polygon_inputs(wl)
         pairs = synth.all_pairs(wl["n_images"])
         if args.impl == "reference":
-            print(json.dumps(run_polygon_reference(args, wl, inp, pairs)), flush=True)
+            emit(run_polygon_reference(args, wl, inp, pairs))
             return 0
         line = run_polygon_ours(args, wl, inp, pairs)
         if rank == 0:
             if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not args.no_cpu_baseline:
                 ref_args = argparse.Namespace(**{**vars(args), "steps": 2, "warmup": 0})
                 line["cpu_baseline"] = run_polygon_reference(ref_args, wl, inp, pairs)["cpu_baseline"]
-            print(json.dumps(line), flush=True)
+            emit(line)
         return 0
     # every rank generates the same seeded input (cheap next to shipping it); rank 0's copy is
     # the "host input" of the e2e leg
     sets = synth.descriptor_bank(wl["n_images"], wl["n_desc"], seed=wl["seed"])
     pairs = synth.all_pairs(wl["n_images"])
     if args.impl == "reference":
-        print(json.dumps(run_reference(args, wl, sets, pairs)), flush=True)
+        emit(run_reference(args, wl, sets, pairs))
         return 0
     line = run_ours(args, wl, sets, pairs)
     if rank == 0:
@@ -685,7 +704,7 @@ def main():
                 "gcmp_per_s": cpu["gcmp_per_s"],
                 "sample": f"cv2 {cpu['cv2']} BFMatcher ({args.mode}) on {cpu['pairs']} of {len(pairs)} pairs "
                           f"({cpu['seconds']:.1f} s), {cpu['cores']} threads; the reference's own CPU call"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     return 0
 
 

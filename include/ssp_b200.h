@@ -83,6 +83,13 @@ int ssp_set_stream(ssp_ctx* ctx, void* cuda_stream);
 int ssp_synchronize(ssp_ctx* ctx);
 /* Device facts used by the roofline report: SM count and SM clock in kHz (max). */
 int ssp_device_info(ssp_ctx* ctx, int* sm_count, int* sm_clock_khz, int64_t* hbm_bytes);
+/* Page-locked host memory for caller-allocated input / output buffers (descriptor banks going
+ * in, survivor arrays coming out): copies to and from it run at full PCIe / C2C rate and truly
+ * asynchronously, where pageable numpy memory is staged by the driver.  The reference has no
+ * counterpart (its arrays never leave the host); optional, any host pointer is accepted by the
+ * MEM_HOST paths.  Free with ssp_host_free. */
+int ssp_host_alloc(ssp_ctx* ctx, int64_t bytes, void** host_ptr);
+int ssp_host_free(ssp_ctx* ctx, void* host_ptr);
 
 /* ---- descriptor bank ------------------------------------------------------------------
  * Replaces the per-pair `ft.descriptors.get()[0:n_orb, :]` host slices handed to

@@ -38,6 +38,8 @@ PROTOTYPES = {
     "ssp_synchronize": (_c.c_int, [_ctx_p]),
     "ssp_device_info": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_int),
                                    _c.POINTER(_c.c_int64)]),
+    "ssp_host_alloc": (_c.c_int, [_ctx_p, _c.c_int64, _c.POINTER(_c.c_void_p)]),
+    "ssp_host_free": (_c.c_int, [_ctx_p, _vp]),
     "ssp_upload_descriptor_bank": (_c.c_int, [_ctx_p, _u8p, _i64p, _c.c_int, _c.c_int]),
     "ssp_bind_descriptor_bank": (_c.c_int, [_ctx_p, _u8p, _i64p, _c.c_int]),
     "ssp_hamming_match_pairs": (_c.c_int, [_ctx_p, _i32p, _c.c_int, _c.c_int, _c.c_int, _c.c_int,

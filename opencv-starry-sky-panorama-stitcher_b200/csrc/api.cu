@@ -115,6 +115,23 @@ int ssp_synchronize(ssp_ctx* ctx) {
   return SSP_OK;
 }
 
+int ssp_host_alloc(ssp_ctx* ctx, int64_t bytes, void** host_ptr) {
+  if (!ctx) return SSP_ERR_INVALID;
+  SSP_REQUIRE(ctx, host_ptr != nullptr && bytes >= 0, SSP_ERR_INVALID, "ssp_host_alloc: bad arguments");
+  if (int rc = ssp::use_device(ctx)) return rc;
+  *host_ptr = nullptr;
+  SSP_CUDA_TRY(ctx, cudaHostAlloc(host_ptr, (size_t)(bytes > 0 ? bytes : 1), cudaHostAllocPortable));
+  return SSP_OK;
+}
+
+int ssp_host_free(ssp_ctx* ctx, void* host_ptr) {
+  if (!ctx) return SSP_ERR_INVALID;
+  if (!host_ptr) return SSP_OK;
+  if (int rc = ssp::use_device(ctx)) return rc;
+  SSP_CUDA_TRY(ctx, cudaFreeHost(host_ptr));
+  return SSP_OK;
+}
+
 int ssp_device_info(ssp_ctx* ctx, int* sm_count, int* sm_clock_khz, int64_t* hbm_bytes) {
   if (!ctx) return SSP_ERR_INVALID;
   if (sm_count) *sm_count = ctx->sm_count;

@@ -98,6 +98,62 @@ def gather_matches(local: HammingResult, local_positions: Sequence[int], n_pairs
     return HammingResult(offsets, q, t, d)
 
 
+_PINNED = {}
+
+
+def _pinned_i32(tag: str, n: int) -> torch.Tensor:
+    """Grow-only pinned staging buffer (cudaHostAlloc per step would cost more than the copy)."""
+    buf = _PINNED.get(tag)
+    if buf is None or buf.numel() < n:
+        buf = torch.empty(max(n, 1), dtype=torch.int32)
+        if torch.cuda.is_available():
+            buf = buf.pin_memory()
+        _PINNED[tag] = buf
+    return buf[:n]
+
+
+def gather_matches_resident(engine, local_offsets: np.ndarray, local_positions: Sequence[int],
+                            n_pairs: int, dst: int = 0):
+    """`gather_matches` without the host round trip (NCCL backend): the rank's survivors of the
+    last `hamming_match_pairs(..., fetch=False)` go device -> NCCL gather -> one permutation on
+    rank `dst`'s GPU (round-robin shards back into global pair order) -> one copy into pinned
+    host memory.  Returns a HammingResult on `dst`, None elsewhere; its arrays are views of a
+    reused staging buffer, valid until the next call."""
+    dev = _device_for_backend()
+    rank, world = dist.get_rank(), dist.get_world_size()
+    counts = torch.zeros(n_pairs, dtype=torch.int64, device=dev)
+    if len(local_positions):
+        counts[rank::world] = torch.from_numpy(np.diff(local_offsets).astype(np.int64)).to(dev)
+    dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+    per_rank = torch.stack([counts[r::world].sum() for r in range(world)])
+    width = max(int(per_rank.max().item()), 1)
+    payload = torch.empty((3, width), dtype=torch.int32, device=dev)
+    n_local = int(local_offsets[-1])
+    if n_local:
+        engine.hamming_fetch_into(payload[0].data_ptr(), payload[1].data_ptr(), payload[2].data_ptr(),
+                                  width, device=True)
+    bufs = [torch.empty_like(payload) for _ in range(world)] if rank == dst else None
+    dist.gather(payload, bufs, dst=dst)
+    if rank != dst:
+        return None
+    offsets = torch.zeros(n_pairs + 1, dtype=torch.int64, device=dev)
+    torch.cumsum(counts, 0, out=offsets[1:])
+    total = int(offsets[-1].item())
+    # where pair p's block starts inside the concatenated per-rank payloads
+    base = torch.empty(n_pairs, dtype=torch.int64, device=dev)
+    for r in range(world):
+        c = counts[r::world]
+        base[r::world] = r * width + torch.cumsum(c, 0) - c
+    src = torch.repeat_interleave(base - offsets[:-1], counts, output_size=total) + \
+        torch.arange(total, dtype=torch.int64, device=dev)
+    flat = torch.cat(bufs, dim=1)                       # (3, world * width)
+    ordered = flat.index_select(1, src)                 # (3, total) in global pair order
+    host = _pinned_i32("gather", 3 * total).view(3, total)
+    host.copy_(ordered, non_blocking=False)
+    h = host.numpy()
+    return HammingResult(offsets.cpu().numpy(), h[0], h[1], h[2])
+
+
 def match_pairs_sharded(match_fn: Callable, bank: Optional[np.ndarray], offsets: Optional[np.ndarray],
                         pairs: Sequence, bind_fn: Optional[Callable] = None, src: int = 0):
     """End-to-end sharded run: broadcast bank -> every rank matches pairs[rank::world] -> gather.

@@ -91,12 +91,16 @@ class Engine:
         self._desc_offsets = None
         self._star_offsets = None
         self._bound = None  # keeps a bound torch tensor alive
+        self._pinned = {}   # tag -> (address, bytes): engine-owned page-locked result buffers
         if stream is not None:
             self.set_stream(stream)
 
     # -- lifetime -------------------------------------------------------------------------
     def close(self):
         if getattr(self, "_ctx", None):
+            for addr, _ in getattr(self, "_pinned", {}).values():
+                self._lib.ssp_host_free(self._ctx, ctypes.c_void_p(addr))
+            self._pinned = {}
             self._lib.ssp_destroy(self._ctx)
             self._ctx = None
 
@@ -120,6 +124,24 @@ class Engine:
             # the reference's math.acos raises ValueError("math domain error") (cbpm:134)
             raise ValueError(f"math domain error: {msg}")
         raise EngineError(f"libssp_b200 error {rc}: {msg}")
+
+    def pinned_array(self, tag: str, n: int, dtype) -> np.ndarray:
+        """numpy view of `n` items of an engine-owned page-locked buffer (grow-only, one per
+        `tag`); the view is valid until the next request for the same tag or `close()`."""
+        dt = np.dtype(dtype)
+        need = max(int(n) * dt.itemsize, 1)
+        addr, size = self._pinned.get(tag, (0, 0))
+        if size < need:
+            if addr:
+                self._check(self._lib.ssp_host_free(self._ctx, ctypes.c_void_p(addr)))
+                self._pinned.pop(tag)
+            p = ctypes.c_void_p()
+            size = need + need // 4
+            self._check(self._lib.ssp_host_alloc(self._ctx, size, ctypes.byref(p)))
+            addr = p.value
+            self._pinned[tag] = (addr, size)
+        raw = (ctypes.c_char * need).from_address(addr)
+        return np.frombuffer(raw, dtype=dt, count=int(n))
 
     def set_stream(self, cuda_stream_handle: Optional[int]):
         """Run subsequent work on this cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
@@ -177,13 +199,15 @@ class Engine:
 
     # -- kernel 1 -------------------------------------------------------------------------
     def hamming_match_pairs(self, pairs, mode="crosscheck", ratio=0.75, variant="auto",
-                            return_best2=False, fetch=True) -> HammingResult:
+                            return_best2=False, fetch=True, pinned=False) -> HammingResult:
         """All-pairs Hamming matching of image pairs (query image, train image).
 
         mode="crosscheck"  == cv.BFMatcher(cv.NORM_HAMMING, crossCheck=True).match per pair
                               (custom_bruteforce_matcher.py:193-199)
         mode="knn2_ratio"  == knnMatch(k=2) + `m.distance < ratio * n.distance`
                               (custom_bruteforce_matcher.py:160-172)
+        pinned=True returns views of engine-owned page-locked buffers (valid until the next
+        call) instead of fresh numpy arrays: the device -> host copy then runs at link rate.
         """
         if self._desc_offsets is None:
             raise EngineError("no descriptor bank uploaded")
@@ -193,9 +217,12 @@ class Engine:
         self._check(self._lib.ssp_hamming_match_pairs(
             self._ctx, _ptr(p), p.shape[0], _MODES[mode], num, den, _VARIANTS[variant], _ptr(offs)))
         n = int(offs[-1])
-        q = np.empty(n, dtype=np.int32)
-        t = np.empty(n, dtype=np.int32)
-        d = np.empty(n, dtype=np.int32)
+        if pinned and fetch:
+            q, t, d = (self.pinned_array(k, n, np.int32) for k in ("hq", "ht", "hd"))
+        else:
+            q = np.empty(n, dtype=np.int32)
+            t = np.empty(n, dtype=np.int32)
+            d = np.empty(n, dtype=np.int32)
         if fetch:
             self._check(self._lib.ssp_hamming_fetch_matches(self._ctx, _ptr(q), _ptr(t), _ptr(d), n,
                                                             N.MEM_HOST))
@@ -209,6 +236,13 @@ class Engine:
             self._check(self._lib.ssp_hamming_fetch_best2(self._ctx, _ptr(b2), b2.shape[0], N.MEM_HOST))
             res.best2, res.best2_offsets = b2, b_off
         return res
+
+    def hamming_fetch_into(self, q_ptr: int, t_ptr: int, d_ptr: int, capacity: int, device: bool = True):
+        """Copies the survivors of the last `hamming_match_pairs(..., fetch=False)` into three
+        int32 buffers given by address (device memory, or pinned / pageable host memory)."""
+        self._check(self._lib.ssp_hamming_fetch_matches(
+            self._ctx, ctypes.c_void_p(q_ptr), ctypes.c_void_p(t_ptr), ctypes.c_void_p(d_ptr),
+            int(capacity), N.MEM_DEVICE if device else N.MEM_HOST))
 
     def hamming_last_stats(self):
         n, ms, cmp_ = ctypes.c_int(), ctypes.c_float(), ctypes.c_int64()

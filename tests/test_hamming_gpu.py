@@ -138,3 +138,25 @@ def test_errors_are_loud(engine):
     with pytest.raises(ssp_b200.EngineError, match="no descriptor bank"):
         fresh.hamming_match_pairs([(0, 0)])
     fresh.close()
+
+
+def test_pinned_results_and_fetch_into_equal_plain_fetch(engine):
+    """The page-locked result views (ssp_host_alloc) and the fetch-by-address path used by the
+    multi-GPU gather return exactly what the plain numpy fetch returns, also after the buffers
+    were reused for a smaller and then a larger result."""
+    sets = synth.descriptor_bank(4, 900, seed=11, world=1200)
+    engine.upload_descriptor_bank(sets)
+    for pairs in ([(0, 1), (1, 2), (2, 3)], [(0, 2)], synth.all_pairs(4)):
+        plain = engine.hamming_match_pairs(pairs, mode="knn2_ratio")
+        pinned = engine.hamming_match_pairs(pairs, mode="knn2_ratio", pinned=True)
+        np.testing.assert_array_equal(plain.offsets, pinned.offsets)
+        for a, b in zip((plain.query_idx, plain.train_idx, plain.distance),
+                        (pinned.query_idx, pinned.train_idx, pinned.distance)):
+            np.testing.assert_array_equal(a, b)
+        lazy = engine.hamming_match_pairs(pairs, mode="knn2_ratio", fetch=False)
+        n = int(lazy.offsets[-1])
+        bufs = [engine.pinned_array(f"test{k}", n, np.int32) for k in range(3)]
+        engine.hamming_fetch_into(*(b.ctypes.data for b in bufs), n, device=False)
+        for a, b in zip((plain.query_idx, plain.train_idx, plain.distance), bufs):
+            np.testing.assert_array_equal(a, b)
+    assert plain.offsets[-1] > 0
