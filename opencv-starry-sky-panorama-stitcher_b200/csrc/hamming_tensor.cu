@@ -69,12 +69,12 @@ constexpr int TC_ROW_BYTES = 256;            // expanded row
 constexpr int TC_A_BYTES = TC_M * TC_ROW_BYTES;      // 32 KB
 constexpr int TC_B_BYTES = TC_N * TC_ROW_BYTES;      // 64 KB
 constexpr int TC_EPI_THREADS = 256;
-constexpr int TC_THREADS = TC_EPI_THREADS + 64;
+constexpr int TC_THREADS = TC_EPI_THREADS + 64 + (TC_PROFILE ? 32 : 0);  // profile builds add an observer warp
 constexpr int TC_PAD = 256;                  // rows of every expanded image are padded to this
 constexpr uint32_t TC_KEY_SHIFT = 22;
 constexpr uint32_t TC_KEY_IDX_MASK = (1u << TC_KEY_SHIFT) - 1u;
 constexpr uint32_t TC_KEY_NONE = 0xFFFFFFFFu;
-constexpr int TC_D_MASKED = -30000;          // stands for "no such column"
+[[maybe_unused]] constexpr int TC_D_MASKED = -30000;          // stands for "no such column"
 constexpr int TC_THR_NONE = -100000;         // "no k-th neighbour yet"
 // bytes after the operand stages: mbarriers + TMEM slot (256), best-2 merge slots, thresholds
 constexpr int TC_TAIL_BYTES = 256 + 2 * TC_M * (int)sizeof(uint2) + 2 * TC_M * (int)sizeof(uint16_t);
@@ -323,6 +323,99 @@ __device__ __forceinline__ void tc_release(uint64_t* acc_empty, int lane) {
   __syncwarp();
   if (lane == 0) mbar_arrive(acc_empty);
 }
+#ifndef TC_REGPASS2
+#define TC_REGPASS2 1     // 1: pass 2 works on the packed registers of pass 1 (no TMEM re-read)
+#endif
+
+// Pass 2 on the registers pass 1 already holds: exact top-2 of one flagged 8-column chunk given as
+// four packed s16x2 registers q[m] = (D of column 2m, D of column 2m + 1).  The tournament runs on
+// PACKED keys D * 8 + (7 - j), which fit s16 for D in [-4096, 4095]: the low halves rank the even
+// columns, the high halves the odd ones, and the two half-tournaments meet at the end.
+template <int K, bool MASKED>
+__device__ __forceinline__ void tc_chunk_exact_packed(uint32_t q0, uint32_t q1, uint32_t q2, uint32_t q3,
+                                                      uint32_t col0, uint32_t nt, TcRow& r) {
+  if (MASKED) {   // pad columns (all-zero train rows, D = 0) must lose against every real column
+    constexpr uint32_t LOW = 0xF060u;  // D = -4000
+    q0 = (col0 + 0 < nt ? (q0 & 0xFFFFu) : LOW) | (col0 + 1 < nt ? (q0 & 0xFFFF0000u) : (LOW << 16));
+    q1 = (col0 + 2 < nt ? (q1 & 0xFFFFu) : LOW) | (col0 + 3 < nt ? (q1 & 0xFFFF0000u) : (LOW << 16));
+    q2 = (col0 + 4 < nt ? (q2 & 0xFFFFu) : LOW) | (col0 + 5 < nt ? (q2 & 0xFFFF0000u) : (LOW << 16));
+    q3 = (col0 + 6 < nt ? (q3 & 0xFFFFu) : LOW) | (col0 + 7 < nt ? (q3 & 0xFFFF0000u) : (LOW << 16));
+  }
+  // (q & 0x1FFF1FFF) * 8 cannot carry between the halves; the constant adds 7 - j
+  const uint32_t k0 = (q0 & 0x1FFF1FFFu) * 8u + 0x00060007u;
+  const uint32_t k1 = (q1 & 0x1FFF1FFFu) * 8u + 0x00040005u;
+  const uint32_t k2 = (q2 & 0x1FFF1FFFu) * 8u + 0x00020003u;
+  const uint32_t k3 = (q3 & 0x1FFF1FFFu) * 8u + 0x00000001u;
+  const uint32_t a = __vmaxs2(k0, k1), c = __vmaxs2(k2, k3);
+  const uint32_t t1 = __vmaxs2(a, c);
+  const int t1l = (int)(short)(t1 & 0xFFFFu), t1h = (int)t1 >> 16;
+  const int hi = max(t1l, t1h);
+  const uint32_t j1 = 7u - ((uint32_t)hi & 7u);
+  uint32_t g1 = ((uint32_t)(r.pq - (hi >> 3)) << TC_KEY_SHIFT) + (col0 + j1);
+  if (MASKED) g1 = (col0 + j1 < nt) ? g1 : TC_KEY_NONE;
+  if (K == 2) {
+    const uint32_t b = __vmins2(k0, k1), d = __vmins2(k2, k3);
+    const uint32_t s2 = __vimax3_s16x2(__vmins2(a, c), b, d);
+    const int s2l = (int)(short)(s2 & 0xFFFFu), s2h = (int)s2 >> 16;
+    const int lo = __vimax3_s32(min(t1l, t1h), s2l, s2h);
+    const uint32_t j2 = 7u - ((uint32_t)lo & 7u);
+    uint32_t g2 = ((uint32_t)(r.pq - (lo >> 3)) << TC_KEY_SHIFT) + (col0 + j2);
+    if (MASKED) g2 = (col0 + j2 < nt) ? g2 : TC_KEY_NONE;
+    r.m2 = min(min(r.m2, g2), max(r.m1, g1));   // g1 <= g2 and m1 <= m2
+  }
+  r.m1 = min(r.m1, g1);
+  const uint32_t kth = (K == 2) ? r.m2 : r.m1;
+  if (kth != TC_KEY_NONE) {
+    const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
+    *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
+    r.thr = max(r.thr, d_own);
+  }
+}
+
+// Pass 2 for a tile in which MANY chunks are flagged (the first tiles of every work item, while
+// the thresholds are still settling): one branch-free tournament over all 128 columns instead of
+// a chain of per-chunk ones.  Packed key of register i = D * 64 + (63 - i) -- 10 bits of D and 6
+// bits of position fill an s16 exactly -- so the low halves rank the 64 even columns, the high
+// halves the 64 odd ones; 2 * key + 1 (even) / 2 * key (odd) = D * 128 + (127 - column) puts both
+// on one scale at the end.  ~310 instructions with full instruction-level parallelism, against
+// ~350 cycles of dependent latency per chunk on the chunk path.
+#ifndef TC_FULL_MIN
+#define TC_FULL_MIN 3     // flagged chunks (of 16) from which the full-tile tournament is used
+#endif
+template <int K>
+__device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_t col_base, TcRow& r) {
+  uint32_t h[32], l[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    const uint32_t k0 = (p[2 * i] & 0x03FF03FFu) * 64u + (uint32_t)(63 - 2 * i) * 0x10001u;
+    const uint32_t k1 = (p[2 * i + 1] & 0x03FF03FFu) * 64u + (uint32_t)(62 - 2 * i) * 0x10001u;
+    h[i] = __vmaxs2(k0, k1);
+    if (K == 2) l[i] = __vmins2(k0, k1);
+  }
+#pragma unroll
+  for (int n = 16; n >= 1; n >>= 1) {
+#pragma unroll
+    for (int i = 0; i < n; ++i) {
+      if (K == 2) l[i] = __vimax3_s16x2(__vmins2(h[2 * i], h[2 * i + 1]), l[2 * i], l[2 * i + 1]);
+      h[i] = __vmaxs2(h[2 * i], h[2 * i + 1]);
+    }
+  }
+  const int a = 2 * (int)(short)(h[0] & 0xFFFFu) + 1, b = 2 * ((int)h[0] >> 16);
+  const int hi = max(a, b);
+  const uint32_t g1 = ((uint32_t)(r.pq - (hi >> 7)) << TC_KEY_SHIFT) + col_base + (127u - ((uint32_t)hi & 127u));
+  if (K == 2) {
+    const int c = 2 * (int)(short)(l[0] & 0xFFFFu) + 1, d = 2 * ((int)l[0] >> 16);
+    const int lo = __vimax3_s32(min(a, b), c, d);
+    const uint32_t g2 = ((uint32_t)(r.pq - (lo >> 7)) << TC_KEY_SHIFT) + col_base + (127u - ((uint32_t)lo & 127u));
+    r.m2 = min(min(r.m2, g2), max(r.m1, g1));   // g1 <= g2 and m1 <= m2
+  }
+  r.m1 = min(r.m1, g1);
+  const uint32_t kth = (K == 2) ? r.m2 : r.m1;   // never NONE here: the tile had 128 real columns
+  const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
+  *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
+  r.thr = max(r.thr, d_own);
+}
+
 template <int K, bool MASKED>
 __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint32_t nt, TcRow& r,
                                         uint64_t* acc_empty, int lane) {
@@ -330,6 +423,44 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
   tc_release(acc_empty, lane);
   return;
 #endif
+#if TC_REGPASS2
+  // The accumulator goes back to the MMA issuer as soon as its 128 columns sit in registers (held
+  // for one TMEM load); both passes then run on the registers while the tensor pipe already
+  // fills the buffer again.
+  const uint32_t thrp = (uint32_t)(max(r.thr, -32768) & 0xFFFF) * 0x10001u;
+  uint32_t p[TC_HALF / 2];
+  tc_ld128_packed(taddr, p);
+  tc_wait_ld(p);
+  tc_release(acc_empty, lane);
+  uint32_t flags = 0;
+#pragma unroll
+  for (int c = 0; c < TC_HALF / TC_CHUNK; ++c) flags |= tc_beats(p + 4 * c, thrp) ? (1u << c) : 0u;
+#if TC_EXPERIMENT == 2 || TC_EXPERIMENT == 3
+  if (flags == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
+  return;
+#endif
+  flags = __reduce_or_sync(0xffffffffu, flags);
+  TC_PROF(r.p_nflag += __popc(flags);)
+  TC_PROF(const long long c_p1 = clock64();)
+  if (!MASKED && __popc(flags) >= TC_FULL_MIN) {
+    tc_tile_full<K>(p, col_base, r);
+    TC_PROF(r.p_pass2 += clock64() - c_p1;)
+    return;
+  }
+  while (flags) {   // warp-uniform: `flags` is the same in every lane
+    const uint32_t c = tc_pop(flags);
+    uint32_t q0, q1, q2, q3;
+    switch (c) {    // warp-uniform jump: register arrays cannot be indexed dynamically
+#define TC_CASE(i) case i: q0 = p[4 * i]; q1 = p[4 * i + 1]; q2 = p[4 * i + 2]; q3 = p[4 * i + 3]; break;
+      TC_CASE(0) TC_CASE(1) TC_CASE(2) TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6) TC_CASE(7)
+      TC_CASE(8) TC_CASE(9) TC_CASE(10) TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14)
+      default: q0 = p[60]; q1 = p[61]; q2 = p[62]; q3 = p[63]; break;
+#undef TC_CASE
+    }
+    tc_chunk_exact_packed<K, MASKED>(q0, q1, q2, q3, col_base + c * TC_CHUNK, nt, r);
+  }
+  TC_PROF(r.p_pass2 += clock64() - c_p1;)
+#else
   const uint32_t thrp = (uint32_t)(max(r.thr, -32768) & 0xFFFF) * 0x10001u;
   uint32_t flags = 0;
   {
@@ -367,6 +498,7 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
     if (n > 3) tc_chunk_exact<K, MASKED>(v3, col_base + c3 * TC_CHUNK, nt, r);
   } while (flags);
   TC_PROF(r.p_pass2 += clock64() - c_p1;)
+#endif
 }
 
 // finds the work item that owns query tile `tile` (tile_begin is ascending; n_work >= 1)
@@ -560,6 +692,34 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
       TC_PROF(if (blockIdx.x == 0) printf("mma thread: total %lld  wait a_full %lld  b_full %lld  acc_empty %lld  stages %u\n",
                                           clock64() - p_t0, p_a, p_b, p_acc, g);)
     }
+#if TC_PROFILE
+  } else if (warp == 10) {
+    // ===== observer (profile builds): when does each accumulator complete, by position of the
+    // train tile inside its work item?  hist[t] = sum over items of (F_t - F_{t-1}).
+    if (lane == 0 && blockIdx.x == 0) {
+      long long hist[24];
+      int cnt[24];
+      for (int i = 0; i < 24; ++i) { hist[i] = 0; cnt[i] = 0; }
+      uint32_t g = 0;
+      long long prev = clock64();
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TcWork w = work[tc_find_work(work, n_work, tile)];
+        const int n_t = (w.nt + TC_N - 1) / TC_N;
+        for (int t = 0; t < n_t; ++t, ++g) {
+          tc_wait(&acc_full[g % TC_ACC], (g / TC_ACC) & 1u);
+          const long long now = clock64();
+          // bins: t = 0..15 one each, then 16-31, 32-63, 64-127, 128+, and the LAST tile of the item
+          int b = t < 16 ? t : (t < 32 ? 16 : (t < 64 ? 17 : (t < 128 ? 18 : 19)));
+          if (t == n_t - 1 && t >= 16) b = 20;
+          hist[b] += now - prev;
+          cnt[b] += 1;
+          prev = now;
+        }
+      }
+      for (int i = 0; i < 21; ++i)
+        if (cnt[i]) printf("stage time bin %d: mean %lld clk over %d stages\n", i, hist[i] / cnt[i], cnt[i]);
+    }
+#endif
   } else {
     // ===== epilogue warpgroups =====
     uint32_t g = 0, item = 0;
