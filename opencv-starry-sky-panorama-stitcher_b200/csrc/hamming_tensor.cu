@@ -379,6 +379,18 @@ __device__ __forceinline__ void tc_chunk_exact_packed(uint32_t q0, uint32_t q1, 
 // halves the 64 odd ones; 2 * key + 1 (even) / 2 * key (odd) = D * 128 + (127 - column) puts both
 // on one scale at the end.  ~310 instructions with full instruction-level parallelism, against
 // ~350 cycles of dependent latency per chunk on the chunk path.
+// packed key ((D & 0x3FF) << 6 | pos) of both halves in two instructions, one per pipe: the shift
+// as IMAD on the FMA pipe, then ONE LOP3 (a & mask) | pos with the mask in a register and the
+// position as the immediate (left alone the compiler emits shift + two immediate LOP3s, and the
+// ALU pipe is what bounds the full-tile tournament)
+__device__ __forceinline__ uint32_t tc_key64(uint32_t p, uint32_t pos) {
+  uint32_t k;
+  uint32_t sh = p * 64u;
+  uint32_t mask = 0xFFC0FFC0u;
+  asm volatile("" : "+r"(mask));   // keep the mask in a register
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(sh), "r"(mask), "r"(pos));
+  return k;
+}
 #ifndef TC_FULL_MIN
 #define TC_FULL_MIN 3     // flagged chunks (of 16) from which the full-tile tournament is used
 #endif
@@ -387,8 +399,8 @@ __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_
   uint32_t h[32], l[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) {
-    const uint32_t k0 = (p[2 * i] & 0x03FF03FFu) * 64u + (uint32_t)(63 - 2 * i) * 0x10001u;
-    const uint32_t k1 = (p[2 * i + 1] & 0x03FF03FFu) * 64u + (uint32_t)(62 - 2 * i) * 0x10001u;
+    const uint32_t k0 = tc_key64(p[2 * i], (uint32_t)(63 - 2 * i) * 0x10001u);
+    const uint32_t k1 = tc_key64(p[2 * i + 1], (uint32_t)(62 - 2 * i) * 0x10001u);
     h[i] = __vmaxs2(k0, k1);
     if (K == 2) l[i] = __vmins2(k0, k1);
   }
