@@ -627,6 +627,8 @@ def run_polygon_ours(args, wl, inp, pairs):
         "flop_per_evaluation": FLOP_PER_EVALUATION, "kernel_ms_per_launch": main_ms,
         "evaluations_per_launch": evals_local, "traffic": None,
     }
+    if not measured and not args.fp32 and world == 1:   # the committed ncu capture is of exactly this launch
+        roofline["traffic"], roofline["traffic_source"] = ncu_traffic("poly_compare_f64_kernel")
     line = None
     if rank == 0:
         line = {
