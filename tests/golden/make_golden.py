@@ -13,6 +13,9 @@ Run in the build container only (needs /root/reference):   python tests/golden/m
   reference_matchesinfo_c1.npz   every MatchesInfo field the unchanged reference
                            CustomBruteForceMatcher.match_n_features() returns for the first 6
                            forest images (15 pairs).
+  eisenberg_c2.npz         BASELINE config 2 on the 4 eisenberg frames the reference ships: stars
+                           from the unchanged compute_star_features, DMatches and polygon banks
+                           of the unchanged BFPolygonMatcher.match for all 6 pairs.
   polygon_golden.npz       unchanged reference BFPolygonMatcher on two synthetic overlapping
                            star views: get_polygons_characteristics arrays, the stored normalised
                            polygon_data_store arrays and the final DMatches of match().
@@ -189,8 +192,53 @@ def make_polygon_golden():
           [len(store[f'v{i}_raw_idx']) for i in (0, 1)], "dmatches", len(dms))
 
 
+EISENBERG = "/root/reference/img_eisenberg_18h06m_ISO1600_10s"
+
+
+def make_eisenberg_c2():
+    """BASELINE config 2 on the real frames the reference ships (4 of the 21 eisenberg JPEGs):
+    the unchanged star finder (image_processors.compute_star_features, Canny + contours) and the
+    unchanged BFPolygonMatcher.match on all 6 pairs, with the polygon cache shared across pairs
+    exactly as custom_bruteforce_matcher.py:57-59 shares it."""
+    names = sorted(n for n in os.listdir(EISENBERG) if n.endswith(".jpg"))
+    tmp = tempfile.mkdtemp(prefix="ssp_golden_c2_")
+    store = {"names": np.array(names), "focal": np.array([1135.0]), "cv2_version": cv.__version__}
+    kps, imgs, scale = [], [], None
+    for i, name in enumerate(names):
+        full = cv.imread(os.path.join(EISENBERG, name))
+        if scale is None:
+            scale = min(1.0, np.sqrt(1.2 * 1e6 / (full.shape[0] * full.shape[1])))
+        img = cv.resize(src=full, dsize=None, fx=scale, fy=scale, interpolation=cv.INTER_AREA)
+        feats = ref_ip.compute_star_features(img, name, tmp, n_brightest_stars=1000)
+        imgs.append(img)
+        kps.append(tuple(feats.keypoints))
+        store[f"i{i}_xy"] = np.array([kp.pt for kp in kps[-1]], dtype=np.float32).reshape(-1, 2)
+        store[f"i{i}_size"] = np.array([kp.size for kp in kps[-1]], dtype=np.float32)
+        store[f"i{i}_gray"] = cv.cvtColor(img, cv.COLOR_BGR2GRAY)
+    store["img_shape"] = np.array(imgs[0].shape)
+    pstore, counter = {}, []
+    pair_list = [(a, b) for a in range(len(names)) for b in range(a + 1, len(names))]
+    store["pairs"] = np.array(pair_list, dtype=np.int32)
+    for p, (a, b) in enumerate(pair_list):
+        bf = ref_poly.BFPolygonMatcher(tmp, names[a], names[b], a, b, imgs[a].shape, 1135)
+        dms = bf.match(kps[a], kps[b], 0, 0, imgs[a], imgs[b], pstore, a, b, counter)
+        store[f"p{p}_dmatches"] = np.array([[m.queryIdx, m.trainIdx] for m in dms], dtype=np.int32).reshape(-1, 2)
+        store[f"p{p}_dist"] = np.array([m.distance for m in dms], dtype=np.float32)
+        print("c2 pair", (a, b), "dmatches", len(dms))
+    for i in range(len(names)):
+        q = pstore[i]["polygons_from_ftX"]
+        store[f"i{i}_candidates"] = np.array(list(pstore[i]["all_possible_polygons_ftX"]), dtype=np.int32).reshape(-1, 5)
+        store[f"i{i}_norm_idx"] = q["keypoint_indices_rotated_list"].astype(np.int32)
+        store[f"i{i}_norm_angle"] = q["keypoint_angles_rotated_list"]
+        store[f"i{i}_norm_side"] = q["side_lengths_rotated_list"]
+        store[f"i{i}_norm_bright"] = q["keypoint_brightnesses_rotated_list"]
+    np.savez_compressed(os.path.join(OUT, "eisenberg_c2.npz"), **store)
+    print("eisenberg_c2: stars", [len(k) for k in kps], "polygons",
+          [len(store[f"i{i}_norm_idx"]) for i in range(len(names))])
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["orb", "hamming", "matchesinfo", "polygon"]
+    which = sys.argv[1:] or ["orb", "hamming", "matchesinfo", "polygon", "c2"]
     names = feats = imgs = None
     if "orb" in which or "matchesinfo" in which:
         names, feats, imgs = make_orb_fixture()
@@ -200,3 +248,5 @@ if __name__ == "__main__":
         make_reference_matchesinfo(names, feats, imgs)
     if "polygon" in which:
         make_polygon_golden()
+    if "c2" in which:
+        make_eisenberg_c2()

@@ -88,3 +88,33 @@ def test_brightness_oracle_equals_reference_values(g):
     xy = g["v0_xy"]
     for k in (0, 7, 33, len(xy) - 1):
         assert star_brightness(gray, xy[k]) == int(g["v0_brightness"][k])
+
+
+# ---- BASELINE config 2: the real eisenberg frames through the unchanged reference ----------------
+
+def test_c2_oracle_reproduces_reference_on_real_star_frames(golden):
+    """Stars found by the unchanged compute_star_features on the 4 eisenberg JPEGs the reference
+    ships; polygon banks and DMatches of the unchanged BFPolygonMatcher for all 6 pairs."""
+    c2 = golden("eisenberg_c2.npz")
+    o = PolygonOracle(tuple(int(v) for v in c2["img_shape"]), float(c2["focal"][0]))
+    feats, idxs = [], []
+    for i in range(len(c2["names"])):
+        xy = c2[f"i{i}_xy"].astype(np.float64)
+        gray = c2[f"i{i}_gray"]
+        bright = np.array([star_brightness(gray, p) for p in xy], dtype=np.float64)
+        got = o.characteristics(xy, bright, c2[f"i{i}_candidates"])
+        np.testing.assert_array_equal(got["star_idx"], c2[f"i{i}_norm_idx"])
+        np.testing.assert_allclose(got["feat"][:, 0:5], c2[f"i{i}_norm_angle"], rtol=0, atol=1e-12)
+        np.testing.assert_allclose(got["feat"][:, 5:10], c2[f"i{i}_norm_side"], rtol=0, atol=1e-12)
+        np.testing.assert_array_equal(got["feat"][:, 10:15], c2[f"i{i}_norm_bright"])
+        feats.append(np.concatenate([c2[f"i{i}_norm_angle"], c2[f"i{i}_norm_side"], c2[f"i{i}_norm_bright"]], axis=1))
+        idxs.append(c2[f"i{i}_norm_idx"])
+    total = 0
+    for p, (a, b) in enumerate(c2["pairs"]):
+        rows, cols, d = PolygonOracle.select(PolygonOracle.compare(feats[a], feats[b]), 0.1566)
+        votes = PolygonOracle.vote(rows, cols, d, idxs[a], idxs[b])
+        np.testing.assert_array_equal(np.array([(x, y) for x, y, _ in votes], dtype=np.int32).reshape(-1, 2),
+                                      c2[f"p{p}_dmatches"])
+        np.testing.assert_array_equal(np.array([w for _, _, w in votes], dtype=np.float32), c2[f"p{p}_dist"])
+        total += len(votes)
+    assert total > 0

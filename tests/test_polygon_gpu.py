@@ -208,3 +208,35 @@ def test_full_match_reproduces_reference_dmatches(engine, g, tmp_path):
     np.testing.assert_allclose(np.array([m.distance for m in dms], dtype=np.float32), g["dmatch_dist"],
                                rtol=0, atol=1e-6)
     assert len(bf.last_polygon_matches[0]) == 150
+
+
+def test_c2_real_star_frames_all_pairs_reproduce_reference(engine, golden, tmp_path):
+    """BASELINE config 2: BFPolygonMatcher.match (brightness kernel -> host candidates -> kernel 2
+    -> kernel 3 -> voting) on the 4 eisenberg frames the reference ships, all 6 pairs with the
+    polygon cache shared across pairs; DMatches and polygon banks equal the unchanged reference's."""
+    c2 = golden("eisenberg_c2.npz")
+    n = len(c2["names"])
+    kps, imgs = [], []
+    for i in range(n):
+        kps.append(tuple(cv2.KeyPoint(float(p[0]), float(p[1]), float(s))
+                         for p, s in zip(c2[f"i{i}_xy"], c2[f"i{i}_size"])))
+        imgs.append(cv2.cvtColor(c2[f"i{i}_gray"], cv2.COLOR_GRAY2BGR))
+    store, counter = {}, []
+    total = 0
+    for p, (a, b) in enumerate(c2["pairs"]):
+        a, b = int(a), int(b)
+        bf = ssp_b200.BFPolygonMatcher(str(tmp_path), str(c2["names"][a]), str(c2["names"][b]), a, b,
+                                       imgs[a].shape, 1135, engine=engine, write_debug_images=False)
+        dms = bf.match(kps[a], kps[b], 0, 0, imgs[a], imgs[b], store, a, b, counter)
+        got = np.array([[m.queryIdx, m.trainIdx] for m in dms], dtype=np.int32).reshape(-1, 2)
+        np.testing.assert_array_equal(got, c2[f"p{p}_dmatches"], err_msg=f"pair {(a, b)}")
+        np.testing.assert_allclose(np.array([m.distance for m in dms], dtype=np.float32), c2[f"p{p}_dist"],
+                                   rtol=0, atol=1e-6)
+        total += len(dms)
+    assert counter == list(range(n)) and total > 0
+    for i in range(n):
+        q = store[i]["polygons_from_ftX"]
+        np.testing.assert_array_equal(q["keypoint_indices_rotated_list"], c2[f"i{i}_norm_idx"])
+        assert np.abs(q["keypoint_angles_rotated_list"] * np.pi - c2[f"i{i}_norm_angle"] * np.pi).max() < 1e-5
+        np.testing.assert_allclose(q["side_lengths_rotated_list"], c2[f"i{i}_norm_side"], rtol=0, atol=1e-10)
+        np.testing.assert_array_equal(q["keypoint_brightnesses_rotated_list"], c2[f"i{i}_norm_bright"])
