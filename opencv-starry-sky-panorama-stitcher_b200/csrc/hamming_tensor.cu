@@ -221,6 +221,7 @@ struct TcRow {
   int pq;              // popcount of the query row: hamming = pq - D
   uint16_t* my_slot;   // where this thread publishes the D of its own k-th best
   uint32_t tag;        // (item & 63) << 10, marks published values of the current work item
+  bool heavy;          // warp-uniform: skip the filter and run the full-tile tournament (thresholds settling)
   TC_PROF(long long p_wait; long long p_pass1; long long p_pass2; long long p_nflag;)
 };
 
@@ -391,6 +392,9 @@ __device__ __forceinline__ uint32_t tc_key64(uint32_t p, uint32_t pos) {
   asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(sh), "r"(mask), "r"(pos));
   return k;
 }
+#ifndef TC_HEAVY_LANES
+#define TC_HEAVY_LANES 4  // rows of a warp whose k-th best a tile must change to keep the warp in unfiltered mode
+#endif
 #ifndef TC_FULL_MIN
 #define TC_FULL_MIN 3     // flagged chunks (of 16) from which the full-tile tournament is used
 #endif
@@ -444,6 +448,20 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
   tc_ld128_packed(taddr, p);
   tc_wait_ld(p);
   tc_release(acc_empty, lane);
+#if TC_EXPERIMENT == 0
+  if (!MASKED && r.heavy) {
+    // thresholds still settling (always so in the first tile of an item): the filter would flag
+    // nearly every chunk, so skip it -- the ALU pipe is what these tiles are short of -- and stay
+    // in this mode while the tournament keeps changing the k-th best of many rows
+    TC_PROF(const long long c_p0 = clock64();)
+    const uint32_t kth_old = (K == 2) ? r.m2 : r.m1;
+    tc_tile_full<K>(p, col_base, r);
+    const uint32_t kth_new = (K == 2) ? r.m2 : r.m1;
+    r.heavy = __popc(__ballot_sync(0xffffffffu, kth_new != kth_old)) >= TC_HEAVY_LANES;
+    TC_PROF(r.p_pass2 += clock64() - c_p0; r.p_nflag += 16;)
+    return;
+  }
+#endif
   uint32_t flags = 0;
 #pragma unroll
   for (int c = 0; c < TC_HALF / TC_CHUNK; ++c) flags |= tc_beats(p + 4 * c, thrp) ? (1u << c) : 0u;
@@ -545,6 +563,7 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   r.pq = (row < w.nq) ? w.q_popc[row] : 0;
   r.my_slot = share + wg * TC_M + row_in_tile;
   r.tag = (item & 63u) << 10;
+  r.heavy = true;
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
   *r.my_slot = 0;
   TC_PROF(r.p_wait = 0; r.p_pass1 = 0; r.p_pass2 = 0; r.p_nflag = 0; const long long p_t0 = clock64();)
