@@ -37,6 +37,9 @@ WORKLOADS = {
                name="synthetic 200-image sweep x 20k descriptors, 19900 pairs"),
     "c1": dict(n_images=21, n_desc=1_000, seed=0,
                name="synthetic stand-in for example_01b: 21 images x 1000 descriptors, 210 pairs"),
+    # whole matcher stage of example_01b through the reference-facing class; see run_stage
+    "c1real": dict(stage=True, name="example_01b: ORB(1000) descriptors of the 21 forest JPEGs (frozen fixture), "
+                                    "CustomBruteForceMatcher.match_n_features, all 210 pairs incl. RANSAC + MatchesInfo"),
     # star-polygon path (kernels 2 + 3); see run_polygon_*
     "c4": dict(n_images=21, n_stars=2_000, seed=2, polygon=True,
                name="synthetic star fields 21 images x 2k stars, f=1135 px, 894x1342, 5-gon polygon matching, all 210 pairs"),
@@ -652,6 +655,96 @@ def run_polygon_ours(args, wl, inp, pairs):
     return line
 
 
+# ---- whole matcher stage at BASELINE config 1 (real ORB descriptors) -------------------------------
+class CvBFMatcherBackend:
+    """The reference's own arithmetic call (cv.BFMatcher(NORM_HAMMING, crossCheck=True).match per
+    pair, custom_bruteforce_matcher.py:193-199) behind the engine's two methods, so that the CPU arm
+    runs the SAME host logic (RANSAC, confidence, mirrored MatchesInfo) as ours."""
+
+    def __init__(self):
+        self.sets = None
+
+    def upload_descriptor_bank(self, rows):
+        self.sets = rows
+
+    def hamming_match_pairs(self, pairs, mode="crosscheck", ratio=0.75, variant="auto"):
+        import cv2 as cv
+        from ssp_b200.engine import HammingResult
+        qs, ts, ds, counts = [], [], [], []
+        for a, b in pairs:
+            ms = cv.BFMatcher(cv.NORM_HAMMING, crossCheck=True).match(cv.UMat(self.sets[a]), cv.UMat(self.sets[b]))
+            qs += [m.queryIdx for m in ms]
+            ts += [m.trainIdx for m in ms]
+            ds += [int(m.distance) for m in ms]
+            counts.append(len(ms))
+        o = np.zeros(len(pairs) + 1, dtype=np.int64)
+        np.cumsum(counts, out=o[1:])
+        return HammingResult(o, np.array(qs, np.int32), np.array(ts, np.int32), np.array(ds, np.int32))
+
+
+def run_stage(args, wl):
+    """One step = CustomBruteForceMatcher(...).match_n_features() from cv2.detail.ImageFeatures to
+    the tuple of 441 cv2.detail.MatchesInfo (the call stitching_detailed_enhanced.py:971-987
+    makes).  Host-side by nature: value == e2e, wall clock."""
+    import tempfile
+    import cv2 as cv
+    import ssp_b200
+    g = np.load(os.path.join(ROOT, "tests", "golden", "orb_forest_c1.npz"), allow_pickle=False)
+    offs = g["offsets"]
+    n = len(offs) - 1
+    h, w = int(g["img_shape"][0]), int(g["img_shape"][1])
+    orb = cv.ORB_create()
+    feats = []
+    for i in range(n):
+        ft = cv.detail.computeImageFeatures2(orb, np.zeros((h, w, 3), np.uint8))
+        ft.descriptors = cv.UMat(np.ascontiguousarray(g["descriptors"][offs[i]:offs[i + 1]]))
+        ft.keypoints = tuple(cv.KeyPoint(float(p[0]), float(p[1]), 30.0) for p in g["points"][offs[i]:offs[i + 1]])
+        ft.img_size = (w, h)
+        ft.img_idx = -1
+        feats.append(ft)
+    imgs = [np.zeros((h, w, 3), np.uint8) for _ in range(n)]
+    names = [str(x) for x in g["names"][:n]]
+    tmp = tempfile.mkdtemp(prefix="ssp_bench_stage_")
+    reference = args.impl == "reference"
+    engine = CvBFMatcherBackend() if reference else ssp_b200.Engine(0)
+    n_pairs = n * (n - 1) // 2
+
+    def step():
+        m = ssp_b200.CustomBruteForceMatcher(
+            imgs_features_orb_and_stars=feats, imgs_features_len_orb=[len(f.keypoints) for f in feats],
+            conf_thresh=0.2, img_names=names, work_scale_imgs=imgs, pairwise_matches_output_dir=tmp,
+            disable_prompts=True, output_dir_polygon_matching=tmp, predefined_overlaps=[],
+            focal_length_pinhole=1135, engine=engine, write_debug_images=False, verbose=False)
+        return m.match_n_features()
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        infos = step()
+    dt = (time.perf_counter() - t0) / args.steps
+    kept = sum(1 for mi in infos if mi.src_img_idx >= 0)
+    bytes_in = int(g["descriptors"].nbytes)
+    line = {
+        "metric": "image_pairs_matched_per_sec", "value": n_pairs / dt, "unit": "pairs/s", "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8 Hamming + f64 RANSAC (OpenCV)", "data": "real (frozen ORB fixture)",
+        "config": {"workload": wl["name"], "pairs": n_pairs, "mode": "crosscheck", "kept_directed_entries": kept,
+                   "note": "whole stage incl. cv.findHomography per pair and MatchesInfo construction on the host; "
+                           "the matching itself is one engine call in front of the pair loop"},
+        "e2e": {"value": n_pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": 0 if reference else bytes_in,
+                "d2h_bytes_per_step": 0},
+    }
+    if reference:
+        line["impl"] = "reference"
+        line["cpu_baseline"] = {"value": n_pairs / dt, "unit": "pairs/s", "cores": cv.getNumThreads(), "kind": "reference",
+                                "sample": f"cv2 {cv.__version__} BFMatcher crossCheck per pair + the same host logic, all {n_pairs} pairs per step"}
+    else:
+        line["gpu_launches"] = args.steps * 4
+        engine.close()
+    return line
+
+
 _JSON_FD = None
 
 
@@ -677,6 +770,10 @@ def main():
     if args.impl == "reference" and rank != 0:
         return 0  # rank 0 alone runs the CPU arm
     from ssp_b200 import synthetic as synth
+    if wl.get("stage"):
+        if rank == 0:
+            emit(run_stage(args, wl))
+        return 0
     if wl.get("polygon"):
         inp = polygon_inputs(wl)
         pairs = synth.all_pairs(wl["n_images"])
