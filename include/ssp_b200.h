@@ -120,7 +120,9 @@ int ssp_bind_descriptor_bank(ssp_ctx* ctx, const uint8_t* d_desc, const int64_t*
  *
  * Survivors of pair p are reported in ascending query index (OpenCV's order) at positions
  * [match_offsets[p], match_offsets[p+1]) of the arrays ssp_hamming_fetch_matches returns.
- * `match_offsets` is host memory with n_pairs+1 entries.  The call synchronises the stream. */
+ * `match_offsets` is host memory with n_pairs+1 entries.  The call synchronises the stream.
+ * A train set (in cross-check mode either image) must have fewer than 2^18 rows, the limit
+ * cv::BFMatcher itself asserts (IMGIDX_SHIFT); more is SSP_ERR_INVALID. */
 int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode,
                             int ratio_num, int ratio_den, int variant, int64_t* match_offsets);
 /* Copies the survivors of the last ssp_hamming_match_pairs call: queryIdx, trainIdx and the

@@ -292,7 +292,16 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
     SSP_REQUIRE(ctx, qi >= 0 && qi < n_images && ti >= 0 && ti < n_images, SSP_ERR_INVALID,
                 "ssp_hamming_match_pairs: pair %d = (%d, %d) out of range [0, %d)", p, qi, ti,
                 n_images);
-    fwd_rows += ctx->row_off[qi + 1] - ctx->row_off[qi];
+    // cv::BFMatcher packs (image, row) into one int and asserts rows < 2^18 per train set
+    // (IMGIDX_SHIFT); the packed best-2 keys here leave 22 bits, the limit kept is OpenCV's.
+    // Cross-check matches both directions, so either image is a train set.
+    const long long nq_p = ctx->row_off[qi + 1] - ctx->row_off[qi];
+    const long long nt_p = ctx->row_off[ti + 1] - ctx->row_off[ti];
+    SSP_REQUIRE(ctx, nt_p < (1LL << 18) && (!cross || nq_p < (1LL << 18)), SSP_ERR_INVALID,
+                "ssp_hamming_match_pairs: pair %d = (%d, %d): a train set of %lld rows exceeds "
+                "cv::BFMatcher's limit of 2^18 - 1 rows per image", p, qi, ti,
+                cross && nq_p > nt_p ? nq_p : nt_p);
+    fwd_rows += nq_p;
   }
   long long rev_cursor = fwd_rows;
   for (int p = 0; p < n_pairs; ++p) {

@@ -134,6 +134,13 @@ def test_errors_are_loud(engine):
     with pytest.raises(ssp_b200.EngineError, match="out of range"):
         engine.hamming_match_pairs([(0, 3)])
     assert engine.hamming_match_pairs([]).offsets.tolist() == [0]
+    # OpenCV's own limit on rows per train set (IMGIDX_SHIFT = 18) is an error, not a wrong answer
+    engine.upload_descriptor_bank([np.zeros((8, 32), np.uint8), np.zeros((1 << 18, 32), np.uint8)])
+    with pytest.raises(ssp_b200.EngineError, match="2\\^18"):
+        engine.hamming_match_pairs([(0, 1)], mode="knn2_ratio")
+    with pytest.raises(ssp_b200.EngineError, match="2\\^18"):
+        engine.hamming_match_pairs([(1, 0)], mode="crosscheck")
+    assert engine.hamming_match_pairs([(1, 0)], mode="knn2_ratio").offsets.tolist() == [0, 0]  # 8 equal rows: no ratio survivors
     fresh = ssp_b200.Engine(0)
     with pytest.raises(ssp_b200.EngineError, match="no descriptor bank"):
         fresh.hamming_match_pairs([(0, 0)])
