@@ -1,4 +1,6 @@
 """Host-side logic that needs no GPU: ratio terms, packing, sharding, generators, ordering."""
+import os
+
 import numpy as np
 import pytest
 
@@ -65,3 +67,24 @@ def test_strict_order_and_dummy_layout():
     fake.imgs_features_orb_and_stars = [None] * 3
     assert fake.strict_order_for_pairwise_matches_list() == [
         (-1, -1), (0, 1), (0, 2), (1, 0), (-1, -1), (1, 2), (2, 0), (2, 1), (-1, -1)]
+
+
+def test_bench_reference_arm_prints_one_contract_line():
+    """`bench.py --impl reference` needs no GPU: one JSON line on stdout with the contract's keys."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--workload", "c1",
+                        "--steps", "2", "--warmup", "1"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
+                "scaling", "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert key in d, key
+    assert d["impl"] == "reference" and d["value"] > 0 and d["steps"] == 2 and d["warmup"] == 1
+    assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0
+    assert "workload" in d["config"]
