@@ -553,7 +553,7 @@ def run_polygon_ours(args, wl, inp, pairs):
         n = 0
         if measured:
             for i in range(n_img):
-                eng.polygon_measure_resident(i, cand_dev[i].data_ptr(), cand_dev[i].shape[0])
+                eng.polygon_measure_resident(i, cand_dev[i].data_ptr(), cand_dev[i].shape[0], wait=False)
                 n += 3
         res = eng.polygon_match_pairs(local_pairs, fp32=args.fp32, fetch=False)
         return res, n + eng.polygon_last_stats()["launches"]

@@ -161,7 +161,10 @@ int ssp_fetch_star_rays(ssp_ctx* ctx, double* rays, int64_t capacity_stars, int 
  * polygon_data_store[img_id], cbpm:744-748).  `status` (optional, host, n_candidates bytes)
  * receives SSP_POLY_* per candidate; `n_valid` receives the number of stored polygons.
  * Returns SSP_ERR_DOMAIN (after storing everything else) if any candidate hit the acos domain
- * error on which the reference raises. */
+ * error on which the reference raises.
+ * With `status` == NULL and `n_valid` == NULL the call does not wait for the device (a batch of
+ * images is then measured back to back); the count -- and a domain error, if any -- is delivered
+ * by the next ssp_polygon_count / _fetch / _match_pairs call. */
 int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int64_t n_candidates,
                         double min_side_px, int mem_kind, uint8_t* status, int64_t* n_valid);
 /* Reads back the stored polygons of `image`, any pointer may be NULL.  All arrays are

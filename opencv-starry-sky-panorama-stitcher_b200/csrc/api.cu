@@ -91,6 +91,7 @@ int ssp_destroy(ssp_ctx* ctx) {
     pi.side.release();
     pi.bright.release();
   }
+  if (ctx->p_slots) cudaFreeHost(ctx->p_slots);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);

@@ -72,6 +72,7 @@ struct PolyImage {
   DevBuf bright;    // P x 5 float64
   long long count = -1;  // -1: not measured yet
   bool has_raw = false;
+  bool pending = false;  // measured without waiting: count / domain flag still sit in the pinned slot
 };
 
 struct PolyPair {
@@ -127,6 +128,10 @@ struct ssp_ctx {
   std::vector<long long> p_match_offsets;
   long long p_total_rows = 0;
   long long p_n_matches = -1;
+  // pinned slots {count, n_domain} of images measured with SSP_MEASURE_NO_WAIT (polygon.cu)
+  long long* p_slots = nullptr;
+  int p_slot_capacity = 0;
+  bool p_any_pending = false;
   int p_launches = 0;
   float p_main_ms = 0.f;
   long long p_evaluations = 0;

@@ -531,6 +531,31 @@ static int ensure_poly_image(ssp_ctx* ctx, int image, const char* who, bool need
   return SSP_OK;
 }
 
+// Completes every ssp_polygon_measure call issued with n_valid == NULL: one stream synchronise,
+// then counts and domain flags are read from their pinned slots.
+static int finish_pending_measures(ssp_ctx* ctx, const char* who) {
+  using namespace ssp;
+  if (!ctx->p_any_pending) return SSP_OK;
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->p_any_pending = false;
+  int bad = -1, n_bad = 0;
+  for (size_t i = 0; i < ctx->poly.size(); ++i) {
+    PolyImage& pi = ctx->poly[i];
+    if (!pi.pending) continue;
+    pi.pending = false;
+    pi.count = ctx->p_slots[2 * i];
+    if (ctx->p_slots[2 * i + 1] > 0 && bad < 0) {
+      bad = (int)i;
+      n_bad = (int)ctx->p_slots[2 * i + 1];
+    }
+  }
+  if (bad >= 0)
+    return fail(ctx, SSP_ERR_DOMAIN,
+                "%s: %d candidate(s) of image %d gave |acos argument| > 1 (the reference raises "
+                "ValueError at custom_bf_polygon_matcher.py:134)", who, n_bad, bad);
+  return SSP_OK;
+}
+
 int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int64_t n_candidates,
                         double min_side_px, int mem_kind, uint8_t* status, int64_t* n_valid) {
   using namespace ssp;
@@ -547,6 +572,7 @@ int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int6
   ctx->p_n_matches = -1;
   if (n == 0) {
     pi.count = 0;
+    pi.pending = false;
     pi.has_raw = true;
     if (n_valid) *n_valid = 0;
     return SSP_OK;
@@ -592,6 +618,29 @@ int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int6
       pi.star_idx.as<int>(), pi.angle.as<double>(), pi.side.as<double>(), pi.bright.as<double>(),
       pi.feat.as<double>());
   SSP_CUDA_TRY(ctx, cudaGetLastError());
+  constexpr int SLOT_IMAGES = 4096;
+  if (!n_valid && !status && image < SLOT_IMAGES) {
+    // no-wait form: the caller does not ask for the count now, so nothing here blocks; the
+    // count and the domain flag travel to a pinned slot and are read by the next call that
+    // needs them (ssp_polygon_count / _fetch / _match_pairs).  Scratch buffers are reused by
+    // the next image in stream order.
+    if (!ctx->p_slots) {
+      SSP_CUDA_TRY(ctx, cudaHostAlloc(reinterpret_cast<void**>(&ctx->p_slots),
+                                      (size_t)SLOT_IMAGES * 16, cudaHostAllocPortable));
+      ctx->p_slot_capacity = SLOT_IMAGES;
+    }
+    ctx->p_slots[2 * image + 1] = 0;
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&ctx->p_slots[2 * image], d_pos + n, 8, cudaMemcpyDeviceToHost,
+                                      ctx->stream));
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&ctx->p_slots[2 * image + 1], d_ndomain, 4, cudaMemcpyDeviceToHost,
+                                      ctx->stream));
+    pi.count = 0;
+    pi.pending = true;
+    pi.has_raw = true;
+    ctx->p_any_pending = true;
+    return SSP_OK;
+  }
+  pi.pending = false;
   long long count = 0;
   int n_domain = 0;
   SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&count, d_pos + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -614,6 +663,8 @@ int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int6
 int ssp_polygon_count(ssp_ctx* ctx, int image, int64_t* n_polygons) {
   using namespace ssp;
   if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  if (int rc = finish_pending_measures(ctx, "ssp_polygon_count")) return rc;
   SSP_REQUIRE(ctx, image >= 0 && (size_t)image < ctx->poly.size() && ctx->poly[(size_t)image].count >= 0,
               SSP_ERR_STATE, "ssp_polygon_count: image %d has no polygon bank", image);
   if (n_polygons) *n_polygons = ctx->poly[(size_t)image].count;
@@ -625,6 +676,7 @@ int ssp_polygon_fetch(ssp_ctx* ctx, int image, int32_t* star_idx, double* angle,
   using namespace ssp;
   if (!ctx) return SSP_ERR_INVALID;
   if (int rc = use_device(ctx)) return rc;
+  if (int rc = finish_pending_measures(ctx, "ssp_polygon_fetch")) return rc;
   SSP_REQUIRE(ctx, image >= 0 && (size_t)image < ctx->poly.size() && ctx->poly[(size_t)image].count >= 0,
               SSP_ERR_STATE, "ssp_polygon_fetch: image %d has no polygon bank", image);
   PolyImage& pi = ctx->poly[(size_t)image];
@@ -654,6 +706,7 @@ int ssp_polygon_upload_features(ssp_ctx* ctx, int image, const double* feat,
   using namespace ssp;
   if (!ctx) return SSP_ERR_INVALID;
   if (int rc = use_device(ctx)) return rc;
+  if (int rc = finish_pending_measures(ctx, "ssp_polygon_upload_features")) return rc;
   if (int rc = ensure_poly_image(ctx, image, "ssp_polygon_upload_features", false)) return rc;
   SSP_REQUIRE(ctx, n_polygons >= 0 && n_polygons < (1LL << 31) - 1024, SSP_ERR_INVALID,
               "ssp_polygon_upload_features: bad polygon count");
@@ -684,6 +737,7 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
   using namespace ssp;
   if (!ctx) return SSP_ERR_INVALID;
   if (int rc = use_device(ctx)) return rc;
+  if (int rc = finish_pending_measures(ctx, "ssp_polygon_match_pairs")) return rc;
   SSP_REQUIRE(ctx, n_pairs >= 0 && (n_pairs == 0 || pairs != nullptr), SSP_ERR_INVALID,
               "ssp_polygon_match_pairs: bad pair list");
   SSP_REQUIRE(ctx, match_offsets != nullptr, SSP_ERR_INVALID,

@@ -291,13 +291,15 @@ class Engine:
         return (n_valid.value, status) if return_status else n_valid.value
 
     def polygon_measure_resident(self, image: int, device_ptr: int, n_candidates: int,
-                                 min_side_px: float = 5.0) -> int:
-        """Same as `polygon_measure` for an int32 (n, 5) candidate table already on this device."""
+                                 min_side_px: float = 5.0, wait: bool = True):
+        """Same as `polygon_measure` for an int32 (n, 5) candidate table already on this device.
+        wait=False does not wait for the device (measure a batch of images back to back); the
+        count is then available from `polygon_count` and returned as None here."""
         n_valid = ctypes.c_int64()
         self._check(self._lib.ssp_polygon_measure(self._ctx, int(image), ctypes.c_void_p(device_ptr),
                                                   int(n_candidates), float(min_side_px), N.MEM_DEVICE,
-                                                  None, ctypes.byref(n_valid)))
-        return n_valid.value
+                                                  None, ctypes.byref(n_valid) if wait else None))
+        return n_valid.value if wait else None
 
     def polygon_count(self, image: int) -> int:
         n = ctypes.c_int64()

@@ -240,3 +240,32 @@ def test_c2_real_star_frames_all_pairs_reproduce_reference(engine, golden, tmp_p
         assert np.abs(q["keypoint_angles_rotated_list"] * np.pi - c2[f"i{i}_norm_angle"] * np.pi).max() < 1e-5
         np.testing.assert_allclose(q["side_lengths_rotated_list"], c2[f"i{i}_norm_side"], rtol=0, atol=1e-10)
         np.testing.assert_array_equal(q["keypoint_brightnesses_rotated_list"], c2[f"i{i}_norm_bright"])
+
+
+def test_no_wait_measure_of_a_batch_equals_the_waiting_form(engine):
+    """ssp_polygon_measure without status / n_valid does not block; counts (and banks) delivered by
+    the next consumer equal those of the waiting calls, also when images are re-measured."""
+    import torch
+    xy_l, b_l, _ = synth.star_fields(3, 300, seed=9)
+    engine.upload_star_bank(xy_l, b_l, 1342, 894, 1135.0)
+    cands = [synth.random_candidates(len(xy_l[i]), 1500 + 500 * i, seed=20 + i) for i in range(3)]
+    want = []
+    for i in range(3):
+        n = engine.polygon_measure(i, cands[i])
+        want.append((n, engine.polygon_fetch(i)))
+    ref = engine.polygon_match_pairs([(0, 1), (1, 2), (0, 2)], threshold=10.0, return_rowmin=True)
+    dev = [torch.from_numpy(c).cuda() for c in cands]
+    for rep in range(2):
+        for i in (2, 0, 1):
+            assert engine.polygon_measure_resident(i, dev[i].data_ptr(), len(cands[i]), wait=False) is None
+        for i in range(3):
+            assert engine.polygon_count(i) == want[i][0]
+            got = engine.polygon_fetch(i)
+            for k in ("star_idx", "feat", "angle", "side", "brightness"):
+                np.testing.assert_array_equal(got[k], want[i][1][k])
+    for i in range(3):
+        engine.polygon_measure_resident(i, dev[i].data_ptr(), len(cands[i]), wait=False)
+    res = engine.polygon_match_pairs([(0, 1), (1, 2), (0, 2)], threshold=10.0, return_rowmin=True)
+    np.testing.assert_array_equal(res.argmin, ref.argmin)
+    np.testing.assert_array_equal(res.mindist, ref.mindist)
+    np.testing.assert_array_equal(res.offsets, ref.offsets)
