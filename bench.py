@@ -355,6 +355,7 @@ def run_ours(args, wl, sets, pairs):
         roofline = {
             "bound": "tensor", "kernel": "hamming_tcgen05_kernel", "achieved": achieved, "peak": peak,
             "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+            "of": "measured" if "MEASURED_PEAKS" in peak_src else "fallback",
             "ops": "int8 multiply-add counted as 2 ops; s8 x s8 -> s32, exact",
             "peak_definition": peak_src,
             "pipe_peak_at_max_clock": pipe_peak,
