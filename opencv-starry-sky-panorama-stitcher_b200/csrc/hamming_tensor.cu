@@ -62,7 +62,7 @@ constexpr int TC_M = 128;                    // query rows per tile = TMEM lanes
 // from shared memory and the A tile is re-read for half as much work.
 constexpr int TC_N = 256;                    // train rows per stage = TMEM columns per accumulator
 constexpr int TC_ACC = 2;                    // accumulators in flight (2 x 256 = all 512 TMEM columns)
-constexpr int TC_CHUNK = 8;                  // columns per epilogue step
+[[maybe_unused]] constexpr int TC_CHUNK = 8;                  // columns per epilogue step
 constexpr int TC_HALF = TC_N / 2;            // columns of an accumulator drained by one warpgroup
 constexpr int TC_STAGES = 3;
 constexpr int TC_ROW_BYTES = 256;            // expanded row
@@ -432,6 +432,80 @@ __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_
   r.thr = max(r.thr, d_own);
 }
 
+#ifndef TC_GROUP16
+#define TC_GROUP16 1      // 1: pass 1 filters 16-column groups (half the ALU work of 8-column chunks)
+#endif
+#ifndef TC_FULL_MIN_G
+#define TC_FULL_MIN_G 3   // flagged groups (of 8) from which the full-tile tournament is used
+#endif
+constexpr int TC_GROUP = 16;   // columns per pass-1 group = 8 packed registers
+
+// Pass 1 on a 16-column group: does any column beat the packed threshold?  4 VIMNMX3 + compare.
+__device__ __forceinline__ bool tc_beats16(const uint32_t* p, uint32_t thrp) {
+  const uint32_t a = __vimax3_s16x2(p[0], p[1], p[2]);
+  const uint32_t b = __vimax3_s16x2(p[3], p[4], p[5]);
+  const uint32_t c = __vimax3_s16x2(p[6], p[7], thrp);
+  return __vimax3_s16x2(a, b, c) != thrp;
+}
+
+// packed key ((D & 0xFFF) << 4 | pos) of both halves, as tc_key64
+__device__ __forceinline__ uint32_t tc_key16(uint32_t p, uint32_t pos) {
+  uint32_t k;
+  const uint32_t sh = p * 16u;
+  uint32_t mask = 0xFFF0FFF0u;
+  asm volatile("" : "+r"(mask));
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(sh), "r"(mask), "r"(pos));
+  return k;
+}
+
+// Pass 2 on the registers: exact top-2 of one flagged 16-column group, q[i] = (D of column 2i, D of
+// column 2i + 1), on packed keys D * 16 + (15 - j) (s16 for D in [-2048, 2047]).
+template <int K, bool MASKED>
+__device__ __forceinline__ void tc_group_exact_packed(uint32_t (&q)[8], uint32_t col0, uint32_t nt, TcRow& r) {
+  if (MASKED) {   // pad columns (all-zero train rows, D = 0) must lose against every real column
+    constexpr uint32_t LOW = 0xF830u;  // D = -2000
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      q[i] = (col0 + 2 * i < nt ? (q[i] & 0xFFFFu) : LOW) | (col0 + 2 * i + 1 < nt ? (q[i] & 0xFFFF0000u) : (LOW << 16));
+  }
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t k0 = tc_key16(q[2 * i], (uint32_t)(14 - 4 * i) << 16 | (uint32_t)(15 - 4 * i));
+    const uint32_t k1 = tc_key16(q[2 * i + 1], (uint32_t)(12 - 4 * i) << 16 | (uint32_t)(13 - 4 * i));
+    h[i] = __vmaxs2(k0, k1);
+    if (K == 2) l[i] = __vmins2(k0, k1);
+  }
+#pragma unroll
+  for (int n = 2; n >= 1; n >>= 1) {
+#pragma unroll
+    for (int i = 0; i < n; ++i) {
+      if (K == 2) l[i] = __vimax3_s16x2(__vmins2(h[2 * i], h[2 * i + 1]), l[2 * i], l[2 * i + 1]);
+      h[i] = __vmaxs2(h[2 * i], h[2 * i + 1]);
+    }
+  }
+  const int t1l = (int)(short)(h[0] & 0xFFFFu), t1h = (int)h[0] >> 16;
+  const int hi = max(t1l, t1h);
+  const uint32_t j1 = 15u - ((uint32_t)hi & 15u);
+  uint32_t g1 = ((uint32_t)(r.pq - (hi >> 4)) << TC_KEY_SHIFT) + (col0 + j1);
+  if (MASKED) g1 = (col0 + j1 < nt) ? g1 : TC_KEY_NONE;
+  if (K == 2) {
+    const int s2l = (int)(short)(l[0] & 0xFFFFu), s2h = (int)l[0] >> 16;
+    const int lo = __vimax3_s32(min(t1l, t1h), s2l, s2h);
+    const uint32_t j2 = 15u - ((uint32_t)lo & 15u);
+    uint32_t g2 = ((uint32_t)(r.pq - (lo >> 4)) << TC_KEY_SHIFT) + (col0 + j2);
+    if (MASKED) g2 = (col0 + j2 < nt) ? g2 : TC_KEY_NONE;
+    r.m2 = min(min(r.m2, g2), max(r.m1, g1));   // g1 <= g2 and m1 <= m2
+  }
+  r.m1 = min(r.m1, g1);
+  const uint32_t kth = (K == 2) ? r.m2 : r.m1;
+  if (kth != TC_KEY_NONE) {
+    const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
+    *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
+    r.thr = max(r.thr, d_own);
+  }
+}
+
 template <int K, bool MASKED>
 __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint32_t nt, TcRow& r,
                                         uint64_t* acc_empty, int lane) {
@@ -462,6 +536,35 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
     return;
   }
 #endif
+#if TC_GROUP16
+  uint32_t flags = 0;
+#pragma unroll
+  for (int g = 0; g < TC_HALF / TC_GROUP; ++g) flags |= tc_beats16(p + 8 * g, thrp) ? (1u << g) : 0u;
+#if TC_EXPERIMENT == 2 || TC_EXPERIMENT == 3
+  if (flags == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
+  return;
+#endif
+  flags = __reduce_or_sync(0xffffffffu, flags);
+  TC_PROF(r.p_nflag += 2 * __popc(flags);)
+  TC_PROF(const long long c_p1 = clock64();)
+  if (!MASKED && __popc(flags) >= TC_FULL_MIN_G) {
+    tc_tile_full<K>(p, col_base, r);
+    TC_PROF(r.p_pass2 += clock64() - c_p1;)
+    return;
+  }
+  while (flags) {   // warp-uniform: `flags` is the same in every lane
+    const uint32_t g = tc_pop(flags);
+    uint32_t q[8];
+    switch (g) {    // warp-uniform jump: register arrays cannot be indexed dynamically
+#define TC_CASE(i) case i: _Pragma("unroll") for (int j = 0; j < 8; ++j) q[j] = p[8 * i + j]; break;
+      TC_CASE(0) TC_CASE(1) TC_CASE(2) TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6)
+      default: _Pragma("unroll") for (int j = 0; j < 8; ++j) q[j] = p[56 + j]; break;
+#undef TC_CASE
+    }
+    tc_group_exact_packed<K, MASKED>(q, col_base + g * TC_GROUP, nt, r);
+  }
+  TC_PROF(r.p_pass2 += clock64() - c_p1;)
+#else
   uint32_t flags = 0;
 #pragma unroll
   for (int c = 0; c < TC_HALF / TC_CHUNK; ++c) flags |= tc_beats(p + 4 * c, thrp) ? (1u << c) : 0u;
@@ -490,6 +593,7 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
     tc_chunk_exact_packed<K, MASKED>(q0, q1, q2, q3, col_base + c * TC_CHUNK, nt, r);
   }
   TC_PROF(r.p_pass2 += clock64() - c_p1;)
+#endif
 #else
   const uint32_t thrp = (uint32_t)(max(r.thr, -32768) & 0xFFFF) * 0x10001u;
   uint32_t flags = 0;
