@@ -56,6 +56,9 @@ namespace ssp {
 #else
 #define TC_PROF(x)
 #endif
+#ifndef TC_QSCALE
+#define TC_QSCALE 64      // query operands are -+TC_QSCALE: accumulators hold TC_QSCALE * D
+#endif
 constexpr int TC_M = 128;                    // query rows per tile = TMEM lanes
 // N = 256 is the only full-rate shape here: with N = 128 (four smaller accumulators, tried for a
 // deeper epilogue pipeline) the MMA-only probe drops from 60 ms to 95 ms -- both operands come
@@ -111,7 +114,11 @@ expand_bank_kernel(const uint8_t* __restrict__ packed, int n_rows, int rows_pad,
       // bit j of the nibble -> lsb of byte j (disjoint partial products)
       const uint32_t t = (nib * 0x00204081u) & 0x01010101u;
       wt[i] = t;                               // train: 0 / 1
+#if TC_QSCALE == 64
+      wq[i] = 0xC0C0C0C0u ^ (t * 0x80u);       // query: 0 -> 0xC0 (-64), 1 -> 0x40 (+64): one bit apart
+#else
       wq[i] = 0xFFFFFFFFu ^ (t * 0xFEu);       // query: 0 -> 0xFF (-1), 1 -> 0x01 (+1)
+#endif
     }
     vq = make_uint4(wq[0], wq[1], wq[2], wq[3]);
     vt = make_uint4(wt[0], wt[1], wt[2], wt[3]);
@@ -385,12 +392,16 @@ __device__ __forceinline__ void tc_chunk_exact_packed(uint32_t q0, uint32_t q1, 
 // position as the immediate (left alone the compiler emits shift + two immediate LOP3s, and the
 // ALU pipe is what bounds the full-tile tournament)
 __device__ __forceinline__ uint32_t tc_key64(uint32_t p, uint32_t pos) {
+#if TC_QSCALE == 64
+  return p | pos;   // the registers already hold 64 * D in both halves: the low 6 bits are free
+#else
   uint32_t k;
   uint32_t sh = p * 64u;
   uint32_t mask = 0xFFC0FFC0u;
   asm volatile("" : "+r"(mask));   // keep the mask in a register
   asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(sh), "r"(mask), "r"(pos));
   return k;
+#endif
 }
 #ifndef TC_HEAVY_LANES
 #define TC_HEAVY_LANES 4  // rows of a warp whose k-th best a tile must change to keep the warp in unfiltered mode
@@ -450,12 +461,16 @@ __device__ __forceinline__ bool tc_beats16(const uint32_t* p, uint32_t thrp) {
 
 // packed key ((D & 0xFFF) << 4 | pos) of both halves, as tc_key64
 __device__ __forceinline__ uint32_t tc_key16(uint32_t p, uint32_t pos) {
+#if TC_QSCALE == 64
+  return p | pos;
+#else
   uint32_t k;
   const uint32_t sh = p * 16u;
   uint32_t mask = 0xFFF0FFF0u;
   asm volatile("" : "+r"(mask));
   asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(sh), "r"(mask), "r"(pos));
   return k;
+#endif
 }
 
 // Pass 2 on the registers: exact top-2 of one flagged 16-column group, q[i] = (D of column 2i, D of
@@ -463,7 +478,7 @@ __device__ __forceinline__ uint32_t tc_key16(uint32_t p, uint32_t pos) {
 template <int K, bool MASKED>
 __device__ __forceinline__ void tc_group_exact_packed(uint32_t (&q)[8], uint32_t col0, uint32_t nt, TcRow& r) {
   if (MASKED) {   // pad columns (all-zero train rows, D = 0) must lose against every real column
-    constexpr uint32_t LOW = 0xF830u;  // D = -2000
+    constexpr uint32_t LOW = (TC_QSCALE == 64) ? 0x8000u : 0xF830u;  // below every real column
 #pragma unroll
     for (int i = 0; i < 8; ++i)
       q[i] = (col0 + 2 * i < nt ? (q[i] & 0xFFFFu) : LOW) | (col0 + 2 * i + 1 < nt ? (q[i] & 0xFFFF0000u) : (LOW << 16));
@@ -486,14 +501,15 @@ __device__ __forceinline__ void tc_group_exact_packed(uint32_t (&q)[8], uint32_t
   }
   const int t1l = (int)(short)(h[0] & 0xFFFFu), t1h = (int)h[0] >> 16;
   const int hi = max(t1l, t1h);
+  constexpr int DSH = (TC_QSCALE == 64) ? 6 : 4;   // key = D << DSH | (15 - j)
   const uint32_t j1 = 15u - ((uint32_t)hi & 15u);
-  uint32_t g1 = ((uint32_t)(r.pq - (hi >> 4)) << TC_KEY_SHIFT) + (col0 + j1);
+  uint32_t g1 = ((uint32_t)(r.pq - (hi >> DSH)) << TC_KEY_SHIFT) + (col0 + j1);
   if (MASKED) g1 = (col0 + j1 < nt) ? g1 : TC_KEY_NONE;
   if (K == 2) {
     const int s2l = (int)(short)(l[0] & 0xFFFFu), s2h = (int)l[0] >> 16;
     const int lo = __vimax3_s32(min(t1l, t1h), s2l, s2h);
     const uint32_t j2 = 15u - ((uint32_t)lo & 15u);
-    uint32_t g2 = ((uint32_t)(r.pq - (lo >> 4)) << TC_KEY_SHIFT) + (col0 + j2);
+    uint32_t g2 = ((uint32_t)(r.pq - (lo >> DSH)) << TC_KEY_SHIFT) + (col0 + j2);
     if (MASKED) g2 = (col0 + j2 < nt) ? g2 : TC_KEY_NONE;
     r.m2 = min(min(r.m2, g2), max(r.m1, g1));   // g1 <= g2 and m1 <= m2
   }
@@ -517,7 +533,7 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
   // The accumulator goes back to the MMA issuer as soon as its 128 columns sit in registers (held
   // for one TMEM load); both passes then run on the registers while the tensor pipe already
   // fills the buffer again.
-  const uint32_t thrp = (uint32_t)(max(r.thr, -32768) & 0xFFFF) * 0x10001u;
+  const uint32_t thrp = (uint32_t)(max(r.thr * TC_QSCALE, -32768) & 0xFFFF) * 0x10001u;
   uint32_t p[TC_HALF / 2];
   tc_ld128_packed(taddr, p);
   tc_wait_ld(p);
