@@ -2,14 +2,16 @@
 // on the 5th-generation tensor cores (tcgen05.mma kind::i8, accumulators in TMEM).
 //
 // Replaces the same reference calls as hamming.cu (custom_bruteforce_matcher.py:160-172 and
-// :193-199).  Encoding: a QUERY row q is expanded to {-1,+1}^256 (bit 0 -> -1, bit 1 -> +1), a
-// TRAIN row t to {0,1}^256.  Then
+// :193-199).  Encoding: a QUERY row q is expanded to {-64,+64}^256 (bit 0 -> -64, bit 1 -> +64), a
+// TRAIN row t to {0,1}^256.  With q' = q / 64 in {-1,+1}:
 //     D(q, t) = sum_k q'_k t_k = popc(q & t) - popc(~q & t) = 2 popc(q & t) - popc(t)
 //     hamming(q, t) = popc(q) + popc(t) - 2 popc(q & t) = popc(q) - D(q, t)      (exact in int32)
 // so for a fixed query row the nearest neighbour is the LARGEST D, and popc(q) is one constant per
-// epilogue thread.  (The symmetric +-1 x +-1 encoding gives the same ordering but toggles every
-// operand bit: the probes in profiles/ show it pulls the SM clock to ~1.54 GHz under the power cap,
-// while 0/1 train operands hold a higher clock.)
+// epilogue thread.  The accumulators hold 64 * D.  Why +-64 and 0/1: the kernel runs at the
+// board's power cap, and operand toggling is what it pays for.  +-1 x +-1 toggles every operand
+// bit (MMA-only probe: 1.54 GHz); +-1 x 0/1 holds ~1.85 GHz in the full kernel; 0xC0 / 0x40 differ
+// in ONE bit and hold ~1.95 GHz -- and 64 * D leaves the low six bits of every packed s16 free,
+// so the tournament keys of the epilogue are a single OR (profiles/r01_tc_sweep_qscale64.txt).
 // on sm_100a the b1 `mma.sync ... and.popc` path is emulated by IMMA + unpack
 // code, the native route is tcgen05 kind::i8 on pre-expanded operands; this file is that route.
 //
@@ -25,18 +27,19 @@
 // next to the bank.
 //
 // Kernel.  Persistent, one CTA per SM, warp-specialised:
-//   warp 8  : TMA producer  — query tile (128 rows, 32 KB) once per work item, then streams the
+//   warp 8  : TMA producer  -- query tile (128 rows, 32 KB) once per work item, then streams the
 //             train image through a ring of three 64 KB stages (256 train rows each)
-//   warp 9  : MMA issuer    — one elected thread issues 8 x tcgen05.mma (M128 N256 K32) per
+//   warp 9  : MMA issuer    -- one elected thread issues 8 x tcgen05.mma (M128 N256 K32) per
 //             stage into one of two 256-column TMEM accumulators, tcgen05.commit signals
 //             "stage free" and "accumulator full" mbarriers
-//   warps 0-7: two epilogue warpgroups, each draining one 128-column half of every accumulator
-//             and handing it back as soon as the values it still needs are in registers.  Each
-//             thread owns one TMEM lane = one query row.  Pass 1 streams the accumulator as packed s16 pairs
-//             (tcgen05.ld .pack::16b) through a VIMNMX3.S16x2 max-tree and compares each
-//             8-column chunk with the row's current k-th best; pass 2 re-reads only the chunks
-//             in which some lane of the warp beat its threshold and extracts their exact top-2
-//             by a log-depth tournament over packed keys, merged into the running best-2 as
+//   warps 0-7: two epilogue warpgroups, each draining one 128-column half of every accumulator.
+//             Each thread owns one TMEM lane = one query row.  One tcgen05.ld (.pack::16b) brings
+//             the 128 columns into 64 registers as packed s16 pairs and the accumulator goes
+//             back to the MMA issuer at once.  Pass 1 runs the registers through a
+//             VIMNMX3.S16x2 max tree per 16-column group against the row's current k-th best;
+//             pass 2 extracts the exact top-2 of the groups in which some lane of the warp beat
+//             its threshold (or of the whole tile, while thresholds are still settling) by a
+//             log-depth tournament over packed keys, merged into the running best-2 as
 //             (distance << 22 | train index), which is OpenCV's (distance, lowest index) order.
 //             The running best-2 stays in registers for the whole train image; the two
 //             warpgroups publish their thresholds to each other through shared memory (each sees
@@ -65,7 +68,6 @@ constexpr int TC_M = 128;                    // query rows per tile = TMEM lanes
 // from shared memory and the A tile is re-read for half as much work.
 constexpr int TC_N = 256;                    // train rows per stage = TMEM columns per accumulator
 constexpr int TC_ACC = 2;                    // accumulators in flight (2 x 256 = all 512 TMEM columns)
-[[maybe_unused]] constexpr int TC_CHUNK = 8;                  // columns per epilogue step
 constexpr int TC_HALF = TC_N / 2;            // columns of an accumulator drained by one warpgroup
 constexpr int TC_STAGES = 3;
 constexpr int TC_ROW_BYTES = 256;            // expanded row
@@ -77,7 +79,6 @@ constexpr int TC_PAD = 256;                  // rows of every expanded image are
 constexpr uint32_t TC_KEY_SHIFT = 22;
 constexpr uint32_t TC_KEY_IDX_MASK = (1u << TC_KEY_SHIFT) - 1u;
 constexpr uint32_t TC_KEY_NONE = 0xFFFFFFFFu;
-[[maybe_unused]] constexpr int TC_D_MASKED = -30000;          // stands for "no such column"
 constexpr int TC_THR_NONE = -100000;         // "no k-th neighbour yet"
 // bytes after the operand stages: mbarriers + TMEM slot (256), best-2 merge slots, thresholds
 constexpr int TC_TAIL_BYTES = 256 + 2 * TC_M * (int)sizeof(uint2) + 2 * TC_M * (int)sizeof(uint16_t);
@@ -202,24 +203,6 @@ __device__ __forceinline__ uint64_t tc_smem_desc(uint32_t smem_addr) {
 constexpr uint32_t TC_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_N >> 3) << 17) |
                               ((uint32_t)(TC_M >> 4) << 24);
 
-// 8 consecutive TMEM columns of this thread's lane
-__device__ __forceinline__ void tc_ld8(uint32_t taddr, int (&v)[8]) {
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
-                 "=r"(v[7])
-               : "r"(taddr)
-               : "memory");
-}
-// The registers of the preceding tcgen05.ld are valid only after this wait; they are passed as
-// in/out operands so the compiler cannot schedule their consumers above it.
-__device__ __forceinline__ void tc_wait_ld(int (&v)[8]) {
-  asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]),
-                 "+r"(v[7])
-               :
-               : "memory");
-}
-
 // ---- epilogue ------------------------------------------------------------------------------------
 // Per-thread state of one query row while a train image streams by.
 struct TcRow {
@@ -247,80 +230,15 @@ __device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[64]) {
                :
                : "memory");
 }
-// waits for up to four 8-column chunks fetched for pass 2
-__device__ __forceinline__ void tc_wait_ld(int (&a)[8], int (&b)[8], int (&c)[8], int (&d)[8]) {
-  asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
-                 "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7]),
-                 "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]), "+r"(c[4]), "+r"(c[5]), "+r"(c[6]), "+r"(c[7]),
-                 "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]), "+r"(d[4]), "+r"(d[5]), "+r"(d[6]), "+r"(d[7])
-               :
-               : "memory");
-}
-
-// Pass 1 (filter): does any of the 8 columns held by p[0..3] beat the packed threshold?
-__device__ __forceinline__ bool tc_beats(const uint32_t* p, uint32_t thrp) {
-  const uint32_t t0 = __vimax3_s16x2(p[0], p[1], p[2]);
-  return __vimax3_s16x2(t0, p[3], thrp) != thrp;   // some half is > its threshold half
-}
-
-// Pass 2 (exact): top-2 of one flagged 8-column chunk, v[j] = D(query row, train row col0 + j),
-// by a tournament over local keys D * 8 + (7 - j) -- larger is better and among equal D the
-// lowest column wins, OpenCV's (distance, lowest index) order -- merged into the running best-2.
-// The key IMADs run on the FMA pipe, the tournament on the ALU pipe.  Every lane of the warp runs
-// it (the merge is exact, so lanes that did not need it are unaffected).
-template <int K, bool MASKED>
-__device__ __forceinline__ void tc_chunk_exact(int (&v)[8], uint32_t col0, uint32_t nt, TcRow& r) {
-  if (MASKED) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = (col0 + j < nt) ? v[j] : TC_D_MASKED;
-  }
-  int hi[4], lo[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int a = v[2 * i] * 8 + (7 - 2 * i);
-    const int b = v[2 * i + 1] * 8 + (6 - 2 * i);
-    hi[i] = max(a, b);
-    if (K == 2) lo[i] = min(a, b);
-  }
-#pragma unroll
-  for (int n = 2; n >= 1; n >>= 1) {
-#pragma unroll
-    for (int i = 0; i < n; ++i) {
-      if (K == 2) lo[i] = __vimax3_s32(min(hi[2 * i], hi[2 * i + 1]), lo[2 * i], lo[2 * i + 1]);
-      hi[i] = max(hi[2 * i], hi[2 * i + 1]);
-    }
-  }
-  // local key -> global packed key
-  const uint32_t j1 = 7u - ((uint32_t)hi[0] & 7u);
-  uint32_t k1 = ((uint32_t)(r.pq - (hi[0] >> 3)) << TC_KEY_SHIFT) + (col0 + j1);
-  if (MASKED) k1 = (col0 + j1 < nt) ? k1 : TC_KEY_NONE;
-  if (K == 2) {
-    const uint32_t j2 = 7u - ((uint32_t)lo[0] & 7u);
-    uint32_t k2 = ((uint32_t)(r.pq - (lo[0] >> 3)) << TC_KEY_SHIFT) + (col0 + j2);
-    if (MASKED) k2 = (col0 + j2 < nt) ? k2 : TC_KEY_NONE;
-    r.m2 = min(min(r.m2, k2), max(r.m1, k1));   // k1 <= k2 and m1 <= m2
-  }
-  r.m1 = min(r.m1, k1);
-  const uint32_t kth = (K == 2) ? r.m2 : r.m1;
-  if (kth != TC_KEY_NONE) {
-    const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
-    *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
-    r.thr = max(r.thr, d_own);
-  }
-}
-
-// This warpgroup's 128-column half of one accumulator, for this thread's lane, in two passes.
-//   Pass 1 reads the 128 columns as packed s16 pairs with ONE tcgen05.ld and records, per
-//   8-column chunk, whether any lane of the warp sees a value above its row's threshold:
-//   branch-free, 4 instructions per chunk and lane.  Pad columns of the last tile read as D = 0
-//   and may raise a flag needlessly.
-//   Pass 2 re-reads only the flagged chunks (typically one of 16 once the thresholds have
-//   settled) as int32, four at a time, and updates the best-2 exactly.
-// The accumulator is handed back to the MMA issuer (`acc_empty`) as soon as the LAST flagged chunk
-// is in registers, before its tournament runs: the tensor pipe needs the buffer of tile g back
-// within one stage time (tile g + 1 runs meanwhile), so what counts is how long the buffer is
-// held, not how long the tile takes.
+// This warpgroup's 128-column half of one accumulator, for this thread's lane, in two passes over
+// the SAME 64 registers (one tcgen05.ld, after which the accumulator is handed back at once: the
+// tensor pipe needs the buffer of tile g back within one stage time, so what counts is how long
+// the buffer is held, not how long the tile takes).
+//   Pass 1 records, per 16-column group, whether any lane of the warp sees a value above its
+//   row's threshold: branch-free.  Pad columns of the last tile read as D = 0 and may raise a
+//   flag needlessly.
+//   Pass 2 updates the best-2 exactly from the flagged groups (tc_group_exact_packed), or from the
+//   whole tile at once when many are flagged (tc_tile_full).
 __device__ __forceinline__ uint32_t tc_pop(uint32_t& flags) {
   const uint32_t c = (uint32_t)__ffs((int)flags) - 1u;
   flags &= flags - 1u;
@@ -331,55 +249,6 @@ __device__ __forceinline__ void tc_release(uint64_t* acc_empty, int lane) {
   __syncwarp();
   if (lane == 0) mbar_arrive(acc_empty);
 }
-#ifndef TC_REGPASS2
-#define TC_REGPASS2 1     // 1: pass 2 works on the packed registers of pass 1 (no TMEM re-read)
-#endif
-
-// Pass 2 on the registers pass 1 already holds: exact top-2 of one flagged 8-column chunk given as
-// four packed s16x2 registers q[m] = (D of column 2m, D of column 2m + 1).  The tournament runs on
-// PACKED keys D * 8 + (7 - j), which fit s16 for D in [-4096, 4095]: the low halves rank the even
-// columns, the high halves the odd ones, and the two half-tournaments meet at the end.
-template <int K, bool MASKED>
-__device__ __forceinline__ void tc_chunk_exact_packed(uint32_t q0, uint32_t q1, uint32_t q2, uint32_t q3,
-                                                      uint32_t col0, uint32_t nt, TcRow& r) {
-  if (MASKED) {   // pad columns (all-zero train rows, D = 0) must lose against every real column
-    constexpr uint32_t LOW = 0xF060u;  // D = -4000
-    q0 = (col0 + 0 < nt ? (q0 & 0xFFFFu) : LOW) | (col0 + 1 < nt ? (q0 & 0xFFFF0000u) : (LOW << 16));
-    q1 = (col0 + 2 < nt ? (q1 & 0xFFFFu) : LOW) | (col0 + 3 < nt ? (q1 & 0xFFFF0000u) : (LOW << 16));
-    q2 = (col0 + 4 < nt ? (q2 & 0xFFFFu) : LOW) | (col0 + 5 < nt ? (q2 & 0xFFFF0000u) : (LOW << 16));
-    q3 = (col0 + 6 < nt ? (q3 & 0xFFFFu) : LOW) | (col0 + 7 < nt ? (q3 & 0xFFFF0000u) : (LOW << 16));
-  }
-  // (q & 0x1FFF1FFF) * 8 cannot carry between the halves; the constant adds 7 - j
-  const uint32_t k0 = (q0 & 0x1FFF1FFFu) * 8u + 0x00060007u;
-  const uint32_t k1 = (q1 & 0x1FFF1FFFu) * 8u + 0x00040005u;
-  const uint32_t k2 = (q2 & 0x1FFF1FFFu) * 8u + 0x00020003u;
-  const uint32_t k3 = (q3 & 0x1FFF1FFFu) * 8u + 0x00000001u;
-  const uint32_t a = __vmaxs2(k0, k1), c = __vmaxs2(k2, k3);
-  const uint32_t t1 = __vmaxs2(a, c);
-  const int t1l = (int)(short)(t1 & 0xFFFFu), t1h = (int)t1 >> 16;
-  const int hi = max(t1l, t1h);
-  const uint32_t j1 = 7u - ((uint32_t)hi & 7u);
-  uint32_t g1 = ((uint32_t)(r.pq - (hi >> 3)) << TC_KEY_SHIFT) + (col0 + j1);
-  if (MASKED) g1 = (col0 + j1 < nt) ? g1 : TC_KEY_NONE;
-  if (K == 2) {
-    const uint32_t b = __vmins2(k0, k1), d = __vmins2(k2, k3);
-    const uint32_t s2 = __vimax3_s16x2(__vmins2(a, c), b, d);
-    const int s2l = (int)(short)(s2 & 0xFFFFu), s2h = (int)s2 >> 16;
-    const int lo = __vimax3_s32(min(t1l, t1h), s2l, s2h);
-    const uint32_t j2 = 7u - ((uint32_t)lo & 7u);
-    uint32_t g2 = ((uint32_t)(r.pq - (lo >> 3)) << TC_KEY_SHIFT) + (col0 + j2);
-    if (MASKED) g2 = (col0 + j2 < nt) ? g2 : TC_KEY_NONE;
-    r.m2 = min(min(r.m2, g2), max(r.m1, g1));   // g1 <= g2 and m1 <= m2
-  }
-  r.m1 = min(r.m1, g1);
-  const uint32_t kth = (K == 2) ? r.m2 : r.m1;
-  if (kth != TC_KEY_NONE) {
-    const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
-    *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
-    r.thr = max(r.thr, d_own);
-  }
-}
-
 // Pass 2 for a tile in which MANY chunks are flagged (the first tiles of every work item, while
 // the thresholds are still settling): one branch-free tournament over all 128 columns instead of
 // a chain of per-chunk ones.  Packed key of register i = D * 64 + (63 - i) -- 10 bits of D and 6
@@ -405,9 +274,6 @@ __device__ __forceinline__ uint32_t tc_key64(uint32_t p, uint32_t pos) {
 }
 #ifndef TC_HEAVY_LANES
 #define TC_HEAVY_LANES 4  // rows of a warp whose k-th best a tile must change to keep the warp in unfiltered mode
-#endif
-#ifndef TC_FULL_MIN
-#define TC_FULL_MIN 3     // flagged chunks (of 16) from which the full-tile tournament is used
 #endif
 template <int K>
 __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_t col_base, TcRow& r) {
@@ -443,9 +309,6 @@ __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_
   r.thr = max(r.thr, d_own);
 }
 
-#ifndef TC_GROUP16
-#define TC_GROUP16 1      // 1: pass 1 filters 16-column groups (half the ALU work of 8-column chunks)
-#endif
 #ifndef TC_FULL_MIN_G
 #define TC_FULL_MIN_G 3   // flagged groups (of 8) from which the full-tile tournament is used
 #endif
@@ -529,7 +392,6 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
   tc_release(acc_empty, lane);
   return;
 #endif
-#if TC_REGPASS2
   // The accumulator goes back to the MMA issuer as soon as its 128 columns sit in registers (held
   // for one TMEM load); both passes then run on the registers while the tensor pipe already
   // fills the buffer again.
@@ -552,7 +414,6 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
     return;
   }
 #endif
-#if TC_GROUP16
   uint32_t flags = 0;
 #pragma unroll
   for (int g = 0; g < TC_HALF / TC_GROUP; ++g) flags |= tc_beats16(p + 8 * g, thrp) ? (1u << g) : 0u;
@@ -580,75 +441,6 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
     tc_group_exact_packed<K, MASKED>(q, col_base + g * TC_GROUP, nt, r);
   }
   TC_PROF(r.p_pass2 += clock64() - c_p1;)
-#else
-  uint32_t flags = 0;
-#pragma unroll
-  for (int c = 0; c < TC_HALF / TC_CHUNK; ++c) flags |= tc_beats(p + 4 * c, thrp) ? (1u << c) : 0u;
-#if TC_EXPERIMENT == 2 || TC_EXPERIMENT == 3
-  if (flags == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
-  return;
-#endif
-  flags = __reduce_or_sync(0xffffffffu, flags);
-  TC_PROF(r.p_nflag += __popc(flags);)
-  TC_PROF(const long long c_p1 = clock64();)
-  if (!MASKED && __popc(flags) >= TC_FULL_MIN) {
-    tc_tile_full<K>(p, col_base, r);
-    TC_PROF(r.p_pass2 += clock64() - c_p1;)
-    return;
-  }
-  while (flags) {   // warp-uniform: `flags` is the same in every lane
-    const uint32_t c = tc_pop(flags);
-    uint32_t q0, q1, q2, q3;
-    switch (c) {    // warp-uniform jump: register arrays cannot be indexed dynamically
-#define TC_CASE(i) case i: q0 = p[4 * i]; q1 = p[4 * i + 1]; q2 = p[4 * i + 2]; q3 = p[4 * i + 3]; break;
-      TC_CASE(0) TC_CASE(1) TC_CASE(2) TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6) TC_CASE(7)
-      TC_CASE(8) TC_CASE(9) TC_CASE(10) TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14)
-      default: q0 = p[60]; q1 = p[61]; q2 = p[62]; q3 = p[63]; break;
-#undef TC_CASE
-    }
-    tc_chunk_exact_packed<K, MASKED>(q0, q1, q2, q3, col_base + c * TC_CHUNK, nt, r);
-  }
-  TC_PROF(r.p_pass2 += clock64() - c_p1;)
-#endif
-#else
-  const uint32_t thrp = (uint32_t)(max(r.thr, -32768) & 0xFFFF) * 0x10001u;
-  uint32_t flags = 0;
-  {
-    uint32_t p[TC_HALF / 2];
-    tc_ld128_packed(taddr, p);
-    tc_wait_ld(p);
-#pragma unroll
-    for (int c = 0; c < TC_HALF / TC_CHUNK; ++c) flags |= tc_beats(p + 4 * c, thrp) ? (1u << c) : 0u;
-  }
-#if TC_EXPERIMENT == 2 || TC_EXPERIMENT == 3
-  if (flags == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
-  tc_release(acc_empty, lane);
-  return;
-#endif
-  flags = __reduce_or_sync(0xffffffffu, flags);
-  TC_PROF(r.p_nflag += __popc(flags);)
-  if (flags == 0) {
-    tc_release(acc_empty, lane);
-    return;
-  }
-  TC_PROF(const long long c_p1 = clock64();)
-  do {   // warp-uniform: `flags` is the same in every lane
-    int v0[8], v1[8], v2[8], v3[8];
-    uint32_t c0 = tc_pop(flags), c1 = 0, c2 = 0, c3 = 0;
-    int n = 1;
-    tc_ld8(taddr + c0 * TC_CHUNK, v0);
-    if (flags) { c1 = tc_pop(flags); tc_ld8(taddr + c1 * TC_CHUNK, v1); n = 2; }
-    if (flags) { c2 = tc_pop(flags); tc_ld8(taddr + c2 * TC_CHUNK, v2); n = 3; }
-    if (flags) { c3 = tc_pop(flags); tc_ld8(taddr + c3 * TC_CHUNK, v3); n = 4; }
-    tc_wait_ld(v0, v1, v2, v3);
-    if (flags == 0) tc_release(acc_empty, lane);
-    tc_chunk_exact<K, MASKED>(v0, col_base + c0 * TC_CHUNK, nt, r);
-    if (n > 1) tc_chunk_exact<K, MASKED>(v1, col_base + c1 * TC_CHUNK, nt, r);
-    if (n > 2) tc_chunk_exact<K, MASKED>(v2, col_base + c2 * TC_CHUNK, nt, r);
-    if (n > 3) tc_chunk_exact<K, MASKED>(v3, col_base + c3 * TC_CHUNK, nt, r);
-  } while (flags);
-  TC_PROF(r.p_pass2 += clock64() - c_p1;)
-#endif
 }
 
 // finds the work item that owns query tile `tile` (tile_begin is ascending; n_work >= 1)
@@ -707,7 +499,7 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   }
   TC_PROF(if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 5) && item < 3)
             printf("epi warp %d item %u: total %lld  wait acc_full %lld  tile work %lld (pass 2 %lld)  flagged %lld of %d chunks\n",
-                   warp, item, clock64() - p_t0, r.p_wait, r.p_pass1, r.p_pass2, r.p_nflag, n_t * (TC_HALF / TC_CHUNK));)
+                   warp, item, clock64() - p_t0, r.p_wait, r.p_pass1, r.p_pass2, r.p_nflag, n_t * (TC_HALF / 8));)
   // merge the two warpgroups' top-2 (disjoint train subsets) and write the row record
   uint2* slot = merge + (item & 1u) * TC_M;
   if (wg == 1) slot[row_in_tile] = make_uint2(r.m1, r.m2);
