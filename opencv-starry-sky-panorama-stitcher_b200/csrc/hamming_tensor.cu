@@ -314,14 +314,6 @@ __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_
 #endif
 constexpr int TC_GROUP = 16;   // columns per pass-1 group = 8 packed registers
 
-// Pass 1 on a 16-column group: does any column beat the packed threshold?  4 VIMNMX3 + compare.
-__device__ __forceinline__ bool tc_beats16(const uint32_t* p, uint32_t thrp) {
-  const uint32_t a = __vimax3_s16x2(p[0], p[1], p[2]);
-  const uint32_t b = __vimax3_s16x2(p[3], p[4], p[5]);
-  const uint32_t c = __vimax3_s16x2(p[6], p[7], thrp);
-  return __vimax3_s16x2(a, b, c) != thrp;
-}
-
 // packed key ((D & 0xFFF) << 4 | pos) of both halves, as tc_key64
 __device__ __forceinline__ uint32_t tc_key16(uint32_t p, uint32_t pos) {
 #if TC_QSCALE == 64
@@ -414,13 +406,24 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
     return;
   }
 #endif
-  uint32_t flags = 0;
+  // group maxima first (3 VIMNMX3 per 8 registers), then ONE test of the whole tile: in the steady
+  // state most tiles beat no row's threshold and the per-group tests are skipped
+  uint32_t gm[TC_HALF / TC_GROUP];
 #pragma unroll
-  for (int g = 0; g < TC_HALF / TC_GROUP; ++g) flags |= tc_beats16(p + 8 * g, thrp) ? (1u << g) : 0u;
+  for (int g = 0; g < TC_HALF / TC_GROUP; ++g) {
+    const uint32_t* q = p + 8 * g;
+    gm[g] = __vimax3_s16x2(__vimax3_s16x2(q[0], q[1], q[2]), __vimax3_s16x2(q[3], q[4], q[5]), __vmaxs2(q[6], q[7]));
+  }
+  const uint32_t all = __vimax3_s16x2(__vimax3_s16x2(gm[0], gm[1], gm[2]), __vimax3_s16x2(gm[3], gm[4], gm[5]),
+                                      __vimax3_s16x2(gm[6], gm[7], thrp));
 #if TC_EXPERIMENT == 2 || TC_EXPERIMENT == 3
-  if (flags == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
+  if (all == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
   return;
 #endif
+  if (!__any_sync(0xffffffffu, all != thrp)) return;
+  uint32_t flags = 0;
+#pragma unroll
+  for (int g = 0; g < TC_HALF / TC_GROUP; ++g) flags |= (__vmaxs2(gm[g], thrp) != thrp) ? (1u << g) : 0u;
   flags = __reduce_or_sync(0xffffffffu, flags);
   TC_PROF(r.p_nflag += 2 * __popc(flags);)
   TC_PROF(const long long c_p1 = clock64();)
