@@ -209,11 +209,31 @@ struct TcRow {
   uint32_t m1, m2;     // running best-2 as packed keys (hamming << 22 | train index)
   int thr;             // skip a chunk unless some D in it is > thr
   int pq;              // popcount of the query row: hamming = pq - D
-  uint16_t* my_slot;   // where this thread publishes the D of its own k-th best
+  uint16_t* my_slot;   // where this thread publishes the D of its own k-th best (tag | D + 512)
   uint32_t tag;        // (item & 63) << 10, marks published values of the current work item
   bool heavy;          // warp-uniform: skip the filter and run the full-tile tournament (thresholds settling)
   TC_PROF(long long p_wait; long long p_pass1; long long p_pass2; long long p_nflag;)
 };
+
+#ifndef TC_PEER_AGED
+#define TC_PEER_AGED 1   // a peer value seen two tiles ago needs no tie margin
+#endif
+// Publishes the D of this thread's k-th best after its best-2 changed (`kth` is not NONE).
+__device__ __forceinline__ void tc_publish(TcRow& r, uint32_t kth) {
+  const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
+  *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
+  r.thr = max(r.thr, d_own);
+}
+// Raises the threshold from what the other warpgroup published (it sees the other half of the
+// train rows): its k best rows precede every column of mine whose D is smaller.  `slack` = 1
+// demands a STRICTLY larger D, because the peer may be up to one tile ahead and its rows may
+// then have higher train indices than my columns (an equal D with a lower index must still be
+// seen).  A value already read two tiles ago comes from tiles before my current one -- the
+// peer cannot be more than one tile ahead of a tile I have released -- so it needs no margin;
+// for thresholds in the tail of the distance distribution that margin is ~50 % more flags.
+__device__ __forceinline__ void tc_peer_bound(TcRow& r, uint32_t pv, int slack) {
+  if ((pv & 0xFFFFFC00u) == r.tag) r.thr = max(r.thr, (int)(pv & 1023u) - 512 - slack);
+}
 
 // 128 consecutive TMEM columns of this thread's lane as 64 registers of two packed s16 values
 // (.pack::16b keeps the low 16 bits of each column: D is in [-256, 256]); register i holds columns
@@ -303,10 +323,7 @@ __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_
     r.m2 = min(min(r.m2, g2), max(r.m1, g1));   // g1 <= g2 and m1 <= m2
   }
   r.m1 = min(r.m1, g1);
-  const uint32_t kth = (K == 2) ? r.m2 : r.m1;   // never NONE here: the tile had 128 real columns
-  const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
-  *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
-  r.thr = max(r.thr, d_own);
+  tc_publish(r, (K == 2) ? r.m2 : r.m1);   // never NONE here: the tile had 128 real columns
 }
 
 #ifndef TC_FULL_MIN_G
@@ -370,11 +387,7 @@ __device__ __forceinline__ void tc_group_exact_packed(uint32_t (&q)[8], uint32_t
   }
   r.m1 = min(r.m1, g1);
   const uint32_t kth = (K == 2) ? r.m2 : r.m1;
-  if (kth != TC_KEY_NONE) {
-    const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
-    *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
-    r.thr = max(r.thr, d_own);
-  }
+  if (kth != TC_KEY_NONE) tc_publish(r, kth);
 }
 
 template <int K, bool MASKED>
@@ -481,14 +494,18 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   r.heavy = true;
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
   *r.my_slot = 0;
+  uint32_t pv1 = 0xFFFFFFFFu, pv2 = 0xFFFFFFFFu;   // peer values read one and two tiles ago (none yet)
   TC_PROF(r.p_wait = 0; r.p_pass1 = 0; r.p_pass2 = 0; r.p_nflag = 0; const long long p_t0 = clock64();)
   for (int t = 0; t < n_t; ++t, ++g) {
     const uint32_t buf = g % TC_ACC;
     TC_PROF(const long long c_w = clock64();)
-    // the other warpgroup's k-th best D bounds this row too; an equal D with a lower train index
-    // still has to be seen, hence the -1
     const uint32_t pv = *reinterpret_cast<const volatile uint16_t*>(peer_slot);
-    if ((pv & 0xFC00u) == r.tag) r.thr = max(r.thr, (int)(pv & 1023u) - 513);
+    tc_peer_bound(r, pv, 1);
+    if (TC_PEER_AGED) {
+      tc_peer_bound(r, wg ? pv1 : pv2, 0);   // wg 1's columns follow wg 0's of the same tile: one tile suffices
+      pv2 = pv1;
+      pv1 = pv;
+    }
     tc_wait(&acc_full[buf], (g / TC_ACC) & 1u);
     tc_fence_after();
     TC_PROF(const long long c_s = clock64(); r.p_wait += c_s - c_w;)
