@@ -55,6 +55,25 @@ def test_ragged_multi_pair_batch_against_oracle(engine, variant, mode):
     assert_result_equals(res, oracle_pairs(sets, pairs, mode))
 
 
+@pytest.mark.parametrize("mode", ["crosscheck", "knn2_ratio"])
+def test_tie_stress_over_many_train_tiles(engine, mode):
+    """Ties across MANY 256-row train tiles: the tensor variant's two warpgroups exchange
+    thresholds (with a tie margin that is dropped once a value is two tiles old), so equal
+    distances in neighbouring tiles and in the two halves of one tile all have to resolve to the
+    lowest train index."""
+    sizes = [8191, 7937, 8000]
+    tie = synth.tie_stress_bank(len(sizes), max(sizes), seed=11, dup_frac=0.3)
+    sets = [tie[i][:n] for i, n in enumerate(sizes)]
+    pairs = [(i, j) for i in range(3) for j in range(3) if i != j]
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs(pairs, mode=mode, variant="tensor", return_best2=(mode == "knn2_ratio"))
+    assert_result_equals(res, oracle_pairs(sets, pairs, mode))
+    if mode == "knn2_ratio":
+        for p, (a, b) in enumerate(pairs):
+            lo, hi = res.best2_offsets[p], res.best2_offsets[p + 1]
+            np.testing.assert_array_equal(res.best2[lo:hi], ho.knn2(sets[a], sets[b]))
+
+
 @pytest.mark.parametrize("variant", VARIANTS)
 def test_best2_records_against_oracle_with_planted_matches(engine, variant):
     sets = synth.descriptor_bank(3, 3000, seed=4, world=4000)
