@@ -54,6 +54,11 @@ struct HammingWork {
   int nt;
   long long out_row;  // first row of this item in the best2 scratch
   int qi, ti;         // image indices of q and t in the bank
+  // tensor variant only: a SPARSE query set.  slot_src[s] = query row held by slot s of the
+  // item's 128-slot query tiles, or -1 (s & 7 == row & 7, so rows keep their place in the
+  // 8-row swizzle pattern); q_tiles = number of such tiles.  NULL = all nq rows in order.
+  const int* slot_src = nullptr;
+  int q_tiles = 0;
 };
 
 // One image pair for the finalize kernels.
@@ -105,6 +110,7 @@ struct ssp_ctx {
   ssp::DevBuf h_expanded;  // int8 expansion of the bank for the tensor variant (swizzled tiles)
   ssp::DevBuf h_popc;      // popcount of every bank row (int32), tensor variant
   ssp::DevBuf h_tc_work, h_tc_err;
+  ssp::DevBuf h_cc_aux, h_cc_mark, h_cc_slots, h_cc_cls;  // sparse reverse pass of the cross-check
   bool h_expanded_valid = false;
   std::vector<long long> exp_byte_off;  // per image byte offset into h_expanded
   std::vector<int> exp_rows_pad;

@@ -14,6 +14,8 @@
 // (distance, lowest index) order OpenCV's stable insertion produces, so no tie handling is
 // needed anywhere.  Finalize kernels apply the ratio test / mutual-nearest test on the device
 // and compact the survivors in ascending query order.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace ssp {
@@ -163,6 +165,61 @@ __device__ __forceinline__ bool survives(const HammingPair& p, const int4* __res
   return best2[p.rev_row + rec.x].x == q;
 }
 
+// ---- cross-check, tensor variant: the reverse pass runs over the CLAIMED train rows only --------
+// A couple (q, t) survives the cross-check iff t is q's nearest neighbour and q is t's, so the
+// reverse direction is needed for exactly those rows of the train image that are somebody's
+// nearest neighbour (~63 % of them on unrelated descriptors).  cc_mark flags them from the forward
+// records, cc_slots lays them out as the sparse query tiles of HammingWork::slot_src.
+struct CrossAux {
+  long long fwd_row;    // forward best2 rows of the pair
+  long long mark_off;   // first mark byte of the pair (nt of them)
+  long long slot_off;   // first slot of the pair
+  int nq, nt;
+};
+
+__global__ void __launch_bounds__(256)
+cc_mark_kernel(const CrossAux* __restrict__ aux, const int4* __restrict__ best2, uint8_t* __restrict__ mark) {
+  const CrossAux a = aux[blockIdx.x];
+  for (int q = blockIdx.y * blockDim.x + threadIdx.x; q < a.nq; q += gridDim.y * blockDim.x) {
+    const int t = best2[a.fwd_row + q].x;
+    if (t >= 0) mark[a.mark_off + t] = 1;
+  }
+}
+
+// block (pair, c): the marked rows t = c (mod 8) in ascending order go to slots c, c + 8, c + 16, ...
+__global__ void __launch_bounds__(256)
+cc_slots_kernel(const CrossAux* __restrict__ aux, const uint8_t* __restrict__ mark, int* __restrict__ slots,
+                int* __restrict__ cls_count) {
+  const CrossAux a = aux[blockIdx.x];
+  const int c = blockIdx.y;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  __shared__ int warp_cnt[8];
+  __shared__ int run;
+  if (threadIdx.x == 0) run = 0;
+  __syncthreads();
+  const int n_c = (a.nt - c + 7) / 8;   // rows of this class
+  for (int base = 0; base < n_c; base += 256) {
+    const int i = base + threadIdx.x;
+    const int t = c + 8 * i;
+    const bool keep = (i < n_c) && mark[a.mark_off + t] != 0;
+    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) warp_cnt[wid] = __popc(ballot);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      const int n = warp_cnt[w];
+      before += (w < wid) ? n : 0;
+      total += n;
+    }
+    if (keep) slots[a.slot_off + (long long)(run + before + __popc(ballot & ((1u << lane) - 1u))) * 8 + c] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) run += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) cls_count[blockIdx.x * 8 + c] = run;
+}
+
 constexpr int FIN_THREADS = 512;
 
 __global__ void __launch_bounds__(FIN_THREADS)
@@ -281,7 +338,15 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
 
   // directed work items + per-pair finalize records
   const bool cross = (mode == SSP_MODE_CROSSCHECK);
-  std::vector<HammingWork> work;
+  // tensor variant: the reverse items of the cross-check wait for the forward ones and run over
+  // the claimed rows only (SSP_B200_CROSSCHECK_DENSE=1 keeps both directions in one dense launch)
+  static const bool dense_env = [] {
+    const char* e = getenv("SSP_B200_CROSSCHECK_DENSE");
+    return e && e[0] == '1';
+  }();
+  const bool sparse_rev = cross && !dense_env &&
+                          (variant == SSP_HAMMING_AUTO || variant == SSP_HAMMING_TENSOR);
+  std::vector<HammingWork> work, rev_work;
   std::vector<HammingPair> hp((size_t)n_pairs);
   work.reserve((size_t)n_pairs * (cross ? 2 : 1));
   const uint4* bank = reinterpret_cast<const uint4*>(ctx->d_desc);
@@ -335,7 +400,7 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
       r.ti = qi;
       hp[p].rev_row = rev_cursor;
       rev_cursor += nt;
-      if (nt > 0) work.push_back(r);
+      if (nt > 0) (sparse_rev ? rev_work : work).push_back(r);
       max_nq = nt > max_nq ? nt : max_nq;
     }
   }
@@ -353,6 +418,7 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
                                     ctx->stream));
 
   const int k = cross ? 1 : 2;
+  float rev_fwd_ms = 0.f;   // sparse cross-check: kernel time of the forward launch (ev0/ev1 then hold the reverse one)
   if (!work.empty()) {
     int v = variant;
     if (v == SSP_HAMMING_AUTO) v = SSP_HAMMING_TENSOR;   // fastest at every size measured
@@ -363,6 +429,59 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
       cudaError_t e = launch_hamming_tensor(ctx, work, k, &why);
       if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
       SSP_CUDA_TRY(ctx, e);
+      if (sparse_rev && !rev_work.empty()) {
+        float fwd_ms = 0.f;
+        SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&fwd_ms, ctx->ev0, ctx->ev1));  // the launch above has completed
+        // claimed train rows of every pair -> sparse query tiles of its reverse item
+        std::vector<CrossAux> aux((size_t)n_pairs);
+        long long marks = 0, slots = 0;
+        int max_q = 1;
+        for (int p = 0; p < n_pairs; ++p) {
+          aux[(size_t)p].fwd_row = hp[(size_t)p].fwd_row;
+          aux[(size_t)p].mark_off = marks;
+          aux[(size_t)p].slot_off = slots;
+          aux[(size_t)p].nq = hp[(size_t)p].nq;
+          aux[(size_t)p].nt = hp[(size_t)p].nt;
+          marks += hp[(size_t)p].nt;
+          slots += ((long long)hp[(size_t)p].nt + 127) / 128 * 128 + 256;
+          max_q = hp[(size_t)p].nq > max_q ? hp[(size_t)p].nq : max_q;
+        }
+        SSP_CUDA_TRY(ctx, ctx->h_cc_aux.ensure(aux.size() * sizeof(CrossAux)));
+        SSP_CUDA_TRY(ctx, ctx->h_cc_mark.ensure((size_t)marks + 1));
+        SSP_CUDA_TRY(ctx, ctx->h_cc_slots.ensure((size_t)slots * sizeof(int)));
+        SSP_CUDA_TRY(ctx, ctx->h_cc_cls.ensure((size_t)n_pairs * 8 * sizeof(int)));
+        SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_cc_aux.p, aux.data(), aux.size() * sizeof(CrossAux),
+                                          cudaMemcpyHostToDevice, ctx->stream));
+        SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_cc_mark.p, 0, (size_t)marks + 1, ctx->stream));
+        SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_cc_slots.p, 0xFF, (size_t)slots * sizeof(int), ctx->stream));
+        int by = (max_q + 255) / 256;
+        by = by > 64 ? 64 : by;
+        cc_mark_kernel<<<dim3((unsigned)n_pairs, (unsigned)by), 256, 0, ctx->stream>>>(
+            ctx->h_cc_aux.as<CrossAux>(), ctx->h_best2.as<int4>(), ctx->h_cc_mark.as<uint8_t>());
+        SSP_CUDA_TRY(ctx, cudaGetLastError());
+        cc_slots_kernel<<<dim3((unsigned)n_pairs, 8), 256, 0, ctx->stream>>>(
+            ctx->h_cc_aux.as<CrossAux>(), ctx->h_cc_mark.as<uint8_t>(), ctx->h_cc_slots.as<int>(),
+            ctx->h_cc_cls.as<int>());
+        SSP_CUDA_TRY(ctx, cudaGetLastError());
+        ctx->h_launches += 2;
+        std::vector<int> cls((size_t)n_pairs * 8);
+        SSP_CUDA_TRY(ctx, cudaMemcpyAsync(cls.data(), ctx->h_cc_cls.p, cls.size() * sizeof(int),
+                                          cudaMemcpyDeviceToHost, ctx->stream));
+        SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        size_t ri = 0;
+        for (int p = 0; p < n_pairs; ++p) {
+          if (hp[(size_t)p].nt <= 0) continue;   // no reverse item was made for this pair
+          HammingWork& r = rev_work[ri++];
+          int most = 0;
+          for (int c = 0; c < 8; ++c) most = cls[(size_t)p * 8 + c] > most ? cls[(size_t)p * 8 + c] : most;
+          r.slot_src = ctx->h_cc_slots.as<int>() + aux[(size_t)p].slot_off;
+          r.q_tiles = (most + 15) / 16;   // 16 slots of every class per 128-slot tile
+        }
+        e = launch_hamming_tensor(ctx, rev_work, k, &why);
+        if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
+        SSP_CUDA_TRY(ctx, e);
+        rev_fwd_ms = fwd_ms;
+      }
     } else {
       SSP_CUDA_TRY(ctx, ctx->h_work.ensure(work.size() * sizeof(HammingWork)));
       SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_work.p, work.data(),
@@ -404,6 +523,7 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
   ctx->h_launches += 1;
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   if (!work.empty()) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->h_main_ms, ctx->ev0, ctx->ev1));
+  ctx->h_main_ms += rev_fwd_ms;
   for (int p = 0; p <= n_pairs; ++p) match_offsets[p] = ctx->h_match_offsets[(size_t)p];
   ctx->h_n_matches = total;
   return SSP_OK;

@@ -90,6 +90,7 @@ struct TcWork {              // one directed image pair
   int nq, nt;
   int q_rows_pad, t_rows_pad;
   long long out_row;         // first best2 row of this item
+  const int* slot_src;       // sparse query set (HammingWork::slot_src) or NULL
   int tile_begin;            // prefix sum of query tiles over the work list
   int pad_;
 };
@@ -221,7 +222,9 @@ struct TcRow {
 // Publishes the D of this thread's k-th best after its best-2 changed (`kth` is not NONE).
 __device__ __forceinline__ void tc_publish(TcRow& r, uint32_t kth) {
   const int d_own = r.pq - (int)(kth >> TC_KEY_SHIFT);
-  *r.my_slot = (uint16_t)(r.tag | (uint32_t)(d_own + 512));
+  // masked: an empty slot of a sparse tile computes on stale operands, and its out-of-range D
+  // must not spill into the tag (the peer would take it for a value of the NEXT work item)
+  *r.my_slot = (uint16_t)(r.tag | ((uint32_t)(d_own + 512) & 1023u));
   r.thr = max(r.thr, d_own);
 }
 // Raises the threshold from what the other warpgroup published (it sees the other half of the
@@ -483,12 +486,15 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   const int row_in_tile = (warp & 3) * 32 + lane;
   const uint32_t taddr0 = tmem_base + wg * TC_HALF + ((uint32_t)((warp & 3) * 32) << 16);
   const int n_t = (w.nt + TC_N - 1) / TC_N;
-  const int row = q_tile * TC_M + row_in_tile;
+  // the query row held by this thread's TMEM lane: rows in order, or whatever the slot list says
+  const int q_slot = q_tile * TC_M + row_in_tile;
+  const int row = w.slot_src ? w.slot_src[q_slot] : (q_slot < w.nq ? q_slot : -1);
   TcRow r;
   r.m1 = TC_KEY_NONE;
   r.m2 = TC_KEY_NONE;
-  r.thr = TC_THR_NONE;
-  r.pq = (row < w.nq) ? w.q_popc[row] : 0;
+  // an empty slot of a sparse tile holds stale operands: no D ever beats its threshold
+  r.thr = (w.slot_src && row < 0) ? 511 : TC_THR_NONE;
+  r.pq = (row >= 0) ? w.q_popc[row] : 0;
   r.my_slot = share + wg * TC_M + row_in_tile;
   r.tag = (item & 63u) << 10;
   r.heavy = true;
@@ -528,7 +534,7 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
     const uint2 o = slot[row_in_tile];
     const uint32_t lo = min(r.m1, o.x);
     const uint32_t hi = min(max(r.m1, o.x), min(r.m2, o.y));
-    if (row < w.nq) {
+    if (row >= 0) {
       int4 out;
       out.x = (lo == TC_KEY_NONE) ? -1 : (int)(lo & TC_KEY_IDX_MASK);
       out.y = (lo == TC_KEY_NONE) ? -1 : (int)(lo >> TC_KEY_SHIFT);
@@ -595,16 +601,42 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
 
   if (warp == 8) {
     // ===== TMA producer =====
-    if (lane == 0) {
-      uint32_t g = 0, item = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
-        const TcWork w = work[tc_find_work(work, n_work, tile)];
-        const int q_tile = tile - w.tile_begin;
-        if (item > 0) tc_wait(a_empty, (item - 1) & 1u);
-        mbar_arrive_expect_tx(a_full, TC_A_BYTES);
-        tma_bulk_g2s(sA, w.q_exp + (size_t)q_tile * (TC_M * 128), TC_M * 128, a_full);
-        tma_bulk_g2s(sA + TC_M * 128, w.q_exp + (size_t)w.q_rows_pad * 128 + (size_t)q_tile * (TC_M * 128),
-                     TC_M * 128, a_full);
+    // Lane 0 runs the pipeline; the other lanes only help to GATHER the query tile of a sparse
+    // item (128 slots -> up to 256 row copies of 128 bytes, four slots per lane).
+    uint32_t g = 0, item = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
+      const TcWork w = work[tc_find_work(work, n_work, tile)];
+      const int q_tile = tile - w.tile_begin;
+      if (lane == 0 && item > 0) tc_wait(a_empty, (item - 1) & 1u);
+      __syncwarp();
+      if (w.slot_src == nullptr) {
+        if (lane == 0) {
+          mbar_arrive_expect_tx(a_full, TC_A_BYTES);
+          tma_bulk_g2s(sA, w.q_exp + (size_t)q_tile * (TC_M * 128), TC_M * 128, a_full);
+          tma_bulk_g2s(sA + TC_M * 128, w.q_exp + (size_t)w.q_rows_pad * 128 + (size_t)q_tile * (TC_M * 128),
+                       TC_M * 128, a_full);
+        }
+      } else {
+        int src[TC_M / 32];
+        int n_valid = 0;
+#pragma unroll
+        for (int j = 0; j < TC_M / 32; ++j) {
+          src[j] = w.slot_src[(size_t)q_tile * TC_M + lane + 32 * j];
+          n_valid += src[j] >= 0 ? 1 : 0;
+        }
+        n_valid = __reduce_add_sync(0xffffffffu, n_valid);
+        if (lane == 0) mbar_arrive_expect_tx(a_full, (uint32_t)n_valid * TC_ROW_BYTES);
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < TC_M / 32; ++j) {
+          if (src[j] < 0) continue;   // the slot keeps stale operands; its results are never written
+          const int slot = lane + 32 * j;
+          tma_bulk_g2s(sA + (size_t)slot * 128, w.q_exp + (size_t)src[j] * 128, 128, a_full);
+          tma_bulk_g2s(sA + TC_M * 128 + (size_t)slot * 128,
+                       w.q_exp + (size_t)w.q_rows_pad * 128 + (size_t)src[j] * 128, 128, a_full);
+        }
+      }
+      if (lane == 0) {
         const int n_t = (w.nt + TC_N - 1) / TC_N;
         for (int t = 0; t < n_t; ++t, ++g) {
           const uint32_t s = g % TC_STAGES;
@@ -617,6 +649,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
                        TC_N * 128, &b_full[s]);
         }
       }
+      __syncwarp();
     }
   } else if (warp == 9) {
     // ===== MMA issuer =====
@@ -768,9 +801,12 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
     t.q_rows_pad = ctx->exp_rows_pad[w.qi];
     t.t_rows_pad = ctx->exp_rows_pad[w.ti];
     t.out_row = w.out_row;
+    t.slot_src = w.slot_src;
     t.tile_begin = total;
     t.pad_ = 0;
-    total += (w.nq + TC_M - 1) / TC_M;
+    const int tiles = w.slot_src ? w.q_tiles : (w.nq + TC_M - 1) / TC_M;
+    if (tiles <= 0) continue;
+    total += tiles;
     tw.push_back(t);
   }
   if (tw.empty()) {

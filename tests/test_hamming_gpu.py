@@ -74,6 +74,20 @@ def test_tie_stress_over_many_train_tiles(engine, mode):
             np.testing.assert_array_equal(res.best2[lo:hi], ho.knn2(sets[a], sets[b]))
 
 
+def test_crosscheck_sparse_reverse_pass_many_items_per_block(engine):
+    """The tensor variant runs the reverse direction of the cross-check over the CLAIMED train
+    rows only (sparse query tiles, gathered row by row).  42 ordered pairs of 6 000 rows give
+    every thread block several work items in a row, tail tiles with empty slots included; twice,
+    because the hazards of this path are timing-dependent."""
+    sets = synth.descriptor_bank(7, 6000, seed=5, world=20_000)
+    pairs = [(i, j) for i in range(7) for j in range(7) if i != j]
+    engine.upload_descriptor_bank(sets)
+    expected = oracle_pairs(sets, pairs, "crosscheck")
+    for _ in range(2):
+        assert_result_equals(engine.hamming_match_pairs(pairs, mode="crosscheck"), expected)
+    assert_result_equals(engine.hamming_match_pairs(pairs, mode="crosscheck", variant="popc_csa"), expected)
+
+
 @pytest.mark.parametrize("variant", VARIANTS)
 def test_best2_records_against_oracle_with_planted_matches(engine, variant):
     sets = synth.descriptor_bank(3, 3000, seed=4, world=4000)
