@@ -46,6 +46,9 @@ struct DevBuf {
   }
 };
 
+constexpr int SSP_SLOT_DIST_SHIFT = 20;
+constexpr int SSP_SLOT_ROW_MASK = (1 << SSP_SLOT_DIST_SHIFT) - 1;
+
 // One directed Hamming work item: every row of `q` against every row of `t`.
 struct HammingWork {
   const uint4* q;    // nq rows x 32 B
@@ -56,7 +59,8 @@ struct HammingWork {
   int qi, ti;         // image indices of q and t in the bank
   // tensor variant only: a SPARSE query set.  slot_src[s] = query row held by slot s of the
   // item's 128-slot query tiles, or -1 (s & 7 == row & 7, so rows keep their place in the
-  // 8-row swizzle pattern); q_tiles = number of such tiles.  NULL = all nq rows in order.
+  // 8-row swizzle pattern), with an upper bound of the row's nearest-neighbour distance in
+  // the bits from SSP_SLOT_DIST_SHIFT up; q_tiles = number of such tiles.  NULL = all nq rows in order.
   const int* slot_src = nullptr;
   int q_tiles = 0;
 };

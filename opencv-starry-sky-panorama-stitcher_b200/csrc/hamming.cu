@@ -177,18 +177,21 @@ struct CrossAux {
   int nq, nt;
 };
 
+// mark[t] = smallest distance at which some query row claims train row t (CC_UNCLAIMED if none):
+// the reverse search of t cannot end above it, so it starts with that threshold already settled.
+constexpr int CC_UNCLAIMED = 0x7F7F7F7F;   // what cudaMemset(0x7F) leaves
 __global__ void __launch_bounds__(256)
-cc_mark_kernel(const CrossAux* __restrict__ aux, const int4* __restrict__ best2, uint8_t* __restrict__ mark) {
+cc_mark_kernel(const CrossAux* __restrict__ aux, const int4* __restrict__ best2, int* __restrict__ mark) {
   const CrossAux a = aux[blockIdx.x];
   for (int q = blockIdx.y * blockDim.x + threadIdx.x; q < a.nq; q += gridDim.y * blockDim.x) {
-    const int t = best2[a.fwd_row + q].x;
-    if (t >= 0) mark[a.mark_off + t] = 1;
+    const int4 rec = best2[a.fwd_row + q];
+    if (rec.x >= 0) atomicMin(&mark[a.mark_off + rec.x], rec.y);
   }
 }
 
 // block (pair, c): the marked rows t = c (mod 8) in ascending order go to slots c, c + 8, c + 16, ...
 __global__ void __launch_bounds__(256)
-cc_slots_kernel(const CrossAux* __restrict__ aux, const uint8_t* __restrict__ mark, int* __restrict__ slots,
+cc_slots_kernel(const CrossAux* __restrict__ aux, const int* __restrict__ mark, int* __restrict__ slots,
                 int* __restrict__ cls_count) {
   const CrossAux a = aux[blockIdx.x];
   const int c = blockIdx.y;
@@ -201,7 +204,8 @@ cc_slots_kernel(const CrossAux* __restrict__ aux, const uint8_t* __restrict__ ma
   for (int base = 0; base < n_c; base += 256) {
     const int i = base + threadIdx.x;
     const int t = c + 8 * i;
-    const bool keep = (i < n_c) && mark[a.mark_off + t] != 0;
+    const int claimed = (i < n_c) ? mark[a.mark_off + t] : CC_UNCLAIMED;
+    const bool keep = claimed != CC_UNCLAIMED;
     const unsigned ballot = __ballot_sync(0xffffffffu, keep);
     if (lane == 0) warp_cnt[wid] = __popc(ballot);
     __syncthreads();
@@ -212,7 +216,10 @@ cc_slots_kernel(const CrossAux* __restrict__ aux, const uint8_t* __restrict__ ma
       before += (w < wid) ? n : 0;
       total += n;
     }
-    if (keep) slots[a.slot_off + (long long)(run + before + __popc(ballot & ((1u << lane) - 1u))) * 8 + c] = t;
+    // slot value: row | claimed distance << SSP_SLOT_DIST_SHIFT (rows < 2^18, distances <= 256)
+    if (keep)
+      slots[a.slot_off + (long long)(run + before + __popc(ballot & ((1u << lane) - 1u))) * 8 + c] =
+          t | (claimed << SSP_SLOT_DIST_SHIFT);
     __syncthreads();
     if (threadIdx.x == 0) run += total;
     __syncthreads();
@@ -447,20 +454,20 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
           max_q = hp[(size_t)p].nq > max_q ? hp[(size_t)p].nq : max_q;
         }
         SSP_CUDA_TRY(ctx, ctx->h_cc_aux.ensure(aux.size() * sizeof(CrossAux)));
-        SSP_CUDA_TRY(ctx, ctx->h_cc_mark.ensure((size_t)marks + 1));
+        SSP_CUDA_TRY(ctx, ctx->h_cc_mark.ensure(((size_t)marks + 1) * sizeof(int)));
         SSP_CUDA_TRY(ctx, ctx->h_cc_slots.ensure((size_t)slots * sizeof(int)));
         SSP_CUDA_TRY(ctx, ctx->h_cc_cls.ensure((size_t)n_pairs * 8 * sizeof(int)));
         SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_cc_aux.p, aux.data(), aux.size() * sizeof(CrossAux),
                                           cudaMemcpyHostToDevice, ctx->stream));
-        SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_cc_mark.p, 0, (size_t)marks + 1, ctx->stream));
+        SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_cc_mark.p, 0x7F, ((size_t)marks + 1) * sizeof(int), ctx->stream));
         SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_cc_slots.p, 0xFF, (size_t)slots * sizeof(int), ctx->stream));
         int by = (max_q + 255) / 256;
         by = by > 64 ? 64 : by;
         cc_mark_kernel<<<dim3((unsigned)n_pairs, (unsigned)by), 256, 0, ctx->stream>>>(
-            ctx->h_cc_aux.as<CrossAux>(), ctx->h_best2.as<int4>(), ctx->h_cc_mark.as<uint8_t>());
+            ctx->h_cc_aux.as<CrossAux>(), ctx->h_best2.as<int4>(), ctx->h_cc_mark.as<int>());
         SSP_CUDA_TRY(ctx, cudaGetLastError());
         cc_slots_kernel<<<dim3((unsigned)n_pairs, 8), 256, 0, ctx->stream>>>(
-            ctx->h_cc_aux.as<CrossAux>(), ctx->h_cc_mark.as<uint8_t>(), ctx->h_cc_slots.as<int>(),
+            ctx->h_cc_aux.as<CrossAux>(), ctx->h_cc_mark.as<int>(), ctx->h_cc_slots.as<int>(),
             ctx->h_cc_cls.as<int>());
         SSP_CUDA_TRY(ctx, cudaGetLastError());
         ctx->h_launches += 2;

@@ -488,16 +488,20 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   const int n_t = (w.nt + TC_N - 1) / TC_N;
   // the query row held by this thread's TMEM lane: rows in order, or whatever the slot list says
   const int q_slot = q_tile * TC_M + row_in_tile;
-  const int row = w.slot_src ? w.slot_src[q_slot] : (q_slot < w.nq ? q_slot : -1);
+  const int sv = w.slot_src ? w.slot_src[q_slot] : (q_slot < w.nq ? q_slot : -1);
+  const int row = sv < 0 ? -1 : (sv & SSP_SLOT_ROW_MASK);
   TcRow r;
   r.m1 = TC_KEY_NONE;
   r.m2 = TC_KEY_NONE;
-  // an empty slot of a sparse tile holds stale operands: no D ever beats its threshold
-  r.thr = (w.slot_src && row < 0) ? 511 : TC_THR_NONE;
   r.pq = (row >= 0) ? w.q_popc[row] : 0;
+  // Sparse items come with an upper bound of every row's nearest distance (K = 1: the distance at
+  // which the row was claimed), i.e. with settled thresholds: only columns at least that near
+  // are looked at, and the unfiltered start-up mode is skipped.  An empty slot holds stale
+  // operands: no D ever beats its threshold.
+  r.thr = !w.slot_src ? TC_THR_NONE : (row < 0 ? 511 : r.pq - (sv >> SSP_SLOT_DIST_SHIFT) - 1);
   r.my_slot = share + wg * TC_M + row_in_tile;
   r.tag = (item & 63u) << 10;
-  r.heavy = true;
+  r.heavy = (w.slot_src == nullptr);
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
   *r.my_slot = 0;
   uint32_t pv1 = 0xFFFFFFFFu, pv2 = 0xFFFFFFFFu;   // peer values read one and two tiles ago (none yet)
@@ -631,9 +635,10 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
         for (int j = 0; j < TC_M / 32; ++j) {
           if (src[j] < 0) continue;   // the slot keeps stale operands; its results are never written
           const int slot = lane + 32 * j;
-          tma_bulk_g2s(sA + (size_t)slot * 128, w.q_exp + (size_t)src[j] * 128, 128, a_full);
-          tma_bulk_g2s(sA + TC_M * 128 + (size_t)slot * 128,
-                       w.q_exp + (size_t)w.q_rows_pad * 128 + (size_t)src[j] * 128, 128, a_full);
+          const size_t row = (size_t)(src[j] & SSP_SLOT_ROW_MASK);
+          tma_bulk_g2s(sA + (size_t)slot * 128, w.q_exp + row * 128, 128, a_full);
+          tma_bulk_g2s(sA + TC_M * 128 + (size_t)slot * 128, w.q_exp + (size_t)w.q_rows_pad * 128 + row * 128,
+                       128, a_full);
         }
       }
       if (lane == 0) {
