@@ -117,6 +117,8 @@ int ssp_bind_descriptor_bank(ssp_ctx* ctx, const uint8_t* d_desc, const int64_t*
  *       would raise; the Python layer raises ValueError for that case).
  *   SSP_MODE_CROSSCHECK : (q, t) survives iff t = argmin_t D[q,.] and q = argmin_q D[.,t],
  *       both with the lowest index on ties (OpenCV batchDistance crosscheck semantics).
+ *       The tensor variant searches the reverse direction only for the train rows some query
+ *       row claims (same result; environment SSP_B200_CROSSCHECK_DENSE=1 searches all of them).
  *
  * Survivors of pair p are reported in ascending query index (OpenCV's order) at positions
  * [match_offsets[p], match_offsets[p+1]) of the arrays ssp_hamming_fetch_matches returns.
