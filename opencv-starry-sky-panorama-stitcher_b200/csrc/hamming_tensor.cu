@@ -51,6 +51,9 @@ namespace ssp {
 #ifndef TC_EXPERIMENT
 #define TC_EXPERIMENT 0   // 1..3: bottleneck probes (tools/tc_bottleneck.sh), results are wrong
 #endif
+#ifndef TC_GATHER_ROWS
+#define TC_GATHER_ROWS 8   // rows a lane of the producer warp has in flight while it gathers a sparse query tile (x 2 K halves)
+#endif
 #ifndef TC_PROFILE
 #define TC_PROFILE 0      // 1: block 0 prints where its MMA thread and one epilogue warp spend cycles
 #endif
@@ -606,7 +609,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
   if (warp == 8) {
     // ===== TMA producer =====
     // Lane 0 runs the pipeline; the other lanes only help to GATHER the query tile of a sparse
-    // item (128 slots -> up to 256 row copies of 128 bytes, four slots per lane).
+    // item.
     uint32_t g = 0, item = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
       const TcWork w = work[tc_find_work(work, n_work, tile)];
@@ -621,25 +624,37 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
                        TC_M * 128, a_full);
         }
       } else {
-        int src[TC_M / 32];
-        int n_valid = 0;
+        // Sparse tile: the warp copies the claimed rows itself (LDG.128 -> STS.128, 16 in flight
+        // per lane; eight lanes cover one 128-byte row segment).  256 bulk copies of 128 bytes
+        // took ~26 k cycles per tile on the TMA unit, this takes a few thousand.  The rows are
+        // written through the generic proxy and read by the tensor core through the async
+        // proxy: every writing lane fences (fence.proxy.async) before lane 0 arrives.
+        const int* slots = w.slot_src + (size_t)q_tile * TC_M;
+        const int chunk = lane & 7;
+#pragma unroll 1
+        for (int base = 0; base < TC_M; base += 4 * TC_GATHER_ROWS) {
+          int sv[TC_GATHER_ROWS];
 #pragma unroll
-        for (int j = 0; j < TC_M / 32; ++j) {
-          src[j] = w.slot_src[(size_t)q_tile * TC_M + lane + 32 * j];
-          n_valid += src[j] >= 0 ? 1 : 0;
+          for (int k = 0; k < TC_GATHER_ROWS; ++k) sv[k] = slots[base + 4 * k + (lane >> 3)];
+          uint4 v[TC_GATHER_ROWS][2];
+#pragma unroll
+          for (int k = 0; k < TC_GATHER_ROWS; ++k) {
+            if (sv[k] < 0) continue;   // the slot keeps stale operands; its results are never written
+            const uint8_t* srow = w.q_exp + (size_t)(sv[k] & SSP_SLOT_ROW_MASK) * 128 + chunk * 16;
+            v[k][0] = *reinterpret_cast<const uint4*>(srow);
+            v[k][1] = *reinterpret_cast<const uint4*>(srow + (size_t)w.q_rows_pad * 128);
+          }
+#pragma unroll
+          for (int k = 0; k < TC_GATHER_ROWS; ++k) {
+            if (sv[k] < 0) continue;
+            uint8_t* drow = sA + (size_t)(base + 4 * k + (lane >> 3)) * 128 + chunk * 16;
+            *reinterpret_cast<uint4*>(drow) = v[k][0];
+            *reinterpret_cast<uint4*>(drow + TC_M * 128) = v[k][1];
+          }
         }
-        n_valid = __reduce_add_sync(0xffffffffu, n_valid);
-        if (lane == 0) mbar_arrive_expect_tx(a_full, (uint32_t)n_valid * TC_ROW_BYTES);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
-#pragma unroll
-        for (int j = 0; j < TC_M / 32; ++j) {
-          if (src[j] < 0) continue;   // the slot keeps stale operands; its results are never written
-          const int slot = lane + 32 * j;
-          const size_t row = (size_t)(src[j] & SSP_SLOT_ROW_MASK);
-          tma_bulk_g2s(sA + (size_t)slot * 128, w.q_exp + row * 128, 128, a_full);
-          tma_bulk_g2s(sA + TC_M * 128 + (size_t)slot * 128, w.q_exp + (size_t)w.q_rows_pad * 128 + row * 128,
-                       128, a_full);
-        }
+        if (lane == 0) mbar_arrive(a_full);
       }
       if (lane == 0) {
         const int n_t = (w.nt + TC_N - 1) / TC_N;
