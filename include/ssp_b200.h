@@ -50,7 +50,7 @@ extern "C" {
 #define SSP_HAMMING_AUTO 0
 #define SSP_HAMMING_POPC 1     /* LOP3 + POPC CUDA-core kernel, TMA-bulk staged train tiles         */
 #define SSP_HAMMING_POPC_CSA 2 /* same, carry-save-adder compression before POPC (4 POPC/compare)   */
-#define SSP_HAMMING_TENSOR 3   /* tcgen05 kind::i8 contraction on int8-expanded descriptors (+-1 query x
+#define SSP_HAMMING_TENSOR 3   /* tcgen05 kind::i8 contraction on int8-expanded descriptors (-+64 query x
                                   0/1 train), accumulators in TMEM; what SSP_HAMMING_AUTO selects   */
 
 /* polygon compare options */

@@ -87,7 +87,7 @@ constexpr int TC_THR_NONE = -100000;         // "no k-th neighbour yet"
 constexpr int TC_TAIL_BYTES = 256 + 2 * TC_M * (int)sizeof(uint2) + 2 * TC_M * (int)sizeof(uint16_t);
 
 struct TcWork {              // one directed image pair
-  const uint8_t* q_exp;      // query image, +-1 encoding
+  const uint8_t* q_exp;      // query image, -+64 encoding
   const uint8_t* t_exp;      // train image, 0/1 encoding
   const int* q_popc;         // popcount of every query row
   int nq, nt;
