@@ -60,7 +60,12 @@ class _Session:
         xy_l = [self.star_xy.get(i, np.zeros((0, 2))) for i in range(n)]
         br_l = [self.star_brightness.get(i, np.zeros(0)) for i in range(n)]
         w, h, f = self.shape_focal
-        self.engine.upload_star_bank(xy_l, br_l, w, h, f)
+        self.engine.upload_star_bank(xy_l, br_l, w, h, f, owner=self)
+
+    def resident(self, img_id):
+        """True while the engine still holds THIS session's polygon bank of `img_id` (another
+        polygon_data_store on the same context may have measured its own image of that id)."""
+        return img_id in self.on_device and self.engine.poly_owner.get(img_id) is self
 
 
 class BFPolygonMatcher:
@@ -230,7 +235,7 @@ class BFPolygonMatcher:
                 cands.append(tpl)
         cand_arr = np.array(cands, dtype=np.int32).reshape(-1, 5)
         eng = sess.engine
-        eng.polygon_measure(img_id, cand_arr, min_side_px=float(self.MIN_SIDE_PX))
+        eng.polygon_measure(img_id, cand_arr, min_side_px=float(self.MIN_SIDE_PX), owner=sess)
         sess.on_device.add(img_id)
         got = eng.polygon_fetch(img_id, raw=True)
         idx = got["star_idx"].astype(np.int64)
@@ -248,12 +253,13 @@ class BFPolygonMatcher:
     def _prepare_image(self, sess, store, counter, img_id, keypoints, n_orb, img, filename, title):
         if img_id in store:
             entry = store[img_id]
-            if img_id not in sess.on_device:
-                # polygon data computed elsewhere (e.g. a resumed store): load it into the engine
+            if not sess.resident(img_id):
+                # polygon data computed elsewhere (a resumed store), or the bank of this image id
+                # was replaced by another store sharing the context: load it into the engine
                 p = entry["polygons_from_ftX"]
                 feat = np.concatenate([p["keypoint_angles_rotated_list"], p["side_lengths_rotated_list"],
                                        p["keypoint_brightnesses_rotated_list"]], axis=1)
-                sess.engine.polygon_upload_features(img_id, feat, p["keypoint_indices_rotated_list"])
+                sess.engine.polygon_upload_features(img_id, feat, p["keypoint_indices_rotated_list"], owner=sess)
                 sess.on_device.add(img_id)
             return entry
         counter.append(img_id)

@@ -25,7 +25,7 @@ from collections import defaultdict
 import cv2 as cv
 import numpy as np
 
-from .bf_matcher import as_descriptor_array, dmatches_from_arrays, shared_engine
+from .bf_matcher import as_descriptor_array, dmatches_from_arrays
 from .custom_bf_polygon_matcher import BFPolygonMatcher, _debug_images_enabled
 from .engine import Engine
 
@@ -68,13 +68,15 @@ class CustomBruteForceMatcher:
         self.polygon_data_store = dict()
         self.fts_calculated_counter = list()
         self.focal_length_pinhole = focal_length_pinhole
-        # engine side
-        self.engine = engine if engine is not None else shared_engine()
+        # engine side: one context per matcher instance (it replaces the per-matcher state of
+        # custom_bruteforce_matcher.py:57-59) unless the caller shares one on purpose; a shared
+        # context is safe too, see `_upload_descriptor_bank`
+        self.engine = engine if engine is not None else Engine()
         self.hamming_mode = hamming_mode
         self.hamming_variant = hamming_variant
         self.write_debug_images = _debug_images_enabled(write_debug_images)
         self.verbose = verbose
-        self._bank_ready = False
+        self._bank_generation = None  # Engine.bank_generation of MY upload
         self._orb_matches = dict()  # (src, dst) -> tuple of cv2.DMatch, filled by prefetch
 
     def _log(self, *a):
@@ -99,14 +101,15 @@ class CustomBruteForceMatcher:
 
     # ---- kernel 1 in front of the pair loop -----------------------------------------------
     def _upload_descriptor_bank(self):
-        if self._bank_ready:
+        # somebody else (another matcher, the BFMatcher drop-in) may have replaced the bank of a
+        # shared context since my upload: the generation token tells
+        if self._bank_generation is not None and self._bank_generation == self.engine.bank_generation:
             return
         rows = []
         for ft, n_orb in zip(self.imgs_features_orb_and_stars, self.imgs_features_len_orb):
             d = as_descriptor_array(ft.descriptors)
             rows.append(d[0:n_orb, :])  # ORB rows only, star descriptors are ignored (Q3, :197-198)
-        self.engine.upload_descriptor_bank(rows)
-        self._bank_ready = True
+        self._bank_generation = self.engine.upload_descriptor_bank(rows)
 
     def prefetch_hamming_matches(self, pairs):
         """One engine call for a whole list of (src, dst) pairs; results are cached as DMatch

@@ -91,6 +91,12 @@ class Engine:
         self._desc_offsets = None
         self._star_offsets = None
         self._bound = None  # keeps a bound torch tensor alive
+        # Who owns what on this context.  Host mirrors that cache "my bank is uploaded" compare these
+        # with what they remember before every call and upload again on a mismatch, so that two
+        # matchers (or a matcher and the BFMatcher drop-in) can share one context safely.
+        self.bank_generation = 0   # bumped by every descriptor-bank upload / bind
+        self.star_owner = None     # whoever uploaded the current star bank
+        self.poly_owner = {}       # image id -> whoever measured / uploaded that polygon bank
         self._pinned = {}   # tag -> (address, bytes): engine-owned page-locked result buffers
         if stream is not None:
             self.set_stream(stream)
@@ -187,6 +193,8 @@ class Engine:
         self.synchronize()  # `bank` may be a temporary
         self._desc_offsets = offs.copy()
         self._bound = None
+        self.bank_generation += 1
+        return self.bank_generation
 
     def bind_descriptor_bank(self, device_ptr: int, row_offsets, keepalive=None):
         """Zero-copy: the bank already lives on this device (e.g. a torch uint8 tensor);
@@ -196,6 +204,8 @@ class Engine:
                                                        _ptr(offs), len(offs) - 1))
         self._desc_offsets = offs.copy()
         self._bound = keepalive
+        self.bank_generation += 1
+        return self.bank_generation
 
     # -- kernel 1 -------------------------------------------------------------------------
     def hamming_match_pairs(self, pairs, mode="crosscheck", ratio=0.75, variant="auto",
@@ -252,7 +262,7 @@ class Engine:
 
     # -- kernel 2 -------------------------------------------------------------------------
     def upload_star_bank(self, xy: Sequence[np.ndarray], brightness: Sequence[np.ndarray],
-                         img_w: int, img_h: int, focal_px: float):
+                         img_w: int, img_h: int, focal_px: float, owner=None):
         """`xy[i]`: (n_i, 2) pixel coordinates of image i's stars (keypoints[n_orb:], cbpm:710);
         `brightness[i]`: (n_i,) get_star_brightness values.  img_w/img_h = work image size."""
         offs = np.zeros(len(xy) + 1, dtype=np.int64)
@@ -271,6 +281,7 @@ class Engine:
                                                    float(focal_px), N.MEM_HOST))
         self.synchronize()
         self._star_offsets = offs
+        self.star_owner = owner
 
     def star_rays(self):
         n = int(self._star_offsets[-1])
@@ -279,12 +290,13 @@ class Engine:
         return rays
 
     def polygon_measure(self, image: int, candidates, min_side_px: float = 5.0,
-                        return_status: bool = False):
+                        return_status: bool = False, owner=None):
         """Measures candidate 5-star polygons of one image (cbpm:500-600 + :722-740) into the
         engine's polygon bank.  Returns n_valid (and the per-candidate status)."""
         cand = np.ascontiguousarray(np.asarray(candidates, dtype=np.int32).reshape(-1, 5))
         status = np.empty(cand.shape[0], dtype=np.uint8) if return_status else None
         n_valid = ctypes.c_int64()
+        self.poly_owner[int(image)] = owner
         self._check(self._lib.ssp_polygon_measure(self._ctx, int(image), _ptr(cand), cand.shape[0],
                                                   float(min_side_px), N.MEM_HOST, _ptr(status),
                                                   ctypes.byref(n_valid)))
@@ -296,6 +308,7 @@ class Engine:
         wait=False does not wait for the device (measure a batch of images back to back); the
         count is then available from `polygon_count` and returned as None here."""
         n_valid = ctypes.c_int64()
+        self.poly_owner[int(image)] = None
         self._check(self._lib.ssp_polygon_measure(self._ctx, int(image), ctypes.c_void_p(device_ptr),
                                                   int(n_candidates), float(min_side_px), N.MEM_DEVICE,
                                                   None, ctypes.byref(n_valid) if wait else None))
@@ -318,7 +331,8 @@ class Engine:
             _ptr(out.get("brightness")), _ptr(out["feat"]), n, N.MEM_HOST))
         return out
 
-    def polygon_upload_features(self, image: int, feat, star_idx=None):
+    def polygon_upload_features(self, image: int, feat, star_idx=None, owner=None):
+        self.poly_owner[int(image)] = owner
         f = np.ascontiguousarray(np.asarray(feat, dtype=np.float64).reshape(-1, 15))
         s = None
         if star_idx is not None:

@@ -16,6 +16,20 @@ Run in the build container only (needs /root/reference):   python tests/golden/m
   eisenberg_c2.npz         BASELINE config 2 on the 4 eisenberg frames the reference ships: stars
                            from the unchanged compute_star_features, DMatches and polygon banks
                            of the unchanged BFPolygonMatcher.match for all 6 pairs.
+  reference_matchesinfo_c1_full.npz   the same for ALL 21 forest images (441 entries), every entry
+                           additionally pushed through the reference's REAL result container
+                           cv2_pickleable.detail.MatchesInfo(x).to_cv2() (cv2_pickleable/detail.py:
+                           154-211, which validates the round trip itself) before it is recorded.
+  eisenberg_c2_stage.npz   BASELINE config 2 as a WHOLE STAGE on the 4 eisenberg frames the reference
+                           ships: ORB + star features merged as stitching_detailed_enhanced.py:784-
+                           834 merges them, the unchanged CustomBruteForceMatcher.match_n_features()
+                           with conf_thresh = 1.0 and example_06's predefined_overlaps re-indexed to
+                           the 4 frames (run "overlaps": ORB -> RANSAC -> fallback decision -> star
+                           MatchesInfo with the int(3 * conf) clamp and the mirror), a second run with
+                           enforced_matches / enforced_no_matches ("enforced") and a third with
+                           enforce_star_polygon_matcher=True ("allstars").  Every MatchesInfo of the
+                           returned tuple AND the raw (forward, mirror) pair every match_2_features
+                           call returned are recorded.
   polygon_golden.npz       unchanged reference BFPolygonMatcher on two synthetic overlapping
                            star views: get_polygons_characteristics arrays, the stored normalised
                            polygon_data_store arrays and the final DMatches of match().
@@ -114,6 +128,7 @@ def matchesinfo_to_arrays(prefix, mi, store):
     store[f"{prefix}_ids"] = np.array([mi.src_img_idx, mi.dst_img_idx, mi.num_inliers], dtype=np.int64)
     store[f"{prefix}_conf"] = np.array([mi.confidence], dtype=np.float64)
     store[f"{prefix}_H"] = np.zeros((0, 0)) if mi.H is None or np.size(mi.H) == 0 else np.asarray(mi.H, dtype=np.float64)
+    store[f"{prefix}_H_is_none"] = np.array([mi.H is None])
     store[f"{prefix}_mask"] = np.asarray(mi.inliers_mask, dtype=np.uint8).ravel()
     store[f"{prefix}_matches"] = np.array([[m.queryIdx, m.trainIdx, m.imgIdx] for m in mi.matches],
                                           dtype=np.int32).reshape(-1, 3)
@@ -237,16 +252,117 @@ def make_eisenberg_c2():
           [len(store[f"i{i}_norm_idx"]) for i in range(len(names))])
 
 
+def make_reference_matchesinfo_full(names, feats, imgs):
+    """All 21 forest images through the unchanged reference matcher, then every entry through the
+    reference's real cv2_pickleable container and back (the path the pipeline pickles through,
+    stitching_detailed_enhanced.py:1194)."""
+    import cv2_pickleable.detail as ref_pickleable  # the unchanged reference package
+    tmp = tempfile.mkdtemp(prefix="ssp_golden_full_")
+    n = len(names)
+    matcher = ref_bf.CustomBruteForceMatcher(
+        imgs_features_orb_and_stars=feats, imgs_features_len_orb=[len(f.keypoints) for f in feats],
+        conf_thresh=0.2, img_names=list(names), work_scale_imgs=imgs,
+        pairwise_matches_output_dir=tmp, disable_prompts=True, output_dir_polygon_matching=tmp,
+        predefined_overlaps=[], focal_length_pinhole=1135)
+    builtins.input = lambda *a: ""
+    infos = matcher.match_n_features()
+    store = {"n_images": np.array([n]), "conf_thresh": np.array([0.2]), "cv2_version": cv.__version__}
+    for k, mi in enumerate(infos):
+        back = ref_pickleable.MatchesInfo(mi).to_cv2()  # raises ValueError if the round trip differs
+        matchesinfo_to_arrays(f"m{k}", back, store)
+    np.savez_compressed(os.path.join(OUT, "reference_matchesinfo_c1_full.npz"), **store)
+    print(f"reference_matchesinfo_c1_full: {len(infos)} entries, "
+          f"{sum(1 for mi in infos if mi.src_img_idx >= 0)} kept, all through cv2_pickleable")
+
+
+# example_06 predefined_overlaps (example_06...py:75-122) restricted to the frames that exist in the
+# checkout -- 17-alt2-n (16), 18-alt2-e (17), 19-alt2-s (18), 21-zenith (20) -- and re-indexed 0..3
+C2_OVERLAPS = [(0, 1), (1, 2), (0, 3), (1, 3), (2, 3)]
+
+
+def make_c2_stage():
+    names = sorted(n for n in os.listdir(EISENBERG) if n.endswith(".jpg"))
+    tmp = tempfile.mkdtemp(prefix="ssp_golden_c2stage_")
+    finder = cv.ORB.create(nfeatures=1000, edgeThreshold=10, patchSize=30)  # 'orb-for-starry-sky'
+    feats, imgs, n_orb, scale = [], [], [], None
+    store = {"names": np.array(names), "focal": np.array([1135.0]), "cv2_version": cv.__version__,
+             "overlaps": np.array(C2_OVERLAPS, dtype=np.int32), "conf_thresh": np.array([1.0])}
+    for i, name in enumerate(names):
+        full = cv.imread(os.path.join(EISENBERG, name))
+        if scale is None:
+            scale = min(1.0, np.sqrt(1.2 * 1e6 / (full.shape[0] * full.shape[1])))
+        img = cv.resize(src=full, dsize=None, fx=scale, fy=scale, interpolation=cv.INTER_AREA)
+        # stitching_detailed_enhanced.py:784-834, unchanged order of operations
+        orb_ft = cv.detail.computeImageFeatures2(finder, ref_ip.optimize_img_for_feature_detection(img, prompt_dialog=False))
+        star_ft = ref_ip.compute_star_features(img, name, tmp, n_brightest_stars=1000)
+        merged = cv.detail.computeImageFeatures2(cv.ORB_create(), np.zeros(img.shape, dtype=np.uint8))
+        merged.descriptors = cv.vconcat([orb_ft.descriptors, star_ft.descriptors])
+        merged.img_idx = -1
+        merged.img_size = orb_ft.img_size
+        merged.keypoints = orb_ft.keypoints + star_ft.keypoints
+        feats.append(merged)
+        imgs.append(img)
+        n_orb.append(len(orb_ft.keypoints))
+        store[f"i{i}_descriptors"] = merged.descriptors.get()
+        store[f"i{i}_xy"] = np.array([kp.pt for kp in merged.keypoints], dtype=np.float32).reshape(-1, 2)
+        store[f"i{i}_size"] = np.array([kp.size for kp in merged.keypoints], dtype=np.float32)
+    store["n_orb"] = np.array(n_orb, dtype=np.int64)
+    store["img_shape"] = np.array(imgs[0].shape)
+    builtins.input = lambda *a: ""
+
+    # the polygon cache is per matcher (custom_bruteforce_matcher.py:57-59); the three runs hand the
+    # same dict on so that the reference's get_star_brightness (148 s per pair) runs once per image.
+    # What is cached is a pure function of the image, so each run records what a fresh one would.
+    shared_store = {}
+
+    def run(tag, **kw):
+        matcher = ref_bf.CustomBruteForceMatcher(
+            imgs_features_orb_and_stars=feats, imgs_features_len_orb=n_orb, conf_thresh=1.0,
+            img_names=list(names), work_scale_imgs=imgs, pairwise_matches_output_dir=tmp,
+            disable_prompts=True, output_dir_polygon_matching=tmp, focal_length_pinhole=1135, **kw)
+        matcher.polygon_data_store = shared_store
+        raw = {}
+        inner = matcher.match_2_features
+
+        def recording(src, dst):
+            out = inner(src, dst)
+            for side, mi in enumerate(out):
+                matchesinfo_to_arrays(f"{tag}_raw_{src}_{dst}_{side}", mi, store)
+            raw[(src, dst)] = out
+            return out
+        matcher.match_2_features = recording
+        infos = matcher.match_n_features()
+        for k, mi in enumerate(infos):
+            matchesinfo_to_arrays(f"{tag}_m{k}", mi, store)
+        kinds = sorted(matcher.kind_of_pairwise_matches.items())
+        store[f"{tag}_kinds"] = np.array([[s, d, 1 if v == "stars" else 0] for (s, d), v in kinds], dtype=np.int32)
+        store[f"{tag}_counter"] = np.array(matcher.fts_calculated_counter, dtype=np.int32)
+        print(f"c2 stage [{tag}]: kinds {dict(kinds)}; kept",
+              [(mi.src_img_idx, mi.dst_img_idx, mi.confidence, mi.num_inliers) for mi in infos if mi.src_img_idx >= 0])
+
+    run("overlaps", predefined_overlaps=C2_OVERLAPS)
+    run("enforced", predefined_overlaps=C2_OVERLAPS, enforced_matches=[(names[0], names[2])],
+        enforced_no_matches=[(names[1], names[3])])
+    run("allstars", predefined_overlaps=[], enforce_star_polygon_matcher=True)
+    np.savez_compressed(os.path.join(OUT, "eisenberg_c2_stage.npz"), **store)
+    print("eisenberg_c2_stage: n_orb", n_orb, "stars", [len(f.keypoints) - k for f, k in zip(feats, n_orb)])
+
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["orb", "hamming", "matchesinfo", "polygon", "c2"]
+    which = sys.argv[1:] or ["orb", "hamming", "matchesinfo", "matchesinfo_full", "polygon", "c2", "c2stage"]
     names = feats = imgs = None
-    if "orb" in which or "matchesinfo" in which:
+    if "orb" in which or "matchesinfo" in which or "matchesinfo_full" in which:
         names, feats, imgs = make_orb_fixture()
     if "hamming" in which:
         make_hamming_golden()
     if "matchesinfo" in which:
         make_reference_matchesinfo(names, feats, imgs)
+    if "matchesinfo_full" in which:
+        make_reference_matchesinfo_full(names, feats, imgs)
     if "polygon" in which:
         make_polygon_golden()
     if "c2" in which:
         make_eisenberg_c2()
+    if "c2stage" in which:
+        make_c2_stage()
