@@ -127,6 +127,13 @@ int ssp_bind_descriptor_bank(ssp_ctx* ctx, const uint8_t* d_desc, const int64_t*
  * cv::BFMatcher itself asserts (IMGIDX_SHIFT); more is SSP_ERR_INVALID. */
 int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode,
                             int ratio_num, int ratio_den, int variant, int64_t* match_offsets);
+/* The same with the Lowe ratio as the float64 the reference multiplies with
+ * (custom_bruteforce_matcher.py:164 `m.distance < 0.75 * n.distance`): the device evaluates
+ * (double)d1 < ratio * (double)d2 with one correctly rounded multiplication, i.e. exactly Python's
+ * comparison for ANY ratio.  ssp_hamming_match_pairs(num, den) is this call with
+ * ratio = (double)num / (double)den. */
+int ssp_hamming_match_pairs_f64(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode,
+                                double ratio, int variant, int64_t* match_offsets);
 /* Copies the survivors of the last ssp_hamming_match_pairs call: queryIdx, trainIdx and the
  * integer Hamming distance (DMatch.distance is this value as float32).  `capacity` is the
  * number of entries each array can hold (>= match_offsets[n_pairs]). */

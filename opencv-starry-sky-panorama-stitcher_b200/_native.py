@@ -44,6 +44,8 @@ PROTOTYPES = {
     "ssp_bind_descriptor_bank": (_c.c_int, [_ctx_p, _u8p, _i64p, _c.c_int]),
     "ssp_hamming_match_pairs": (_c.c_int, [_ctx_p, _i32p, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
                                            _c.c_int, _i64p]),
+    "ssp_hamming_match_pairs_f64": (_c.c_int, [_ctx_p, _i32p, _c.c_int, _c.c_int, _c.c_double,
+                                               _c.c_int, _i64p]),
     "ssp_hamming_fetch_matches": (_c.c_int, [_ctx_p, _i32p, _i32p, _i32p, _c.c_int64, _c.c_int]),
     "ssp_hamming_fetch_best2": (_c.c_int, [_ctx_p, _i32p, _c.c_int64, _c.c_int]),
     "ssp_hamming_last_stats": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_float),

@@ -9,9 +9,20 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>   // header-only; ranges cost nothing unless a profiler is attached
+
 #include "ssp_b200.h"
 
 namespace ssp {
+
+// NVTX range around one stage of a C-ABI call (upload / expand / kernel 1 / finalize / kernel 2 /
+// kernel 3 / fetch), so that an nsys / ncu timeline of a step names its pieces.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 // Growable device allocation owned by a context.
 struct DevBuf {
@@ -63,12 +74,17 @@ struct HammingWork {
   // the bits from SSP_SLOT_DIST_SHIFT up; q_tiles = number of such tiles.  NULL = all nq rows in order.
   const int* slot_src = nullptr;
   int q_tiles = 0;
+  // tensor variant, fused cross-check: per train row of the pair the running nearest query row
+  // (hamming << 18 | row, atomicMin) and its 16-bit filter threshold; NULL = row direction only
+  uint32_t* col_key = nullptr;
+  int16_t* col_thr = nullptr;
 };
 
 // One image pair for the finalize kernels.
 struct HammingPair {
   long long fwd_row;  // best2 rows of query image vs train image
-  long long rev_row;  // best2 rows of train image vs query image (cross-check only)
+  long long rev_row;  // best2 rows of train image vs query image (cross-check, two-pass forms), or the
+                      // pair's first entry in the column-key array (fused cross-check)
   int nq;
   int nt;
 };
@@ -115,6 +131,7 @@ struct ssp_ctx {
   ssp::DevBuf h_popc;      // popcount of every bank row (int32), tensor variant
   ssp::DevBuf h_tc_work, h_tc_err;
   ssp::DevBuf h_cc_aux, h_cc_mark, h_cc_slots, h_cc_cls;  // sparse reverse pass of the cross-check
+  ssp::DevBuf h_col_key, h_col_thr;                        // fused cross-check: column keys / thresholds
   bool h_expanded_valid = false;
   std::vector<long long> exp_byte_off;  // per image byte offset into h_expanded
   std::vector<int> exp_rows_pad;

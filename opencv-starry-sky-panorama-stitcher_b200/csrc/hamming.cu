@@ -154,15 +154,33 @@ hamming_popc_kernel(const HammingWork* __restrict__ work, int4* __restrict__ bes
 
 // ---- finalize: survivor test, per-pair count, scan over pairs, ordered compaction ----------
 
+// internal finalize mode: cross-check whose reverse direction sits in the column-key array
+constexpr int SSP_MODE_CROSS_FUSED = 2;
+constexpr uint32_t COL_KEY_ROW_MASK = (1u << 18) - 1u;
+
 __device__ __forceinline__ bool survives(const HammingPair& p, const int4* __restrict__ best2,
-                                         int q, int mode, int rnum, int rden, int4& rec) {
+                                         const uint32_t* __restrict__ col_key, int q, int mode, double ratio,
+                                         int4& rec) {
   rec = best2[p.fwd_row + q];
   if (mode == SSP_MODE_KNN2_RATIO) {
-    // m.distance < ratio * n.distance  <=>  den*d1 < num*d2 (exact for ratio = num/den)
-    return rec.z >= 0 && (long long)rden * rec.y < (long long)rnum * rec.w;
+    // `m.distance < ratio * n.distance` exactly as Python evaluates it (custom_bruteforce_matcher.py:
+    // 164): both distances are small integers held in floats, the product and the comparison are
+    // float64 -- one correctly rounded multiplication, no FMA involved
+    return rec.z >= 0 && (double)rec.y < __dmul_rn(ratio, (double)rec.w);
   }
   if (rec.x < 0) return false;
+  if (mode == SSP_MODE_CROSS_FUSED) return (col_key[p.rev_row + rec.x] & COL_KEY_ROW_MASK) == (uint32_t)q;
   return best2[p.rev_row + rec.x].x == q;
+}
+
+// fused cross-check: thresholds of real train rows start at "anything gets through", those of the
+// pad rows of the last tile at "nothing does" (hamming_tensor.cu, tc_cols)
+__global__ void __launch_bounds__(256)
+col_thr_init_kernel(const HammingPair* __restrict__ pairs, int16_t* __restrict__ thr) {
+  const HammingPair p = pairs[blockIdx.x];
+  const int nt_pad = (p.nt + 255) / 256 * 256;
+  for (int t = blockIdx.y * blockDim.x + threadIdx.x; t < nt_pad; t += gridDim.y * blockDim.x)
+    thr[p.rev_row + t] = (t < p.nt) ? (int16_t)16382 : (int16_t)-16384;
 }
 
 // ---- cross-check, tensor variant: the reverse pass runs over the CLAIMED train rows only --------
@@ -231,12 +249,12 @@ constexpr int FIN_THREADS = 512;
 
 __global__ void __launch_bounds__(FIN_THREADS)
 hamming_count_kernel(const HammingPair* __restrict__ pairs, const int4* __restrict__ best2,
-                     int mode, int rnum, int rden, int* __restrict__ counts) {
+                     const uint32_t* __restrict__ col_key, int mode, double ratio, int* __restrict__ counts) {
   const HammingPair p = pairs[blockIdx.x];
   int local = 0;
   for (int q = threadIdx.x; q < p.nq; q += FIN_THREADS) {
     int4 rec;
-    local += survives(p, best2, q, mode, rnum, rden, rec) ? 1 : 0;
+    local += survives(p, best2, col_key, q, mode, ratio, rec) ? 1 : 0;
   }
   __shared__ int warp_sum[FIN_THREADS / 32];
 #pragma unroll
@@ -252,7 +270,8 @@ hamming_count_kernel(const HammingPair* __restrict__ pairs, const int4* __restri
 
 __global__ void __launch_bounds__(FIN_THREADS)
 hamming_compact_kernel(const HammingPair* __restrict__ pairs, const int4* __restrict__ best2,
-                       int mode, int rnum, int rden, const long long* __restrict__ offsets,
+                       const uint32_t* __restrict__ col_key, int mode, double ratio,
+                       const long long* __restrict__ offsets,
                        int* __restrict__ mq, int* __restrict__ mt, int* __restrict__ md) {
   const HammingPair p = pairs[blockIdx.x];
   __shared__ int warp_cnt[FIN_THREADS / 32];
@@ -263,7 +282,7 @@ hamming_compact_kernel(const HammingPair* __restrict__ pairs, const int4* __rest
   for (int base = 0; base < p.nq; base += FIN_THREADS) {
     const int q = base + threadIdx.x;
     int4 rec = make_int4(0, 0, 0, 0);
-    const bool keep = (q < p.nq) && survives(p, best2, q, mode, rnum, rden, rec);
+    const bool keep = (q < p.nq) && survives(p, best2, col_key, q, mode, ratio, rec);
     const unsigned ballot = __ballot_sync(0xffffffffu, keep);
     if (lane == 0) warp_cnt[wid] = __popc(ballot);
     __syncthreads();
@@ -303,15 +322,28 @@ static cudaError_t launch_popc(ssp_ctx* ctx, int n_work, int max_nq) {
 
 // implemented in hamming_tensor.cu
 cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& work, int k,
-                                  std::string* why_not);
+                                  std::string* why_not, bool wait);
 
 }  // namespace ssp
 
-extern "C" {
+namespace ssp {
 
-int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode,
-                            int ratio_num, int ratio_den, int variant, int64_t* match_offsets) {
-  using namespace ssp;
+// How the tensor variant does the cross-check (environment variable SSP_B200_CROSSCHECK):
+//   fused  (default) one launch: the column direction comes out of the forward accumulators
+//   sparse           round 1's form: forward launch, then a reverse launch over the claimed rows
+//   dense            both directions as dense work items of one launch (what the POPC variants do)
+enum CrossForm { CC_FUSED, CC_SPARSE, CC_DENSE };
+static CrossForm cross_form() {   // read per call: tests and A/B runs switch it between calls
+  const char* d = getenv("SSP_B200_CROSSCHECK_DENSE");
+  if (d && d[0] == '1') return CC_DENSE;
+  const char* e = getenv("SSP_B200_CROSSCHECK");
+  if (e && e[0] == 's') return CC_SPARSE;
+  if (e && e[0] == 'd') return CC_DENSE;
+  return CC_FUSED;
+}
+
+static int hamming_match_impl(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode, double ratio,
+                              int variant, int64_t* match_offsets) {
   if (!ctx) return SSP_ERR_INVALID;
   if (int rc = use_device(ctx)) return rc;
   SSP_REQUIRE(ctx, ctx->d_desc != nullptr || (!ctx->row_off.empty() && ctx->row_off.back() == 0),
@@ -327,9 +359,10 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
   SSP_REQUIRE(ctx, variant >= SSP_HAMMING_AUTO && variant <= SSP_HAMMING_TENSOR, SSP_ERR_INVALID,
               "ssp_hamming_match_pairs: unknown variant %d", variant);
   if (mode == SSP_MODE_KNN2_RATIO)
-    SSP_REQUIRE(ctx, ratio_num > 0 && ratio_den > 0, SSP_ERR_INVALID,
+    SSP_REQUIRE(ctx, ratio > 0.0 && ratio == ratio, SSP_ERR_INVALID,
                 "ssp_hamming_match_pairs: ratio must be positive");
   const int n_images = (int)ctx->row_off.size() - 1;
+  NvtxRange range_all("ssp_hamming_match_pairs");
 
   ctx->h_n_matches = -1;
   ctx->h_launches = 0;
@@ -345,20 +378,18 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
 
   // directed work items + per-pair finalize records
   const bool cross = (mode == SSP_MODE_CROSSCHECK);
-  // tensor variant: the reverse items of the cross-check wait for the forward ones and run over
-  // the claimed rows only (SSP_B200_CROSSCHECK_DENSE=1 keeps both directions in one dense launch)
-  static const bool dense_env = [] {
-    const char* e = getenv("SSP_B200_CROSSCHECK_DENSE");
-    return e && e[0] == '1';
-  }();
-  const bool sparse_rev = cross && !dense_env &&
-                          (variant == SSP_HAMMING_AUTO || variant == SSP_HAMMING_TENSOR);
+  int v = variant;
+  if (v == SSP_HAMMING_AUTO) v = SSP_HAMMING_TENSOR;   // fastest at every size measured
+  const bool tensor = (v == SSP_HAMMING_TENSOR);
+  const CrossForm form = (cross && tensor) ? cross_form() : CC_DENSE;
+  const bool fused = cross && form == CC_FUSED;
+  const bool sparse_rev = cross && form == CC_SPARSE;
   std::vector<HammingWork> work, rev_work;
   std::vector<HammingPair> hp((size_t)n_pairs);
   work.reserve((size_t)n_pairs * (cross ? 2 : 1));
   const uint4* bank = reinterpret_cast<const uint4*>(ctx->d_desc);
   long long fwd_rows = 0, rows = 0;
-  int max_nq = 0;
+  int max_nq = 0, max_nt = 1;
   for (int p = 0; p < n_pairs; ++p) {
     const int qi = pairs[2 * p], ti = pairs[2 * p + 1];
     SSP_REQUIRE(ctx, qi >= 0 && qi < n_images && ti >= 0 && ti < n_images, SSP_ERR_INVALID,
@@ -375,7 +406,8 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
                 cross && nq_p > nt_p ? nq_p : nt_p);
     fwd_rows += nq_p;
   }
-  long long rev_cursor = fwd_rows;
+  long long rev_cursor = fwd_rows;   // two-pass forms: reverse best2 rows follow the forward ones
+  long long col_cursor = 0;          // fused form: entries of the column-key array
   for (int p = 0; p < n_pairs; ++p) {
     const int qi = pairs[2 * p], ti = pairs[2 * p + 1];
     const int nq = (int)(ctx->row_off[qi + 1] - ctx->row_off[qi]);
@@ -393,10 +425,15 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
     hp[p].nq = nq;
     hp[p].nt = nt;
     rows += nq;
-    if (nq > 0) work.push_back(f);
     max_nq = nq > max_nq ? nq : max_nq;
+    max_nt = nt > max_nt ? nt : max_nt;
     ctx->h_comparisons += (long long)nq * nt;
-    if (cross) {
+    if (fused) {
+      hp[p].rev_row = col_cursor;               // 256-entry aligned: 16-byte aligned threshold rows
+      col_cursor += ((long long)nt + 255) / 256 * 256;
+    }
+    if (nq > 0) work.push_back(f);              // col pointers are filled in below (fused)
+    if (cross && !fused) {
       HammingWork r;
       r.q = f.t;
       r.t = f.q;
@@ -411,29 +448,55 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
       max_nq = nt > max_nq ? nt : max_nq;
     }
   }
-  const long long total_rows = cross ? rev_cursor : rows;
+  const long long total_rows = (cross && !fused) ? rev_cursor : rows;
   ctx->h_total_rows = rows;
 
   SSP_CUDA_TRY(ctx, ctx->h_best2.ensure((size_t)(total_rows + 1) * sizeof(int4)));
   SSP_CUDA_TRY(ctx, ctx->h_pairs.ensure(hp.size() * sizeof(HammingPair)));
   SSP_CUDA_TRY(ctx, ctx->h_counts.ensure((size_t)n_pairs * sizeof(int)));
-  SSP_CUDA_TRY(ctx, ctx->h_offsets.ensure(((size_t)n_pairs + 1) * sizeof(long long)));
+  SSP_CUDA_TRY(ctx, ctx->h_offsets.ensure(((size_t)n_pairs + 2) * sizeof(long long)));
+  // survivors: at most one per forward query row, so the output arrays are sized up front and the
+  // whole call needs ONE host synchronisation (at its end)
+  SSP_CUDA_TRY(ctx, ctx->h_mq.ensure((size_t)(rows + 1) * sizeof(int)));
+  SSP_CUDA_TRY(ctx, ctx->h_mt.ensure((size_t)(rows + 1) * sizeof(int)));
+  SSP_CUDA_TRY(ctx, ctx->h_md.ensure((size_t)(rows + 1) * sizeof(int)));
+  SSP_CUDA_TRY(ctx, ctx->h_tc_err.ensure(sizeof(int)));
+  SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_tc_err.p, 0, sizeof(int), ctx->stream));
   SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_pairs.p, hp.data(), hp.size() * sizeof(HammingPair),
                                     cudaMemcpyHostToDevice, ctx->stream));
   // rows of empty train sets are never written by a kernel: make them read as "no neighbour"
   SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_best2.p, 0xFF, (size_t)(total_rows + 1) * sizeof(int4),
                                     ctx->stream));
+  if (fused) {
+    SSP_CUDA_TRY(ctx, ctx->h_col_key.ensure((size_t)(col_cursor + 1) * sizeof(uint32_t)));
+    SSP_CUDA_TRY(ctx, ctx->h_col_thr.ensure((size_t)(col_cursor + 8) * sizeof(int16_t)));
+    SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_col_key.p, 0xFF, (size_t)(col_cursor + 1) * sizeof(uint32_t),
+                                      ctx->stream));
+    int by = (max_nt + 255) / 256;
+    by = by > 32 ? 32 : by;
+    col_thr_init_kernel<<<dim3((unsigned)n_pairs, (unsigned)by), 256, 0, ctx->stream>>>(
+        ctx->h_pairs.as<HammingPair>(), ctx->h_col_thr.as<int16_t>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    ctx->h_launches += 1;
+    size_t wi = 0;
+    for (int p = 0; p < n_pairs; ++p) {
+      if (hp[(size_t)p].nq <= 0) continue;
+      work[wi].col_key = ctx->h_col_key.as<uint32_t>() + hp[(size_t)p].rev_row;
+      work[wi].col_thr = ctx->h_col_thr.as<int16_t>() + hp[(size_t)p].rev_row;
+      ++wi;
+    }
+  }
 
   const int k = cross ? 1 : 2;
   float rev_fwd_ms = 0.f;   // sparse cross-check: kernel time of the forward launch (ev0/ev1 then hold the reverse one)
+  bool timed = false;
   if (!work.empty()) {
-    int v = variant;
-    if (v == SSP_HAMMING_AUTO) v = SSP_HAMMING_TENSOR;   // fastest at every size measured
     SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    const bool tensor = (v == SSP_HAMMING_TENSOR);
+    timed = true;
     if (tensor) {
+      NvtxRange range_k("kernel 1 (tcgen05)");
       std::string why;
-      cudaError_t e = launch_hamming_tensor(ctx, work, k, &why);
+      cudaError_t e = launch_hamming_tensor(ctx, work, k, &why, /*wait=*/sparse_rev && !rev_work.empty());
       if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
       SSP_CUDA_TRY(ctx, e);
       if (sparse_rev && !rev_work.empty()) {
@@ -484,12 +547,13 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
           r.slot_src = ctx->h_cc_slots.as<int>() + aux[(size_t)p].slot_off;
           r.q_tiles = (most + 15) / 16;   // 16 slots of every class per 128-slot tile
         }
-        e = launch_hamming_tensor(ctx, rev_work, k, &why);
+        e = launch_hamming_tensor(ctx, rev_work, k, &why, /*wait=*/false);
         if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
         SSP_CUDA_TRY(ctx, e);
         rev_fwd_ms = fwd_ms;
       }
     } else {
+      NvtxRange range_k("kernel 1 (popc)");
       SSP_CUDA_TRY(ctx, ctx->h_work.ensure(work.size() * sizeof(HammingWork)));
       SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_work.p, work.data(),
                                         work.size() * sizeof(HammingWork), cudaMemcpyHostToDevice,
@@ -502,38 +566,62 @@ int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int
         e = (k == 2) ? launch_popc<4, 4, 2>(ctx, nw, max_nq) : launch_popc<4, 4, 1>(ctx, nw, max_nq);
       SSP_CUDA_TRY(ctx, e);
       ctx->h_launches += 1;
+      SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     }
-    if (!tensor) SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   }
 
-  hamming_count_kernel<<<n_pairs, FIN_THREADS, 0, ctx->stream>>>(
-      ctx->h_pairs.as<HammingPair>(), ctx->h_best2.as<int4>(), mode, ratio_num, ratio_den,
-      ctx->h_counts.as<int>());
-  SSP_CUDA_TRY(ctx, cudaGetLastError());
-  scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->h_counts.as<int>(), n_pairs,
-                                                  ctx->h_offsets.as<long long>());
-  SSP_CUDA_TRY(ctx, cudaGetLastError());
-  ctx->h_launches += 2;
+  {
+    NvtxRange range_f("finalize (count, scan, compact)");
+    const int fmode = fused ? SSP_MODE_CROSS_FUSED : mode;
+    const uint32_t* ck = fused ? ctx->h_col_key.as<uint32_t>() : nullptr;
+    hamming_count_kernel<<<n_pairs, FIN_THREADS, 0, ctx->stream>>>(
+        ctx->h_pairs.as<HammingPair>(), ctx->h_best2.as<int4>(), ck, fmode, ratio, ctx->h_counts.as<int>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->h_counts.as<int>(), n_pairs,
+                                                    ctx->h_offsets.as<long long>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    hamming_compact_kernel<<<n_pairs, FIN_THREADS, 0, ctx->stream>>>(
+        ctx->h_pairs.as<HammingPair>(), ctx->h_best2.as<int4>(), ck, fmode, ratio,
+        ctx->h_offsets.as<long long>(), ctx->h_mq.as<int>(), ctx->h_mt.as<int>(), ctx->h_md.as<int>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    ctx->h_launches += 3;
+  }
+  // offsets and the tensor kernel's error flag come back together: the call's only synchronisation
+  int tc_flag = 0;
   SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_match_offsets.data(), ctx->h_offsets.p,
                                     ((size_t)n_pairs + 1) * sizeof(long long),
                                     cudaMemcpyDeviceToHost, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&tc_flag, ctx->h_tc_err.p, sizeof(int), cudaMemcpyDeviceToHost,
+                                    ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (tc_flag != 0)
+    return fail(ctx, SSP_ERR_INVALID,
+                "tensor variant unavailable: dynamic shared memory window is not 1024-byte aligned");
   const long long total = ctx->h_match_offsets[(size_t)n_pairs];
-  SSP_CUDA_TRY(ctx, ctx->h_mq.ensure((size_t)(total + 1) * sizeof(int)));
-  SSP_CUDA_TRY(ctx, ctx->h_mt.ensure((size_t)(total + 1) * sizeof(int)));
-  SSP_CUDA_TRY(ctx, ctx->h_md.ensure((size_t)(total + 1) * sizeof(int)));
-  hamming_compact_kernel<<<n_pairs, FIN_THREADS, 0, ctx->stream>>>(
-      ctx->h_pairs.as<HammingPair>(), ctx->h_best2.as<int4>(), mode, ratio_num, ratio_den,
-      ctx->h_offsets.as<long long>(), ctx->h_mq.as<int>(), ctx->h_mt.as<int>(),
-      ctx->h_md.as<int>());
-  SSP_CUDA_TRY(ctx, cudaGetLastError());
-  ctx->h_launches += 1;
-  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  if (!work.empty()) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->h_main_ms, ctx->ev0, ctx->ev1));
+  if (timed) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->h_main_ms, ctx->ev0, ctx->ev1));
   ctx->h_main_ms += rev_fwd_ms;
   for (int p = 0; p <= n_pairs; ++p) match_offsets[p] = ctx->h_match_offsets[(size_t)p];
   ctx->h_n_matches = total;
   return SSP_OK;
+}
+
+}  // namespace ssp
+
+extern "C" {
+
+int ssp_hamming_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode,
+                            int ratio_num, int ratio_den, int variant, int64_t* match_offsets) {
+  if (!ctx) return SSP_ERR_INVALID;
+  if (mode == SSP_MODE_KNN2_RATIO)
+    SSP_REQUIRE(ctx, ratio_num > 0 && ratio_den > 0, SSP_ERR_INVALID,
+                "ssp_hamming_match_pairs: ratio must be positive");
+  const double ratio = (ratio_den > 0) ? (double)ratio_num / (double)ratio_den : 0.75;
+  return ssp::hamming_match_impl(ctx, pairs, n_pairs, mode, ratio, variant, match_offsets);
+}
+
+int ssp_hamming_match_pairs_f64(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode,
+                                double ratio, int variant, int64_t* match_offsets) {
+  return ssp::hamming_match_impl(ctx, pairs, n_pairs, mode, ratio, variant, match_offsets);
 }
 
 int ssp_hamming_fetch_matches(ssp_ctx* ctx, int32_t* query_idx, int32_t* train_idx,

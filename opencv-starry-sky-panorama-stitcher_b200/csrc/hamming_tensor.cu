@@ -96,6 +96,11 @@ struct TcWork {              // one directed image pair
   const int* slot_src;       // sparse query set (HammingWork::slot_src) or NULL
   int tile_begin;            // prefix sum of query tiles over the work list
   int pad_;
+  // fused cross-check (K = 1): per train row the running nearest QUERY row of the pair as a packed
+  // key (hamming << 18 | query row), updated with atomicMin from the same accumulators that serve
+  // the row direction, and the 16-bit filter thresholds derived from it.  NULL = row direction only.
+  uint32_t* col_key;
+  int16_t* col_thr;
 };
 
 // ---- bank expansion ---------------------------------------------------------------------------
@@ -216,6 +221,8 @@ struct TcRow {
   uint16_t* my_slot;   // where this thread publishes the D of its own k-th best (tag | D + 512)
   uint32_t tag;        // (item & 63) << 10, marks published values of the current work item
   bool heavy;          // warp-uniform: skip the filter and run the full-tile tournament (thresholds settling)
+  int slack;           // 1 once a rotated train sweep has wrapped: my best may then have a HIGHER train index
+                       // than a column still to come, so the own threshold must let an equal D through
   TC_PROF(long long p_wait; long long p_pass1; long long p_pass2; long long p_nflag;)
 };
 
@@ -228,7 +235,7 @@ __device__ __forceinline__ void tc_publish(TcRow& r, uint32_t kth) {
   // masked: an empty slot of a sparse tile computes on stale operands, and its out-of-range D
   // must not spill into the tag (the peer would take it for a value of the NEXT work item)
   *r.my_slot = (uint16_t)(r.tag | ((uint32_t)(d_own + 512) & 1023u));
-  r.thr = max(r.thr, d_own);
+  r.thr = max(r.thr, d_own - r.slack);
 }
 // Raises the threshold from what the other warpgroup published (it sees the other half of the
 // train rows): its k best rows precede every column of mine whose D is smaller.  `slack` = 1
@@ -396,21 +403,12 @@ __device__ __forceinline__ void tc_group_exact_packed(uint32_t (&q)[8], uint32_t
   if (kth != TC_KEY_NONE) tc_publish(r, kth);
 }
 
+// Row direction of one visit: `p` = this lane's 128 columns as packed s16 pairs (already loaded, the
+// accumulator already handed back).
 template <int K, bool MASKED>
-__device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint32_t nt, TcRow& r,
-                                        uint64_t* acc_empty, int lane) {
-#if TC_EXPERIMENT == 1
-  tc_release(acc_empty, lane);
-  return;
-#endif
-  // The accumulator goes back to the MMA issuer as soon as its 128 columns sit in registers (held
-  // for one TMEM load); both passes then run on the registers while the tensor pipe already
-  // fills the buffer again.
+__device__ __forceinline__ void tc_tile(uint32_t (&p)[TC_HALF / 2], uint32_t col_base, uint32_t nt, TcRow& r,
+                                        int lane) {
   const uint32_t thrp = (uint32_t)(max(r.thr * TC_QSCALE, -32768) & 0xFFFF) * 0x10001u;
-  uint32_t p[TC_HALF / 2];
-  tc_ld128_packed(taddr, p);
-  tc_wait_ld(p);
-  tc_release(acc_empty, lane);
 #if TC_EXPERIMENT == 0
   if (!MASKED && r.heavy) {
     // thresholds still settling (always so in the first tile of an item): the filter would flag
@@ -465,6 +463,86 @@ __device__ __forceinline__ void tc_tile(uint32_t taddr, uint32_t col_base, uint3
   TC_PROF(r.p_pass2 += clock64() - c_p1;)
 }
 
+// ---- fused cross-check: the COLUMN direction from the same accumulators -----------------------------
+// cv.BFMatcher(crossCheck=True) keeps (q, t) iff t is q's nearest train row AND q is t's nearest query
+// row.  The second half needs, per train row t of the pair, min over ALL query rows of
+// (hamming, query row) -- a reduction ACROSS the lanes, warps and CTAs that hold the rows.  It is
+// kept in global memory as col_key[t] = hamming << 18 | q (atomicMin; rows < 2^18, OpenCV's own limit)
+// and filtered exactly like the row direction, only with one threshold PER COLUMN:
+//   col_thr[t] = min(64 * T, 16382) as s16,  T >= the hamming part of col_key[t] at all times,
+// so that an entry can change col_key[t] only if hamming <= T (non-strict: rows arrive in any order
+// across CTAs, an equal distance with a lower row index must still get through).  With the packed
+// accumulators p (64 * D per s16 half, hamming = pq - D) the test  hamming <= T  is
+//   64 * D + 64 * T >= 64 * pq   <=>   (p + c) per half  >  64 * pq - 32,
+// ONE 32-bit add per register pair: a carry out of the low half pollutes the high half by +1, which
+// the -32 absorbs (all sums are multiples of 64; c is capped so that no half overflows).  Stale
+// thresholds are older, i.e. larger: they only flag more.  Exactness rests on the atomicMin of
+// full keys alone.  Pad columns carry c = -16384 and D = 0 (zero train rows): never flagged.
+// Lanes without a query row carry the threshold 0x7FFF: never flagged.
+constexpr uint32_t TC_COL_KEY_SHIFT = 18;
+constexpr int TC_COL_THR_CAP = 16382;
+
+__device__ __forceinline__ void tc_col_group(const uint32_t (&q)[8], const uint32_t (&c)[8], uint32_t thrq,
+                                             uint32_t col0, int pq, int row, uint32_t* __restrict__ col_key,
+                                             int16_t* __restrict__ col_thr) {
+  // which of the 16 columns does THIS lane beat?
+  uint32_t mine = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t d = __vmaxs2(q[j] + c[j], thrq) ^ thrq;   // half != 0 <=> beaten
+    mine |= ((d & 0xFFFFu) ? 1u : 0u) << (2 * j);
+    mine |= ((d >> 16) ? 1u : 0u) << (2 * j + 1);
+  }
+  const uint32_t any = __reduce_or_sync(0xffffffffu, mine);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    if (!(any & (1u << j))) continue;   // warp-uniform
+    const int d64 = (j & 1) ? ((int)q[j >> 1] >> 16) : (int)(short)(q[j >> 1] & 0xFFFFu);
+    const int ham = pq - ((TC_QSCALE == 64) ? (d64 >> 6) : d64 / TC_QSCALE);   // exact: d64 is a multiple of TC_QSCALE
+    const bool hit = (mine >> j) & 1u;
+    const uint32_t key = hit ? (((uint32_t)ham << TC_COL_KEY_SHIFT) | (uint32_t)row) : 0xFFFFFFFFu;
+    const uint32_t best = __reduce_min_sync(0xffffffffu, key);
+    if (hit && key == best) {   // one lane: keys of different rows differ
+      atomicMin(col_key + col0 + j, key);
+      // fire and forget: my distance is an upper bound of the column's best from now on
+      col_thr[col0 + j] = (int16_t)min(ham * TC_QSCALE, TC_COL_THR_CAP);
+    }
+  }
+}
+
+// Column pass of one visit.  `c` = the 128 column thresholds of this warpgroup's half tile (same in
+// every lane), thrq = packed (64 * pq - 32) of this lane's row.
+__device__ __forceinline__ void tc_cols(const uint32_t (&p)[TC_HALF / 2], const uint32_t (&c)[TC_HALF / 2],
+                                        uint32_t thrq, uint32_t col_base, int pq, int row,
+                                        uint32_t* __restrict__ col_key, int16_t* __restrict__ col_thr) {
+  uint32_t gm[TC_HALF / TC_GROUP];
+#pragma unroll
+  for (int g = 0; g < TC_HALF / TC_GROUP; ++g) {
+    uint32_t s[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = p[8 * g + j] + c[8 * g + j];
+    gm[g] = __vimax3_s16x2(__vimax3_s16x2(s[0], s[1], s[2]), __vimax3_s16x2(s[3], s[4], s[5]), __vmaxs2(s[6], s[7]));
+  }
+  const uint32_t all = __vimax3_s16x2(__vimax3_s16x2(gm[0], gm[1], gm[2]), __vimax3_s16x2(gm[3], gm[4], gm[5]),
+                                      __vimax3_s16x2(gm[6], gm[7], thrq));
+  if (!__any_sync(0xffffffffu, all != thrq)) return;
+  uint32_t flags = 0;
+#pragma unroll
+  for (int g = 0; g < TC_HALF / TC_GROUP; ++g) flags |= (__vmaxs2(gm[g], thrq) != thrq) ? (1u << g) : 0u;
+  flags = __reduce_or_sync(0xffffffffu, flags);
+  while (flags) {   // warp-uniform
+    const uint32_t g = tc_pop(flags);
+    uint32_t q[8], cc[8];
+    switch (g) {
+#define TC_CASE(i) case i: _Pragma("unroll") for (int j = 0; j < 8; ++j) { q[j] = p[8 * i + j]; cc[j] = c[8 * i + j]; } break;
+      TC_CASE(0) TC_CASE(1) TC_CASE(2) TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6)
+      default: _Pragma("unroll") for (int j = 0; j < 8; ++j) { q[j] = p[56 + j]; cc[j] = c[56 + j]; } break;
+#undef TC_CASE
+    }
+    tc_col_group(q, cc, thrq, col_base + g * TC_GROUP, pq, row, col_key, col_thr);
+  }
+}
+
 // finds the work item that owns query tile `tile` (tile_begin is ascending; n_work >= 1)
 __device__ __forceinline__ int tc_find_work(const TcWork* __restrict__ work, int n_work, int tile) {
   int lo = 0, hi = n_work - 1;
@@ -480,7 +558,16 @@ __device__ __forceinline__ int tc_find_work(const TcWork* __restrict__ work, int
 // warpgroups drain every accumulator, wg 0 its columns [0, 128) and wg 1 [128, 256): what stalls
 // the tensor pipe is the LATENCY of getting a buffer back (the MMA of tile g + 2 needs the
 // buffer of tile g while tile g + 1 runs), so each buffer is drained by all eight warps.
-template <int K>
+// Start tile of the train sweep of a fused cross-check item: CTA b starts at tile
+// (b * n_t) / gridDim.x and wraps around.  Without it all CTAs of a round sweep the train image in
+// lockstep, every column tile is first seen by ~148 query tiles AT ONCE and none of them finds a
+// settled column threshold; rotated, the CTA that reaches a column tile finds the thresholds of
+// all CTAs that passed it before.  The train image (12.8 MB expanded at 50 k rows) stays in L2.
+__device__ __forceinline__ int tc_rot_start(const TcWork& w, int n_t) {
+  return w.col_key ? (int)(((long long)blockIdx.x * n_t) / gridDim.x) : 0;
+}
+
+template <int K, bool COL>
 __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, uint32_t item, uint32_t& g,
                                                  int warp, int lane, uint32_t tmem_base,
                                                  uint64_t* acc_full, uint64_t* acc_empty, uint2* merge,
@@ -505,29 +592,68 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   r.my_slot = share + wg * TC_M + row_in_tile;
   r.tag = (item & 63u) << 10;
   r.heavy = (w.slot_src == nullptr);
+  r.slack = 0;
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
   *r.my_slot = 0;
   uint32_t pv1 = 0xFFFFFFFFu, pv2 = 0xFFFFFFFFu;   // peer values read one and two tiles ago (none yet)
+  const bool cols = COL && w.col_key != nullptr;   // uniform per item
+  const int rot = COL ? tc_rot_start(w, n_t) : 0;
+  // packed (64 * pq - 32) of this lane's row for the column test; rows that do not exist never flag
+  const uint32_t thrq = (row >= 0) ? (uint32_t)((r.pq * TC_QSCALE - 32) & 0xFFFF) * 0x10001u : 0x7FFF7FFFu;
   TC_PROF(r.p_wait = 0; r.p_pass1 = 0; r.p_pass2 = 0; r.p_nflag = 0; const long long p_t0 = clock64();)
   for (int t = 0; t < n_t; ++t, ++g) {
     const uint32_t buf = g % TC_ACC;
+    int te = t + rot;                 // train tile of this visit
+    if (te >= n_t) te -= n_t;
+    if (COL && rot != 0 && te == 0) {
+      // The sweep wraps: from here on every column has a LOWER train index than everything seen
+      // so far, so a column that only EQUALS the row's best must get through once (lowest index
+      // wins the tie).  Non-strict from here to the end of the item (tc_publish).
+      r.thr -= 1;
+      r.slack = 1;
+    }
     TC_PROF(const long long c_w = clock64();)
     const uint32_t pv = *reinterpret_cast<const volatile uint16_t*>(peer_slot);
     tc_peer_bound(r, pv, 1);
-    if (TC_PEER_AGED) {
+    if (TC_PEER_AGED && !(COL && rot != 0)) {   // the aged form relies on tiles arriving in index order
       tc_peer_bound(r, wg ? pv1 : pv2, 0);   // wg 1's columns follow wg 0's of the same tile: one tile suffices
       pv2 = pv1;
       pv1 = pv;
+    }
+    const uint32_t col_base = (uint32_t)te * TC_N + wg * TC_HALF;
+    // column thresholds of this half tile: issued before the wait so that the L2 round trip hides
+    // behind the MMA of the tile (all lanes read the same 256 bytes)
+    uint32_t c[TC_HALF / 2];
+    if (COL) {
+      if (cols) {
+        const uint4* src = reinterpret_cast<const uint4*>(w.col_thr + col_base);
+#pragma unroll
+        for (int i = 0; i < TC_HALF / 8; ++i) {
+          const uint4 v = __ldcg(src + i);
+          c[4 * i] = v.x; c[4 * i + 1] = v.y; c[4 * i + 2] = v.z; c[4 * i + 3] = v.w;
+        }
+      }
     }
     tc_wait(&acc_full[buf], (g / TC_ACC) & 1u);
     tc_fence_after();
     TC_PROF(const long long c_s = clock64(); r.p_wait += c_s - c_w;)
     const uint32_t taddr = taddr0 + buf * TC_N;
-    const uint32_t col_base = (uint32_t)t * TC_N + wg * TC_HALF;
-    if (t == n_t - 1 && (w.nt % TC_N) != 0)
-      tc_tile<K, true>(taddr, col_base, (uint32_t)w.nt, r, &acc_empty[buf], lane);
+    // The accumulator goes back to the MMA issuer as soon as its 128 columns sit in registers (held
+    // for one TMEM load); everything below runs on the registers while the tensor pipe already
+    // fills the buffer again.
+    uint32_t p[TC_HALF / 2];
+    tc_ld128_packed(taddr, p);
+    tc_wait_ld(p);
+    tc_release(&acc_empty[buf], lane);
+#if TC_EXPERIMENT != 1
+    if (COL) {
+      if (cols) tc_cols(p, c, thrq, col_base, r.pq, row, w.col_key, w.col_thr);
+    }
+    if (te == n_t - 1 && (w.nt % TC_N) != 0)
+      tc_tile<K, true>(p, col_base, (uint32_t)w.nt, r, lane);
     else
-      tc_tile<K, false>(taddr, col_base, (uint32_t)w.nt, r, &acc_empty[buf], lane);
+      tc_tile<K, false>(p, col_base, (uint32_t)w.nt, r, lane);
+#endif
     TC_PROF(r.p_pass1 += clock64() - c_s;)
   }
   TC_PROF(if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 5) && item < 3)
@@ -553,7 +679,7 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
 }
 
 // ---- 1-CTA kernel ----------------------------------------------------------------------------------
-template <int K>
+template <int K, bool COL>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_tiles,
                        int4* __restrict__ best2, int* __restrict__ error_flag) {
@@ -658,14 +784,17 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
       }
       if (lane == 0) {
         const int n_t = (w.nt + TC_N - 1) / TC_N;
+        const int rot = COL ? tc_rot_start(w, n_t) : 0;   // the epilogue walks the same order
         for (int t = 0; t < n_t; ++t, ++g) {
           const uint32_t s = g % TC_STAGES;
           const uint32_t ph = (g / TC_STAGES) & 1u;
+          int te = t + rot;
+          if (te >= n_t) te -= n_t;
           tc_wait(&b_empty[s], ph ^ 1u);
           mbar_arrive_expect_tx(&b_full[s], TC_B_BYTES);
           uint8_t* dst = sB + (size_t)s * TC_B_BYTES;
-          tma_bulk_g2s(dst, w.t_exp + (size_t)t * (TC_N * 128), TC_N * 128, &b_full[s]);
-          tma_bulk_g2s(dst + TC_N * 128, w.t_exp + (size_t)w.t_rows_pad * 128 + (size_t)t * (TC_N * 128),
+          tma_bulk_g2s(dst, w.t_exp + (size_t)te * (TC_N * 128), TC_N * 128, &b_full[s]);
+          tma_bulk_g2s(dst + TC_N * 128, w.t_exp + (size_t)w.t_rows_pad * 128 + (size_t)te * (TC_N * 128),
                        TC_N * 128, &b_full[s]);
         }
       }
@@ -741,8 +870,8 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
     uint32_t g = 0, item = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
       const TcWork w = work[tc_find_work(work, n_work, tile)];
-      tc_epilogue_item<K>(w, tile - w.tile_begin, item, g, warp, lane, tmem_base, acc_full,
-                                 acc_empty, merge, share, best2);
+      tc_epilogue_item<K, COL>(w, tile - w.tile_begin, item, g, warp, lane, tmem_base, acc_full,
+                               acc_empty, merge, share, best2);
     }
   }
 
@@ -798,8 +927,10 @@ static cudaError_t tc_launch(ssp_ctx* ctx, Kern kern, size_t smem, int grid, int
   return cudaGetLastError();
 }
 
+// wait = false: nothing is read back here; the caller reads ctx->h_tc_err (non-zero: the dynamic
+// shared memory window was not 1024-byte aligned) after its own synchronise.
 cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& work, int k,
-                                  std::string* why_not) {
+                                  std::string* why_not, bool wait) {
   cudaError_t e = ensure_expanded(ctx);
   if (e != cudaSuccess) return e;
   if ((reinterpret_cast<uintptr_t>(ctx->h_expanded.p) & 15) != 0) {
@@ -809,6 +940,9 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
   std::vector<TcWork> tw;
   tw.reserve(work.size());
   int total = 0;  // query tiles
+  bool cols = false;
+  if ((e = ctx->h_tc_err.ensure(sizeof(int))) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(ctx->h_tc_err.p, 0, sizeof(int), ctx->stream)) != cudaSuccess) return e;
   for (const HammingWork& w : work) {
     if (w.nq <= 0 || w.nt <= 0) continue;  // rows of such items keep the "no neighbour" memset
     TcWork t;
@@ -824,6 +958,9 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
     t.slot_src = w.slot_src;
     t.tile_begin = total;
     t.pad_ = 0;
+    t.col_key = w.col_key;
+    t.col_thr = w.col_thr;
+    cols = cols || (w.col_key != nullptr);
     const int tiles = w.slot_src ? w.q_tiles : (w.nq + TC_M - 1) / TC_M;
     if (tiles <= 0) continue;
     total += tiles;
@@ -831,24 +968,29 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
   }
   if (tw.empty()) {
     if ((e = cudaEventRecord(ctx->ev0, ctx->stream)) != cudaSuccess) return e;
-    return cudaEventRecord(ctx->ev1, ctx->stream);
+    if ((e = cudaEventRecord(ctx->ev1, ctx->stream)) != cudaSuccess) return e;
+    // a caller that waits may read the elapsed time of ev0/ev1 right away
+    return wait ? cudaStreamSynchronize(ctx->stream) : cudaSuccess;
   }
   if ((e = ctx->h_tc_work.ensure(tw.size() * sizeof(TcWork))) != cudaSuccess) return e;
-  if ((e = ctx->h_tc_err.ensure(sizeof(int))) != cudaSuccess) return e;
   if ((e = cudaMemcpyAsync(ctx->h_tc_work.p, tw.data(), tw.size() * sizeof(TcWork),
                            cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
     return e;
-  if ((e = cudaMemsetAsync(ctx->h_tc_err.p, 0, sizeof(int), ctx->stream)) != cudaSuccess) return e;
   // the caller's ev0 marks the whole variant; re-record it here so that main_kernel_ms times the
   // tcgen05 kernel alone (bank expansion happens once per upload, outside)
   if ((e = cudaEventRecord(ctx->ev0, ctx->stream)) != cudaSuccess) return e;
   const int n_work = (int)tw.size();
   const int grid = total < ctx->sm_count ? total : ctx->sm_count;
-  e = (k == 2) ? tc_launch(ctx, hamming_tcgen05_kernel<2>, TC_SMEM_BYTES, grid, n_work, total)
-               : tc_launch(ctx, hamming_tcgen05_kernel<1>, TC_SMEM_BYTES, grid, n_work, total);
+  if (k == 2)
+    e = tc_launch(ctx, hamming_tcgen05_kernel<2, false>, TC_SMEM_BYTES, grid, n_work, total);
+  else if (cols)
+    e = tc_launch(ctx, hamming_tcgen05_kernel<1, true>, TC_SMEM_BYTES, grid, n_work, total);
+  else
+    e = tc_launch(ctx, hamming_tcgen05_kernel<1, false>, TC_SMEM_BYTES, grid, n_work, total);
   if (e != cudaSuccess) return e;
   if ((e = cudaEventRecord(ctx->ev1, ctx->stream)) != cudaSuccess) return e;
   ctx->h_launches += 1;
+  if (!wait) return cudaSuccess;
   int flag = 0;
   if ((e = cudaMemcpyAsync(&flag, ctx->h_tc_err.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream)) !=
       cudaSuccess)

@@ -5,7 +5,6 @@ computation happens in the hand-written CUDA kernels behind `include/ssp_b200.h`
 """
 import ctypes
 from dataclasses import dataclass
-from fractions import Fraction
 from typing import Optional, Sequence
 
 import numpy as np
@@ -53,18 +52,19 @@ _VARIANTS = {"auto": N.HAMMING_AUTO, "popc": N.HAMMING_POPC, "popc_csa": N.HAMMI
              "tensor": N.HAMMING_TENSOR}
 
 
-def _ratio_terms(ratio):
-    """Lowe ratio as an exact integer fraction (0.75 -> (3, 4))."""
+def _ratio_value(ratio):
+    """Lowe ratio as the float64 the reference multiplies with (`m.distance < 0.75 * n.distance`,
+    custom_bruteforce_matcher.py:164); a (num, den) pair means num / den.  The device evaluates
+    float64(d1) < ratio * float64(d2), which IS Python's comparison for any ratio."""
     if isinstance(ratio, (tuple, list)):
         num, den = int(ratio[0]), int(ratio[1])
-    else:
-        fr = Fraction(ratio)
-        if fr.denominator >= 1 << 20:
-            fr = Fraction(ratio).limit_denominator(4096)
-        num, den = fr.numerator, fr.denominator
-    if num <= 0 or den <= 0:
+        if num <= 0 or den <= 0:
+            raise ValueError("ratio must be positive")
+        return num / den
+    r = float(ratio)
+    if not r > 0.0:
         raise ValueError("ratio must be positive")
-    return num, den
+    return r
 
 
 def _ptr(a):
@@ -222,10 +222,9 @@ class Engine:
         if self._desc_offsets is None:
             raise EngineError("no descriptor bank uploaded")
         p = _as_pairs(pairs)
-        num, den = _ratio_terms(ratio)
         offs = np.zeros(p.shape[0] + 1, dtype=np.int64)
-        self._check(self._lib.ssp_hamming_match_pairs(
-            self._ctx, _ptr(p), p.shape[0], _MODES[mode], num, den, _VARIANTS[variant], _ptr(offs)))
+        self._check(self._lib.ssp_hamming_match_pairs_f64(
+            self._ctx, _ptr(p), p.shape[0], _MODES[mode], _ratio_value(ratio), _VARIANTS[variant], _ptr(offs)))
         n = int(offs[-1])
         if pinned and fetch:
             q, t, d = (self.pinned_array(k, n, np.int32) for k in ("hq", "ht", "hd"))

@@ -200,3 +200,89 @@ def test_pinned_results_and_fetch_into_equal_plain_fetch(engine):
         for a, b in zip((plain.query_idx, plain.train_idx, plain.distance), bufs):
             np.testing.assert_array_equal(a, b)
     assert plain.offsets[-1] > 0
+
+
+# ---- round 2: the three forms of the tensor variant's cross-check, larger multi-item cases ----------
+
+CROSS_FORMS = ["fused", "sparse", "dense"]
+
+
+@pytest.fixture
+def cross_form(monkeypatch):
+    def use(form):
+        monkeypatch.setenv("SSP_B200_CROSSCHECK", form)   # read per call by libssp_b200.so
+    return use
+
+
+@pytest.mark.parametrize("form", CROSS_FORMS)
+def test_crosscheck_forms_on_ragged_tie_stress(engine, cross_form, form):
+    """Every form against the oracle on tie-heavy ragged sets, including pairs in both orders where
+    one image has no rows at all (forward launch empty, reverse work present: ADVICE r1)."""
+    cross_form(form)
+    sizes = [0, 1, 7, 128, 129, 255, 256, 257, 700, 1500, 2100]
+    tie = synth.tie_stress_bank(len(sizes), max(sizes), seed=17)
+    sets = [tie[i][:n] for i, n in enumerate(sizes)]
+    pairs = [(i, j) for i in range(len(sizes)) for j in range(len(sizes)) if i != j]
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs(pairs, mode="crosscheck", variant="tensor")
+    assert_result_equals(res, oracle_pairs(sets, pairs, "crosscheck"))
+    only_empty_queries = [(0, 9), (9, 0), (0, 10), (10, 0)]
+    res = engine.hamming_match_pairs(only_empty_queries, mode="crosscheck", variant="tensor")
+    assert res.offsets.tolist() == [0, 0, 0, 0, 0]
+
+
+@pytest.mark.parametrize("form", CROSS_FORMS)
+def test_crosscheck_forms_tie_stress_over_many_tiles_and_items(engine, cross_form, form):
+    """Ties across many train tiles AND several work items per CTA: 5 images x 9 000 tie-heavy rows,
+    all 20 ordered pairs = 1 420 query tiles over 148 CTAs.  In the fused form the train sweep of
+    every CTA is rotated, so equal distances arrive in every index order."""
+    cross_form(form)
+    sets = synth.tie_stress_bank(5, 9000, seed=23)
+    pairs = [(i, j) for i in range(5) for j in range(5) if i != j]
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs(pairs, mode="crosscheck", variant="tensor")
+    assert_result_equals(res, oracle_pairs(sets, pairs, "crosscheck"))
+
+
+@pytest.mark.parametrize("mode", ["crosscheck", "knn2_ratio"])
+def test_c5_sized_items_20k_several_items_per_cta(engine, mode):
+    """BASELINE configs[4] shape: 20 000 x 20 000 items (79 train tiles, where warps spend most of an
+    item settling their thresholds), 4 images -> 6 pairs -> 942 query tiles, 6+ items per CTA."""
+    sets = synth.descriptor_bank(4, 20_000, seed=1, world=60_000)
+    pairs = synth.all_pairs(4)
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs(pairs, mode=mode, return_best2=(mode == "knn2_ratio"))
+    assert_result_equals(res, oracle_pairs(sets, pairs, mode))
+    if mode == "knn2_ratio":
+        for p, (a, b) in enumerate(pairs[:2]):
+            lo, hi = res.best2_offsets[p], res.best2_offsets[p + 1]
+            np.testing.assert_array_equal(res.best2[lo:hi], ho.knn2(sets[a], sets[b]))
+    assert res.offsets[-1] > 1000
+
+
+@pytest.mark.parametrize("mode", ["crosscheck", "knn2_ratio"])
+def test_full_size_tie_stress_pair_50k(engine, mode):
+    """50 000 x 50 000 rows drawn from a 2-bit-per-byte alphabet with exact duplicates: thousands of
+    equal distances per row and per column, at the headline size."""
+    sets = synth.tie_stress_bank(2, 50_000, seed=29)
+    engine.upload_descriptor_bank(sets)
+    res = engine.hamming_match_pairs([(0, 1)], mode=mode, return_best2=(mode == "knn2_ratio"))
+    assert_result_equals(res, oracle_pairs(sets, [(0, 1)], mode))
+    if mode == "knn2_ratio":
+        np.testing.assert_array_equal(res.best2, ho.knn2(sets[0], sets[1]))
+
+
+def test_ratio_is_pythons_float64_comparison_for_any_ratio(engine):
+    """`m.distance < ratio * n.distance` (custom_bruteforce_matcher.py:164) for ratios that have no
+    small rational form; 0.7000001 keeps (7, 10), which a rounded 7/10 would reject."""
+    sets = synth.descriptor_bank(2, 3000, seed=31, world=3500)
+    engine.upload_descriptor_bank(sets)
+    for ratio in (0.75, 0.7000001, 0.1, 1.0 / 3.0, 0.9999999999, 0.8):
+        res = engine.hamming_match_pairs([(0, 1)], mode="knn2_ratio", ratio=ratio, return_best2=True)
+        b = res.best2
+        keep = [i for i in range(len(b)) if b[i, 2] >= 0 and float(np.float32(b[i, 1])) < ratio * float(np.float32(b[i, 3]))]
+        np.testing.assert_array_equal(res.query_idx, np.array(keep, dtype=np.int32), err_msg=str(ratio))
+    # the integer entry point is the same test with ratio = num / den
+    res = engine.hamming_match_pairs([(0, 1)], mode="knn2_ratio", ratio=(7, 10), return_best2=True)
+    keep = [i for i in range(len(res.best2)) if res.best2[i, 2] >= 0 and float(res.best2[i, 1]) < 0.7 * float(res.best2[i, 3])]
+    np.testing.assert_array_equal(res.query_idx, np.array(keep, dtype=np.int32))

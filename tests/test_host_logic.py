@@ -6,18 +6,19 @@ import pytest
 
 import ssp_b200
 from ssp_b200 import synthetic as synth
-from ssp_b200.engine import Engine, _ratio_terms
+from ssp_b200.engine import Engine, _ratio_value
 from ssp_b200.distributed import shard_pairs
 from ssp_b200.custom_bf_polygon_matcher import disc_offsets
 
 
-def test_ratio_terms():
-    assert _ratio_terms(0.75) == (3, 4)
-    assert _ratio_terms(0.5) == (1, 2)
-    assert _ratio_terms((7, 10)) == (7, 10)
-    assert _ratio_terms(0.7) == (7, 10)
+def test_ratio_value_is_the_float_the_reference_multiplies_with():
+    assert _ratio_value(0.75) == 0.75
+    assert _ratio_value((7, 10)) == 0.7
+    assert _ratio_value(0.7000001) == 0.7000001   # no rational approximation any more
     with pytest.raises(ValueError):
-        _ratio_terms(0.0)
+        _ratio_value(0.0)
+    with pytest.raises(ValueError):
+        _ratio_value(float("nan"))
 
 
 def test_pack_descriptors_handles_ragged_and_empty():
