@@ -104,15 +104,27 @@ struct TcWork {              // one directed image pair
 };
 
 // ---- bank expansion ---------------------------------------------------------------------------
-// one thread per (padded row, 16-byte output chunk); `out` = query encoding, `out + enc_stride`
-// = train encoding of the same image
+// one thread per (padded row, 16-byte output chunk) of image blockIdx.y; per image the query encoding
+// sits at out_off and the train encoding rows_pad * 256 bytes behind it.  ONE launch for the whole
+// bank (round 1 launched once per image: 21 launches in front of every end-to-end step).
+struct ExpandImg {
+  long long row0;      // first row of the image in the packed bank
+  long long out_off;   // byte offset of the image in the expanded bank
+  int n_rows, rows_pad;
+};
 __global__ void __launch_bounds__(256)
-expand_bank_kernel(const uint8_t* __restrict__ packed, int n_rows, int rows_pad,
-                   uint8_t* __restrict__ out, size_t enc_stride, int* __restrict__ popc) {
+expand_bank_kernel(const uint8_t* __restrict__ bank, const ExpandImg* __restrict__ imgs,
+                   uint8_t* __restrict__ out_base, int* __restrict__ popc_base) {
+  const ExpandImg im = imgs[blockIdx.y];
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int row = (int)(gid >> 4);
   const int c = (int)(gid & 15);
+  const int n_rows = im.n_rows, rows_pad = im.rows_pad;
   if (row >= rows_pad) return;
+  const uint8_t* packed = bank + (size_t)im.row0 * 32;
+  uint8_t* out = out_base + im.out_off;
+  const size_t enc_stride = (size_t)rows_pad * 256;
+  int* popc = popc_base + im.row0;
   uint4 vq = make_uint4(0, 0, 0, 0), vt = make_uint4(0, 0, 0, 0);
   if (row < n_rows) {
     const uint32_t bits = (uint32_t)packed[(size_t)row * 32 + c * 2] |
@@ -901,18 +913,35 @@ static cudaError_t ensure_expanded(ssp_ctx* ctx) {
   cudaError_t e = ctx->h_expanded.ensure((size_t)ctx->exp_byte_off[n_images] + 1024);
   if (e != cudaSuccess) return e;
   if ((e = ctx->h_popc.ensure(((size_t)ctx->row_off[n_images] + 1) * sizeof(int))) != cudaSuccess) return e;
+  std::vector<ExpandImg> imgs;
+  int max_pad = 0;
   for (int i = 0; i < n_images; ++i) {
-    const int n = (int)(ctx->row_off[i + 1] - ctx->row_off[i]);
     const int pad = ctx->exp_rows_pad[i];
     if (pad == 0) continue;
-    const long long threads = (long long)pad * 16;
-    expand_bank_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(
-        ctx->d_desc + (size_t)ctx->row_off[i] * 32, n, pad,
-        ctx->h_expanded.as<uint8_t>() + ctx->exp_byte_off[i], (size_t)pad * TC_ROW_BYTES,
-        ctx->h_popc.as<int>() + ctx->row_off[i]);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    ctx->h_launches += 1;
+    ExpandImg im;
+    im.row0 = ctx->row_off[i];
+    im.out_off = ctx->exp_byte_off[i];
+    im.n_rows = (int)(ctx->row_off[i + 1] - ctx->row_off[i]);
+    im.rows_pad = pad;
+    imgs.push_back(im);
+    max_pad = pad > max_pad ? pad : max_pad;
+  }
+  if (!imgs.empty()) {
+    NvtxRange range("expand descriptor bank");
+    if ((e = ctx->h_tc_work.ensure(imgs.size() * sizeof(ExpandImg))) != cudaSuccess) return e;
+    // pageable source: the runtime stages it before returning, `imgs` may go out of scope
+    if ((e = cudaMemcpyAsync(ctx->h_tc_work.p, imgs.data(), imgs.size() * sizeof(ExpandImg),
+                             cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
+      return e;
+    const long long threads = (long long)max_pad * 16;
+    for (size_t first = 0; first < imgs.size(); first += 65535) {   // gridDim.y limit
+      const size_t n = imgs.size() - first < 65535 ? imgs.size() - first : 65535;
+      expand_bank_kernel<<<dim3((unsigned)((threads + 255) / 256), (unsigned)n), 256, 0, ctx->stream>>>(
+          ctx->d_desc, ctx->h_tc_work.as<ExpandImg>() + first, ctx->h_expanded.as<uint8_t>(),
+          ctx->h_popc.as<int>());
+      if ((e = cudaGetLastError()) != cudaSuccess) return e;
+      ctx->h_launches += 1;
+    }
   }
   ctx->h_expanded_valid = true;
   return cudaSuccess;

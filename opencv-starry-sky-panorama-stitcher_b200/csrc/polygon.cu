@@ -697,7 +697,8 @@ int ssp_polygon_fetch(ssp_ctx* ctx, int image, int32_t* star_idx, double* angle,
       SSP_CUDA_TRY(ctx, cudaMemcpyAsync(brightness, pi.bright.p, (size_t)n * 40, kind, ctx->stream));
     if (feat) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(feat, pi.feat.p, (size_t)n * 120, kind, ctx->stream));
   }
-  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  // device destinations are stream-ordered with whatever the caller enqueues next on this stream
+  if (mem_kind != SSP_MEM_DEVICE) SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return SSP_OK;
 }
 
@@ -725,7 +726,7 @@ int ssp_polygon_upload_features(ssp_ctx* ctx, int image, const double* feat,
   } else {
     pi.star_idx.release();
   }
-  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (mem_kind != SSP_MEM_DEVICE) SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // host source may be a temporary
   pi.count = n_polygons;
   pi.has_raw = false;
   ctx->p_n_matches = -1;

@@ -282,6 +282,17 @@ class Engine:
         self._star_offsets = offs
         self.star_owner = owner
 
+    def upload_star_bank_resident(self, xy_ptr: int, brightness_ptr: int, star_offsets, img_w: int, img_h: int,
+                                  focal_px: float, owner=None):
+        """`upload_star_bank` for float64 arrays already on this device (e.g. the receive buffer of
+        an NCCL broadcast): xy (N, 2) and brightness (N,), images back to back per `star_offsets`."""
+        offs = np.ascontiguousarray(star_offsets, dtype=np.int64)
+        self._check(self._lib.ssp_upload_star_bank(self._ctx, ctypes.c_void_p(xy_ptr), ctypes.c_void_p(brightness_ptr),
+                                                   _ptr(offs), len(offs) - 1, int(img_w), int(img_h),
+                                                   float(focal_px), N.MEM_DEVICE))
+        self._star_offsets = offs.copy()
+        self.star_owner = owner
+
     def star_rays(self):
         n = int(self._star_offsets[-1])
         rays = np.empty((n, 3), dtype=np.float64)
@@ -330,6 +341,21 @@ class Engine:
             _ptr(out.get("brightness")), _ptr(out["feat"]), n, N.MEM_HOST))
         return out
 
+    def polygon_fetch_resident(self, image: int, star_idx_ptr: int, feat_ptr: int, capacity: int):
+        """Copies the stored polygons of one image device -> device: int32 (P, 5) star indices and
+        float64 (P, 15) normalised features (either address may be 0)."""
+        self._check(self._lib.ssp_polygon_fetch(
+            self._ctx, int(image), ctypes.c_void_p(star_idx_ptr or None), None, None, None,
+            ctypes.c_void_p(feat_ptr or None), int(capacity), N.MEM_DEVICE))
+
+    def polygon_upload_features_resident(self, image: int, feat_ptr: int, star_idx_ptr: int, n_polygons: int,
+                                         owner=None):
+        """`polygon_upload_features` from device memory (the all-gathered banks of other ranks)."""
+        self.poly_owner[int(image)] = owner
+        self._check(self._lib.ssp_polygon_upload_features(
+            self._ctx, int(image), ctypes.c_void_p(feat_ptr), ctypes.c_void_p(star_idx_ptr or None),
+            int(n_polygons), N.MEM_DEVICE))
+
     def polygon_upload_features(self, image: int, feat, star_idx=None, owner=None):
         self.poly_owner[int(image)] = owner
         f = np.ascontiguousarray(np.asarray(feat, dtype=np.float64).reshape(-1, 15))
@@ -371,6 +397,13 @@ class Engine:
                                                            N.MEM_HOST))
             res.argmin, res.mindist, res.row_offsets = am, mn, r_off
         return res
+
+    def polygon_fetch_into(self, p1_ptr: int, p2_ptr: int, dist_ptr: int, capacity: int, device: bool = True):
+        """Copies the matches of the last `polygon_match_pairs(..., fetch=False)` into int32 / int32 /
+        float64 buffers given by address (device memory, or host memory)."""
+        self._check(self._lib.ssp_polygon_fetch_matches(
+            self._ctx, ctypes.c_void_p(p1_ptr), ctypes.c_void_p(p2_ptr), ctypes.c_void_p(dist_ptr),
+            int(capacity), N.MEM_DEVICE if device else N.MEM_HOST))
 
     def polygon_last_stats(self):
         n, ms, ev = ctypes.c_int(), ctypes.c_float(), ctypes.c_int64()
