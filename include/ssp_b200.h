@@ -206,6 +206,10 @@ int ssp_polygon_fetch_rowmin(ssp_ctx* ctx, int32_t* argmin, double* mindist,
                              int64_t capacity_rows, int mem_kind);
 int ssp_polygon_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
                            int64_t* evaluations);
+/* The parity compare prunes exactly (a column whose partial sum already reaches the row's best is
+ * dropped): flops it actually executed in the last call, counted on the device, or -1 when the
+ * kernel that ran does not count (fp32 / min-over-shifts / legacy). */
+int ssp_polygon_last_executed_flops(ssp_ctx* ctx, int64_t* executed_flops);
 
 /* ---- row N1: star brightness ----------------------------------------------------------
  * get_star_brightness (image_processors.py:222-254) for many stars of one image:

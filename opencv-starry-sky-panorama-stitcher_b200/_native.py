@@ -66,6 +66,7 @@ PROTOTYPES = {
     "ssp_polygon_fetch_rowmin": (_c.c_int, [_ctx_p, _i32p, _f64p, _c.c_int64, _c.c_int]),
     "ssp_polygon_last_stats": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_float),
                                           _c.POINTER(_c.c_int64)]),
+    "ssp_polygon_last_executed_flops": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int64)]),
     "ssp_star_brightness": (_c.c_int, [_ctx_p, _u8p, _c.c_int, _c.c_int, _i32p, _c.c_int64, _i32p,
                                        _c.c_int, _c.c_int, _i32p, _c.c_int]),
 }

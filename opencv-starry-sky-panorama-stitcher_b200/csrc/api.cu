@@ -82,7 +82,7 @@ int ssp_destroy(ssp_ctx* ctx) {
                          &ctx->p_tmp_idx,  &ctx->p_tmp_angle, &ctx->p_tmp_side,  &ctx->p_tmp_bright,
                          &ctx->p_tmp_feat, &ctx->p_pairs,     &ctx->p_argmin,    &ctx->p_mindist,
                          &ctx->p_counts,   &ctx->p_offsets,   &ctx->p_m1,        &ctx->p_m2,
-                         &ctx->p_md,       &ctx->b_img,       &ctx->b_xy,        &ctx->b_disc,
+                         &ctx->p_md,       &ctx->p_flops,     &ctx->b_img,       &ctx->b_xy,        &ctx->b_disc,
                          &ctx->b_out};
   for (ssp::DevBuf* b : bufs) b->release();
   for (ssp::PolyImage& pi : ctx->poly) {

@@ -353,6 +353,177 @@ poly_compare_f64_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ ar
   }
 }
 
+// FP64 parity kernel, shift 0, with COMPACTED pruning (round 2).  In the kernel above every lane
+// prunes against its own row's threshold, so after the first property group (which all 32 lanes
+// evaluate for every column) the warp drags 2-3 surviving lanes through the other two groups for
+// ~40 % of the columns: ncu showed 18.6 of 32 lanes active per FP64 instruction.  Here the first
+// group stays thread-per-row (row features in registers, column broadcast from shared memory),
+// but a survivor is only QUEUED: (row lane, column, first-group value) goes to a per-warp queue in
+// shared memory (ballot + prefix), and whenever 32 entries are waiting the warp evaluates them as one
+// dense batch -- lane i takes entry i, whatever row it belongs to (row features of the other two
+// groups sit in shared memory too).  An entry that beats its row's threshold is handed to the lane
+// that owns the row (shuffle broadcast, ascending lane = ascending column order per row, rare:
+// O(log P2) per row), which applies the sequential rule of the reference unchanged.  Thresholds
+// used for pruning are the row's own, possibly a few entries stale, i.e. never too small: exact.
+constexpr int PQ_TILE = 256;                 // columns per shared-memory tile
+constexpr int PQ_QUEUE = 64;                 // queue entries per warp (a batch runs as soon as 32 wait)
+constexpr int PQ_G2 = 3 - POLY_G0 - POLY_G1; // the third property group
+
+__global__ void __launch_bounds__(PC_THREADS)
+poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ argmin,
+                              double* __restrict__ mindist, unsigned long long* __restrict__ executed_flops) {
+  __shared__ __align__(16) double tile[PQ_TILE * 15];
+  __shared__ __align__(16) double rows_s[PC_THREADS * 10];     // groups POLY_G1 and PQ_G2 of every row of the CTA
+  __shared__ double thr_s[PC_THREADS];
+  __shared__ double q_g0[PC_THREADS / 32][PQ_QUEUE];
+  __shared__ int q_rc[PC_THREADS / 32][PQ_QUEUE];             // row lane << 16 | column in tile
+  const PolyPair pp = pairs[blockIdx.x];
+  const int row0 = blockIdx.y * PC_THREADS;
+  if (row0 >= pp.p1) return;
+  const int r = row0 + threadIdx.x;
+  const bool live = r < pp.p1;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  double a[15];
+#pragma unroll
+  for (int k = 0; k < 15; ++k) a[k] = live ? pp.f1[(long long)r * 15 + k] : 0.0;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    rows_s[threadIdx.x * 10 + k] = a[POLY_G1 * 5 + k];
+    rows_s[threadIdx.x * 10 + 5 + k] = a[PQ_G2 * 5 + k];
+  }
+  // a dead lane (row beyond p1) never passes the first test
+  double thr = live ? INFINITY : -1.0, best = INFINITY;
+  int best_c = 0;
+  thr_s[threadIdx.x] = thr;
+  unsigned flops = 0;
+  int q_n = 0;                                   // entries waiting in this warp's queue (warp-uniform)
+  double* my_g0 = q_g0[wid];
+  int* my_rc = q_rc[wid];
+  const double* my_rows = rows_s + wid * 32 * 10;
+  double* my_thr = thr_s + wid * 32;
+
+  // evaluates up to 32 queued entries [first, first + n) as one dense batch
+  auto run_batch = [&](int first, int n, int c0) {
+    double v = 0.0;
+    int rl = 0, col = 0;
+    bool cand = false;
+    if (lane < n) {
+      const int rc = my_rc[first + lane];
+      rl = rc >> 16;
+      col = rc & 0xFFFF;
+      const double g0 = my_g0[first + lane];
+      const double* b = tile + col * 15;
+      const double* ar = my_rows + rl * 10;
+      const double t = my_thr[rl];
+      double g1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const double d = __dsub_rn(ar[k], b[POLY_G1 * 5 + k]);
+        const double sq = __dmul_rn(d, d);
+        g1 = (k == 0) ? sq : __dadd_rn(g1, sq);
+      }
+      flops += 15;
+      if (__dadd_rn(g0, g1) < t) {
+        double g2 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const double d = __dsub_rn(ar[5 + k], b[PQ_G2 * 5 + k]);
+          const double sq = __dmul_rn(d, d);
+          g2 = (k == 0) ? sq : __dadd_rn(g2, sq);
+        }
+        flops += 16;
+        double g[3];
+        g[POLY_G0] = g0;
+        g[POLY_G1] = g1;
+        g[PQ_G2] = g2;
+        v = __dadd_rn(__dadd_rn(g[0], g[1]), g[2]);   // (angles + sides) + brightnesses, cbpm:1011-1016
+        cand = v < t;
+      }
+    }
+    // improvements go to the lane that owns the row, in ascending entry (= column) order
+    unsigned todo = __ballot_sync(0xffffffffu, cand);
+    while (todo) {
+      const int src = __ffs((int)todo) - 1;
+      todo &= todo - 1;
+      const int o_rl = __shfl_sync(0xffffffffu, rl, src);
+      const int o_col = __shfl_sync(0xffffffffu, col, src);
+      const double o_v = __shfl_sync(0xffffffffu, v, src);
+      if (lane == o_rl && o_v < thr) {
+        const double sv = sqrt(o_v);
+        if (sv < best) {
+          best = sv;
+          best_c = c0 + o_col;
+        }
+        thr = o_v;
+        my_thr[lane] = o_v;
+      }
+      __syncwarp();
+    }
+  };
+
+  for (int c0 = 0; c0 < pp.p2; c0 += PQ_TILE) {
+    const int ncol = min(PQ_TILE, pp.p2 - c0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < ncol * 15; i += PC_THREADS)
+      tile[i] = pp.f2[(long long)c0 * 15 + i];
+    __syncthreads();
+    for (int j = 0; j < ncol; ++j) {
+      const double* b = tile + j * 15;
+      double g0 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const double d = __dsub_rn(a[POLY_G0 * 5 + k], b[POLY_G0 * 5 + k]);
+        const double sq = __dmul_rn(d, d);
+        g0 = (k == 0) ? sq : __dadd_rn(g0, sq);
+      }
+      const bool pass = g0 < thr;
+      const unsigned m = __ballot_sync(0xffffffffu, pass);
+      if (m) {
+        if (pass) {
+          const int pos = q_n + __popc(m & ((1u << lane) - 1u));
+          my_g0[pos] = g0;
+          my_rc[pos] = (lane << 16) | j;
+        }
+        q_n += __popc(m);
+        __syncwarp();
+        if (q_n >= 32) {
+          run_batch(0, 32, c0);
+          // the (at most 31) entries behind the batch move to the front
+          const int rest = q_n - 32;
+          double mg = 0.0;
+          int mr = 0;
+          if (lane < rest) {
+            mg = my_g0[32 + lane];
+            mr = my_rc[32 + lane];
+          }
+          __syncwarp();
+          if (lane < rest) {
+            my_g0[lane] = mg;
+            my_rc[lane] = mr;
+          }
+          q_n = rest;
+          __syncwarp();
+        }
+      }
+    }
+    flops += live ? 14u * (unsigned)ncol : 0u;
+    // the tile is about to be overwritten: drain what is left
+    if (q_n > 0) {
+      run_batch(0, q_n, c0);
+      q_n = 0;
+      __syncwarp();
+    }
+  }
+  if (live) {
+    argmin[pp.out_row + r] = best_c;
+    mindist[pp.out_row + r] = best;
+  }
+  // flops executed by this warp (lane-level: pruned terms are not counted)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) flops += __shfl_xor_sync(0xffffffffu, flops, o);
+  if (lane == 0 && executed_flops) atomicAdd(executed_flops, (unsigned long long)flops);
+}
+
 // FP32 fast mode (non-parity): features converted on the fly, FMA accumulation.
 template <bool MIN_SHIFTS>
 __global__ void __launch_bounds__(PC_THREADS)
@@ -784,16 +955,33 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
   SSP_CUDA_TRY(ctx, ctx->p_offsets.ensure(((size_t)n_pairs + 1) * 8));
   SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_pairs.p, pp.data(), pp.size() * sizeof(PolyPair),
                                     cudaMemcpyHostToDevice, ctx->stream));
+  // matches: at most one per row of the first image, so the output arrays are sized up front and the
+  // call synchronises with the host once, at its end
+  SSP_CUDA_TRY(ctx, ctx->p_m1.ensure((size_t)(rows + 1) * 4));
+  SSP_CUDA_TRY(ctx, ctx->p_m2.ensure((size_t)(rows + 1) * 4));
+  SSP_CUDA_TRY(ctx, ctx->p_md.ensure((size_t)(rows + 1) * 8));
+  SSP_CUDA_TRY(ctx, ctx->p_flops.ensure(16));
+  SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->p_flops.p, 0, 16, ctx->stream));
+  ctx->p_executed_flops = -1;
+  bool counted = false;
   if (max_p1 > 0) {
+    NvtxRange range("kernel 3 (polygon compare)");
     dim3 grid((unsigned)n_pairs, (unsigned)((max_p1 + PC_THREADS - 1) / PC_THREADS));
     SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     const PolyPair* dp = ctx->p_pairs.as<PolyPair>();
     int* am = ctx->p_argmin.as<int>();
     double* md = ctx->p_mindist.as<double>();
     const bool ms = (shift_mode == SSP_SHIFT_MIN_OVER_SHIFTS);
+    const char* env = getenv("SSP_B200_POLY_COMPARE");   // "legacy": round 1's per-lane pruning (A/B)
+    const bool legacy = env && env[0] == 'l';
     if (precision == SSP_PRECISION_FP64) {
       if (ms) poly_compare_f64_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
-      else poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+      else if (legacy) poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+      else {
+        poly_compare_f64_queue_kernel<<<grid, PC_THREADS, 0, ctx->stream>>>(
+            dp, am, md, ctx->p_flops.as<unsigned long long>());
+        counted = true;
+      }
     } else {
       if (ms) poly_compare_f32_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
       else poly_compare_f32_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
@@ -802,27 +990,28 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
     SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->p_launches += 1;
   }
-  poly_count_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
-      ctx->p_pairs.as<PolyPair>(), ctx->p_mindist.as<double>(), threshold, ctx->p_counts.as<int>());
-  SSP_CUDA_TRY(ctx, cudaGetLastError());
-  scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->p_counts.as<int>(), n_pairs,
-                                                  ctx->p_offsets.as<long long>());
-  SSP_CUDA_TRY(ctx, cudaGetLastError());
-  ctx->p_launches += 2;
+  {
+    NvtxRange range("finalize (count, scan, compact)");
+    poly_count_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
+        ctx->p_pairs.as<PolyPair>(), ctx->p_mindist.as<double>(), threshold, ctx->p_counts.as<int>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->p_counts.as<int>(), n_pairs,
+                                                    ctx->p_offsets.as<long long>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    poly_compact_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
+        ctx->p_pairs.as<PolyPair>(), ctx->p_argmin.as<int>(), ctx->p_mindist.as<double>(), threshold,
+        ctx->p_offsets.as<long long>(), ctx->p_m1.as<int>(), ctx->p_m2.as<int>(),
+        ctx->p_md.as<double>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    ctx->p_launches += 3;
+  }
+  unsigned long long flops = 0;
   SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_match_offsets.data(), ctx->p_offsets.p,
                                     ((size_t)n_pairs + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&flops, ctx->p_flops.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   const long long total = ctx->p_match_offsets[(size_t)n_pairs];
-  SSP_CUDA_TRY(ctx, ctx->p_m1.ensure((size_t)(total + 1) * 4));
-  SSP_CUDA_TRY(ctx, ctx->p_m2.ensure((size_t)(total + 1) * 4));
-  SSP_CUDA_TRY(ctx, ctx->p_md.ensure((size_t)(total + 1) * 8));
-  poly_compact_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
-      ctx->p_pairs.as<PolyPair>(), ctx->p_argmin.as<int>(), ctx->p_mindist.as<double>(), threshold,
-      ctx->p_offsets.as<long long>(), ctx->p_m1.as<int>(), ctx->p_m2.as<int>(),
-      ctx->p_md.as<double>());
-  SSP_CUDA_TRY(ctx, cudaGetLastError());
-  ctx->p_launches += 1;
-  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (counted) ctx->p_executed_flops = (long long)flops;
   if (max_p1 > 0) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->p_main_ms, ctx->ev0, ctx->ev1));
   for (int p = 0; p <= n_pairs; ++p) match_offsets[p] = ctx->p_match_offsets[(size_t)p];
   ctx->p_n_matches = total;
@@ -861,6 +1050,12 @@ int ssp_polygon_fetch_rowmin(ssp_ctx* ctx, int32_t* argmin, double* mindist, int
   if (argmin) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(argmin, ctx->p_argmin.p, (size_t)n * 4, kind, ctx->stream));
   if (mindist) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(mindist, ctx->p_mindist.p, (size_t)n * 8, kind, ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+int ssp_polygon_last_executed_flops(ssp_ctx* ctx, int64_t* executed_flops) {
+  if (!ctx || !executed_flops) return SSP_ERR_INVALID;
+  *executed_flops = ctx->p_executed_flops;
   return SSP_OK;
 }
 

@@ -409,7 +409,10 @@ class Engine:
         n, ms, ev = ctypes.c_int(), ctypes.c_float(), ctypes.c_int64()
         self._check(self._lib.ssp_polygon_last_stats(self._ctx, ctypes.byref(n), ctypes.byref(ms),
                                                      ctypes.byref(ev)))
-        return {"launches": n.value, "main_kernel_ms": ms.value, "evaluations": ev.value}
+        fl = ctypes.c_int64()
+        self._check(self._lib.ssp_polygon_last_executed_flops(self._ctx, ctypes.byref(fl)))
+        return {"launches": n.value, "main_kernel_ms": ms.value, "evaluations": ev.value,
+                "executed_flops": fl.value if fl.value >= 0 else None}
 
     # -- row N1 ---------------------------------------------------------------------------
     def star_brightness(self, gray: np.ndarray, centers_xy, disc_dxdy, top_k: int = 10):
