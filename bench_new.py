@@ -637,7 +637,7 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
     def measure_all_local():
         for i in range(n_img):
             eng.polygon_measure_resident(i, cand_t[int(co[i]):].data_ptr(), int(co[i + 1] - co[i]), wait=False)
-        return 3 * n_img
+        return 2 * n_img   # measure + scatter per image
 
     kernel_ms = []
 
@@ -646,7 +646,7 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
         if measured:
             if world > 1:
                 measure_polygons_sharded(eng, so, co, xy_t, br_t, cand_t, IMG_W, IMG_H, FOCAL)
-                n += 3 * len(range(rank, n_img, world)) + 1
+                n += 2 * len(range(rank, n_img, world)) + 1
             else:
                 n += measure_all_local()
         res = eng.polygon_match_pairs(local_pairs, fp32=fp32, fetch=False)

@@ -90,6 +90,9 @@ int ssp_device_info(ssp_ctx* ctx, int* sm_count, int* sm_clock_khz, int64_t* hbm
  * MEM_HOST paths.  Free with ssp_host_free. */
 int ssp_host_alloc(ssp_ctx* ctx, int64_t bytes, void** host_ptr);
 int ssp_host_free(ssp_ctx* ctx, void* host_ptr);
+/* Copies `bytes` from an engine-owned device table (an address an entry point handed out, e.g.
+ * ssp_polygon_candidates) to host memory, ordered after the work queued on the context's stream. */
+int ssp_copy_to_host(ssp_ctx* ctx, void* host_dst, const void* device_src, int64_t bytes);
 
 /* ---- descriptor bank ------------------------------------------------------------------
  * Replaces the per-pair `ft.descriptors.get()[0:n_orb, :]` host slices handed to
@@ -210,6 +213,34 @@ int ssp_polygon_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
  * dropped): flops it actually executed in the last call, counted on the device, or -1 when the
  * kernel that ran does not count (fp32 / min-over-shifts / legacy). */
 int ssp_polygon_last_executed_flops(ssp_ctx* ctx, int64_t* executed_flops);
+
+/* ---- row N2: candidate generation ------------------------------------------------------
+ * The data-parallel parts of reduce_amount_of_keypoints_and_create_polygon_spanning_tuples_of_keypoints
+ * (cbpm:261-443) and reduce_amount_of_keypoints_by_clustering (cbpm:137-259); the Ward clustering
+ * (sklearn, cbpm:175-181) stays on the host and its labels are an input.
+ *
+ * ssp_star_regions: bit r of region_mask[i] = star i of `image` (star bank) lies in region r of
+ * cbpm:328-375, regions in the reference's dict order (left_top, left_bot, left_mid, right_top,
+ * right_bot, right_mid, top_left, top_right, top_mid, bot_left, bot_right, bot_mid); the strict
+ * float64 comparisons of the reference, evaluated in its order. */
+int ssp_star_regions(ssp_ctx* ctx, int image, uint16_t* region_mask, int64_t capacity);
+/* cbpm:230-245 for several regions at once: region g owns members[region_offsets[g] ..
+ * region_offsets[g+1]) (star ids of `image`, in the order the host clustered them) with their
+ * cluster labels (0 .. max_labels-1); survivors[g * max_labels + l] = the brightest star of cluster
+ * l of region g, the LAST listed among equally bright ones, or -1 for an unused label. */
+int ssp_cluster_brightest(ssp_ctx* ctx, int image, const int32_t* members, const int32_t* labels,
+                          const int32_t* region_offsets, int n_regions, int max_labels,
+                          int32_t* survivors);
+/* cbpm:407-413: the union over the 12 regions of all 5-combinations of each region's stars
+ * (region_members: the regions' ascending star ids back to back, region_counts[12]).  *n_unique =
+ * size of the union.  If 0 < *n_unique <= max_candidates and device_candidates != NULL the tuples
+ * are written to an engine-owned int32 (n, 5) table on the device -- region-major, lexicographic
+ * inside a region; a set listed by several regions belongs to the first -- and its address is
+ * returned for ssp_polygon_measure(..., SSP_MEM_DEVICE); otherwise *device_candidates = NULL (the
+ * host retries with fewer stars per region, as the reference's while loop does). */
+int ssp_polygon_candidates(ssp_ctx* ctx, const int32_t* region_members, const int32_t* region_counts,
+                           int n_regions, int64_t max_candidates, int64_t* n_unique,
+                           const int32_t** device_candidates);
 
 /* ---- row N1: star brightness ----------------------------------------------------------
  * get_star_brightness (image_processors.py:222-254) for many stars of one image:

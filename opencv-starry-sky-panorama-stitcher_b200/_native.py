@@ -40,6 +40,7 @@ PROTOTYPES = {
                                    _c.POINTER(_c.c_int64)]),
     "ssp_host_alloc": (_c.c_int, [_ctx_p, _c.c_int64, _c.POINTER(_c.c_void_p)]),
     "ssp_host_free": (_c.c_int, [_ctx_p, _vp]),
+    "ssp_copy_to_host": (_c.c_int, [_ctx_p, _vp, _vp, _c.c_int64]),
     "ssp_upload_descriptor_bank": (_c.c_int, [_ctx_p, _u8p, _i64p, _c.c_int, _c.c_int]),
     "ssp_bind_descriptor_bank": (_c.c_int, [_ctx_p, _u8p, _i64p, _c.c_int]),
     "ssp_hamming_match_pairs": (_c.c_int, [_ctx_p, _i32p, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
@@ -67,6 +68,10 @@ PROTOTYPES = {
     "ssp_polygon_last_stats": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_float),
                                           _c.POINTER(_c.c_int64)]),
     "ssp_polygon_last_executed_flops": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int64)]),
+    "ssp_star_regions": (_c.c_int, [_ctx_p, _c.c_int, _vp, _c.c_int64]),
+    "ssp_cluster_brightest": (_c.c_int, [_ctx_p, _c.c_int, _i32p, _i32p, _i32p, _c.c_int, _c.c_int, _i32p]),
+    "ssp_polygon_candidates": (_c.c_int, [_ctx_p, _i32p, _i32p, _c.c_int, _c.c_int64, _c.POINTER(_c.c_int64),
+                                          _c.POINTER(_c.c_void_p)]),
     "ssp_star_brightness": (_c.c_int, [_ctx_p, _u8p, _c.c_int, _c.c_int, _i32p, _c.c_int64, _i32p,
                                        _c.c_int, _c.c_int, _i32p, _c.c_int]),
 }

@@ -83,7 +83,7 @@ int ssp_destroy(ssp_ctx* ctx) {
                          &ctx->p_tmp_feat, &ctx->p_pairs,     &ctx->p_argmin,    &ctx->p_mindist,
                          &ctx->p_counts,   &ctx->p_offsets,   &ctx->p_m1,        &ctx->p_m2,
                          &ctx->p_md,       &ctx->p_flops,     &ctx->b_img,       &ctx->b_xy,        &ctx->b_disc,
-                         &ctx->b_out};
+                         &ctx->b_out,      &ctx->c_mask,      &ctx->c_work,      &ctx->c_blocks,    &ctx->c_cand};
   for (ssp::DevBuf* b : bufs) b->release();
   for (ssp::PolyImage& pi : ctx->poly) {
     pi.feat.release();
@@ -131,6 +131,17 @@ int ssp_host_free(ssp_ctx* ctx, void* host_ptr) {
   if (!host_ptr) return SSP_OK;
   if (int rc = ssp::use_device(ctx)) return rc;
   SSP_CUDA_TRY(ctx, cudaFreeHost(host_ptr));
+  return SSP_OK;
+}
+
+int ssp_copy_to_host(ssp_ctx* ctx, void* host_dst, const void* device_src, int64_t bytes) {
+  if (!ctx) return SSP_ERR_INVALID;
+  SSP_REQUIRE(ctx, bytes >= 0 && (bytes == 0 || (host_dst != nullptr && device_src != nullptr)), SSP_ERR_INVALID,
+              "ssp_copy_to_host: bad arguments");
+  if (int rc = ssp::use_device(ctx)) return rc;
+  if (bytes > 0)
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(host_dst, device_src, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return SSP_OK;
 }
 

@@ -166,6 +166,9 @@ struct ssp_ctx {
 
   // brightness scratch
   ssp::DevBuf b_img, b_xy, b_disc, b_out;
+
+  // candidate generation (row N2)
+  ssp::DevBuf c_mask, c_work, c_blocks, c_cand;
 };
 
 namespace ssp {

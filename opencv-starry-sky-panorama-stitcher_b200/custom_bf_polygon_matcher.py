@@ -80,7 +80,7 @@ class BFPolygonMatcher:
 
     def __init__(self, output_dir_polygon_matching, filename_img1, filename_img2, idx_img1, idx_img2,
                  img_shape, focal_length_pinhole, engine: Engine = None, write_debug_images=None,
-                 min_over_shifts=False, fp32=False):
+                 min_over_shifts=False, fp32=False, candidate_generation="host"):
         self.filename_img1 = filename_img1
         self.filename_img2 = filename_img2
         self.idx_img1 = idx_img1
@@ -91,6 +91,12 @@ class BFPolygonMatcher:
         self.write_debug_images = _debug_images_enabled(write_debug_images)
         self.min_over_shifts = min_over_shifts
         self.fp32 = fp32
+        # "host": the reference's own itertools / set() enumeration (parity: polygon ORDER decides
+        # DMatch order).  "device": regions, per-cluster selection and the C(k, 5) enumeration run
+        # on the GPU (row N2); the candidate SET is the reference's, its order is region-major.
+        if candidate_generation not in ("host", "device"):
+            raise ValueError("candidate_generation must be 'host' or 'device'")
+        self.candidate_generation = candidate_generation
         self.output_dir = os.path.join(output_dir_polygon_matching, f"{filename_img1}___{filename_img2}")
         if self.write_debug_images:
             os.makedirs(self.output_dir, exist_ok=True)
@@ -212,6 +218,40 @@ class BFPolygonMatcher:
             k -= 1
         return polygons
 
+    def device_candidates(self, sess, img_id, keypoints, workscale_img, n_polygon_sides=5,
+                          maximum_number_of_polygons_per_image_region=15000):
+        """cbpm:261-443 with everything but the Ward clustering on the GPU (row N2).  The star bank of
+        `img_id` must be on the engine (`sess.set_stars`).  Same reduction loop as the reference:
+        k = 15, 14, ... stars per region until the union of all C(region, 5) has between 1 and the
+        maximum number of tuples.  Returns (n candidates, device address of the int32 (n, 5) table,
+        stars kept per region)."""
+        from sklearn.cluster import AgglomerativeClustering
+        if n_polygon_sides != self.N_SIDES:
+            raise NotImplementedError("the candidate kernels enumerate 5-combinations (cbpm:704)")
+        eng = sess.engine
+        masks = eng.star_regions(img_id)
+        coords = np.array([kp.pt for kp in keypoints]).reshape(-1, 2)
+        regions = [np.nonzero(masks & (1 << r))[0].tolist() for r in range(12)]   # ascending ids, like filter()
+        k = self.START_STARS_PER_REGION
+        while True:
+            if k < 1:
+                raise ValueError("no image region is left with five stars: no polygon can be spanned")
+            todo = [r for r in range(12) if len(regions[r]) > k]
+            if todo:
+                members, labels, off = [], [], [0]
+                for r in todo:
+                    members += regions[r]
+                    labels += AgglomerativeClustering(n_clusters=k).fit(coords[regions[r]]).labels_.tolist()
+                    off.append(len(members))
+                surv = eng.cluster_brightest(img_id, members, labels, off, k)
+                for g, r in enumerate(todo):
+                    used = sorted(set(labels[off[g]:off[g + 1]]))        # `for cluster_id in unique_labels`
+                    regions[r] = [int(surv[g, lab]) for lab in used]
+            n, ptr = eng.polygon_candidates(regions, maximum_number_of_polygons_per_image_region)
+            if ptr:
+                return n, ptr, regions
+            k -= 1
+
     # ---- kernel 2 -----------------------------------------------------------------------
     def get_polygons_characteristics(self, keypoints, workscale_image, img_title, n_sides,
                                      all_possible_polygons, _img_id=None, _session=None):
@@ -250,6 +290,31 @@ class BFPolygonMatcher:
         out["_normalised_features"] = got["feat"]
         return out
 
+    def _measure_with_device_candidates(self, sess, img_id, stars, img):
+        """Row N2 + kernel 2 without a host round trip of the candidate table."""
+        xy = np.array([kp.pt for kp in stars], dtype=np.float64).reshape(-1, 2)
+        brightness = self.star_brightnesses(stars, img).astype(np.float64)
+        sess.set_stars(img_id, xy, brightness, img.shape, self.focal_length_pinhole)
+        eng = sess.engine
+        n, ptr, _ = self.device_candidates(sess, img_id, stars, img, self.N_SIDES, self.MAX_POLYGONS)
+        eng.poly_owner[img_id] = sess
+        eng.polygon_measure_resident(img_id, ptr, n, min_side_px=float(self.MIN_SIDE_PX))
+        eng.poly_owner[img_id] = sess      # polygon_measure_resident resets the owner
+        sess.on_device.add(img_id)
+        got = eng.polygon_fetch(img_id, raw=True)
+        idx = got["star_idx"].astype(np.int64)
+        polys = {
+            "keypoint_indices_rotated_list": idx,
+            "keypoint_x_coordinates_list": xy[idx, 0] if len(idx) else np.zeros((0, 5)),
+            "keypoint_y_coordinates_list": xy[idx, 1] if len(idx) else np.zeros((0, 5)),
+            "keypoint_angles_rotated_list": got["angle"],
+            "keypoint_brightnesses_rotated_list": got["brightness"],
+            "side_lengths_rotated_list": got["side"],
+            "_normalised_features": got["feat"],
+        }
+        cands = set(map(tuple, eng.copy_to_host(ptr, (n, 5), np.int32).tolist()))
+        return cands, polys
+
     def _prepare_image(self, sess, store, counter, img_id, keypoints, n_orb, img, filename, title):
         if img_id in store:
             entry = store[img_id]
@@ -264,10 +329,13 @@ class BFPolygonMatcher:
             return entry
         counter.append(img_id)
         stars = keypoints[n_orb:]  # ORB keypoints come first (cbpm:710)
-        cands = self.reduce_amount_of_keypoints_and_create_polygon_spanning_tuples_of_keypoints(
-            stars, filename, img, self.N_SIDES, self.MAX_POLYGONS)
-        polys = self.get_polygons_characteristics(stars, img, title, self.N_SIDES, cands,
-                                                  _img_id=img_id, _session=sess)
+        if self.candidate_generation == "device":
+            cands, polys = self._measure_with_device_candidates(sess, img_id, stars, img)
+        else:
+            cands = self.reduce_amount_of_keypoints_and_create_polygon_spanning_tuples_of_keypoints(
+                stars, filename, img, self.N_SIDES, self.MAX_POLYGONS)
+            polys = self.get_polygons_characteristics(stars, img, title, self.N_SIDES, cands,
+                                                      _img_id=img_id, _session=sess)
         feat = polys.pop("_normalised_features")
         # the reference normalises in place (cbpm:722-740); kernel 2 already did: angle / pi,
         # side / row max, brightness / row max

@@ -49,7 +49,7 @@ class CustomBruteForceMatcher:
                  disable_prompts=False, enforce_star_polygon_matcher=False,
                  output_dir_polygon_matching, predefined_overlaps, focal_length_pinhole,
                  engine: Engine = None, hamming_mode="crosscheck", hamming_variant="auto",
-                 write_debug_images=None, verbose=True):
+                 write_debug_images=None, verbose=True, polygon_candidate_generation="host"):
         self.imgs_features_orb_and_stars = imgs_features_orb_and_stars
         self.imgs_features_len_orb = imgs_features_len_orb
         self.conf_thresh = conf_thresh
@@ -76,6 +76,7 @@ class CustomBruteForceMatcher:
         self.hamming_variant = hamming_variant
         self.write_debug_images = _debug_images_enabled(write_debug_images)
         self.verbose = verbose
+        self.polygon_candidate_generation = polygon_candidate_generation  # "device": row N2 (BFPolygonMatcher)
         self._bank_generation = None  # Engine.bank_generation of MY upload
         self._orb_matches = dict()  # (src, dst) -> tuple of cv2.DMatch, filled by prefetch
 
@@ -230,7 +231,7 @@ class CustomBruteForceMatcher:
             filename_img1=self.img_names[src_idx], filename_img2=self.img_names[dst_idx],
             idx_img1=src_idx, idx_img2=dst_idx, img_shape=self.work_scale_imgs[src_idx].shape,
             focal_length_pinhole=self.focal_length_pinhole, engine=self.engine,
-            write_debug_images=self.write_debug_images)
+            write_debug_images=self.write_debug_images, candidate_generation=self.polygon_candidate_generation)
         matches = poly.match(ft1.keypoints, ft2.keypoints,
                              self.imgs_features_len_orb[src_idx], self.imgs_features_len_orb[dst_idx],
                              self.work_scale_imgs[src_idx], self.work_scale_imgs[dst_idx],

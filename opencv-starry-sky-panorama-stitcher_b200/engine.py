@@ -414,6 +414,44 @@ class Engine:
         return {"launches": n.value, "main_kernel_ms": ms.value, "evaluations": ev.value,
                 "executed_flops": fl.value if fl.value >= 0 else None}
 
+    # -- row N2 ---------------------------------------------------------------------------
+    def star_regions(self, image: int) -> np.ndarray:
+        """uint16 bit mask per star of `image`: membership in the 12 border regions of cbpm:328-375."""
+        n = int(self._star_offsets[image + 1] - self._star_offsets[image])
+        out = np.zeros(n, dtype=np.uint16)
+        self._check(self._lib.ssp_star_regions(self._ctx, int(image), _ptr(out), n))
+        return out
+
+    def cluster_brightest(self, image: int, members, labels, region_offsets, max_labels: int) -> np.ndarray:
+        """Brightest star per (region, cluster label), last of equals (cbpm:230-245); int32
+        (n_regions, max_labels), -1 for unused labels."""
+        m = np.ascontiguousarray(members, dtype=np.int32)
+        lab = np.ascontiguousarray(labels, dtype=np.int32)
+        off = np.ascontiguousarray(region_offsets, dtype=np.int32)
+        out = np.empty((len(off) - 1, int(max_labels)), dtype=np.int32)
+        self._check(self._lib.ssp_cluster_brightest(self._ctx, int(image), _ptr(m), _ptr(lab), _ptr(off),
+                                                    len(off) - 1, int(max_labels), _ptr(out)))
+        return out
+
+    def polygon_candidates(self, region_members: Sequence[Sequence[int]], max_candidates: int = 15000):
+        """Union of all 5-combinations of every region's stars (cbpm:407-413).  Returns (n_unique,
+        device address of the int32 (n, 5) table or None when n_unique is 0 or above the maximum)."""
+        counts = np.array([len(r) for r in region_members], dtype=np.int32)
+        flat = np.ascontiguousarray(np.concatenate([np.sort(np.asarray(r, dtype=np.int32)) for r in region_members])
+                                    if counts.sum() else np.zeros(0, np.int32))
+        n = ctypes.c_int64()
+        ptr = ctypes.c_void_p()
+        self._check(self._lib.ssp_polygon_candidates(self._ctx, _ptr(flat) if flat.size else ctypes.c_void_p(flat.ctypes.data),
+                                                     _ptr(counts), len(counts), int(max_candidates),
+                                                     ctypes.byref(n), ctypes.byref(ptr)))
+        return n.value, ptr.value
+
+    def copy_to_host(self, device_ptr: int, shape, dtype) -> np.ndarray:
+        """numpy copy of an engine-owned device table (e.g. the candidate table)."""
+        out = np.empty(shape, dtype=dtype)
+        self._check(self._lib.ssp_copy_to_host(self._ctx, _ptr(out), ctypes.c_void_p(device_ptr), out.nbytes))
+        return out
+
     # -- row N1 ---------------------------------------------------------------------------
     def star_brightness(self, gray: np.ndarray, centers_xy, disc_dxdy, top_k: int = 10):
         """get_star_brightness (image_processors.py:222-254) for many stars of one grey image."""

@@ -269,3 +269,77 @@ def test_no_wait_measure_of_a_batch_equals_the_waiting_form(engine):
     np.testing.assert_array_equal(res.argmin, ref.argmin)
     np.testing.assert_array_equal(res.mindist, ref.mindist)
     np.testing.assert_array_equal(res.offsets, ref.offsets)
+
+
+# ---- row N2: candidate generation on the device ------------------------------------------------------
+
+def _c2_frames(c2):
+    kps, imgs = [], []
+    for i in range(len(c2["names"])):
+        kps.append(tuple(cv2.KeyPoint(float(p[0]), float(p[1]), float(s))
+                         for p, s in zip(c2[f"i{i}_xy"], c2[f"i{i}_size"])))
+        imgs.append(cv2.cvtColor(c2[f"i{i}_gray"], cv2.COLOR_GRAY2BGR))
+    return kps, imgs
+
+
+def test_star_regions_kernel_equals_the_reference_region_filters(engine, golden):
+    """cbpm:328-375: 12 overlapping regions, strict float64 comparisons -- including stars placed
+    exactly ON the region borders."""
+    c2 = golden("eisenberg_c2.npz")
+    kps, imgs = _c2_frames(c2)
+    h, w = imgs[0].shape[:2]
+    xy = np.array([kp.pt for kp in kps[0]], dtype=np.float64)
+    border = np.array([[np.float32(0.33 * w), np.float32(0.70 * h)], [0.5 * w, 0.5 * h], [np.float32(0.67 * w), np.float32(0.3 * h)],
+                       [0.5 * w - 0.25 * w, 10.0], [0.5 * w + 0.25 * w, h - 10.0], [w * 0.33, h * 0.33]], dtype=np.float64)
+    xy = np.concatenate([xy, border.astype(np.float32).astype(np.float64)])
+    engine.upload_star_bank([xy], [np.ones(len(xy))], w, h, 1135.0)
+    masks = engine.star_regions(0)
+    bf = ssp_b200.BFPolygonMatcher("/tmp", "a", "b", 0, 1, imgs[0].shape, 1135, engine=engine, write_debug_images=False)
+    all_kps = tuple(cv2.KeyPoint(float(np.float32(p[0])), float(np.float32(p[1])), 4.0) for p in xy)
+    want = bf._regions(all_kps, w, h)
+    for r, name in enumerate(want):
+        assert np.nonzero(masks & (1 << r))[0].tolist() == want[name], name
+
+
+def test_cluster_brightest_kernel_keeps_the_last_of_equally_bright_stars(engine):
+    rng = np.random.default_rng(3)
+    n = 400
+    xy = rng.uniform(20, 800, size=(n, 2))
+    bright = rng.integers(2500, 2551, size=n).astype(np.float64)   # saturated stars: ties are the norm
+    engine.upload_star_bank([xy], [bright], 1342, 894, 1135.0)
+    members, labels, off = [], [], [0]
+    for g in range(5):
+        m = rng.permutation(n)[:60 + 10 * g].tolist()
+        members += m
+        labels += rng.integers(0, 15, size=len(m)).tolist()
+        off.append(len(members))
+    got = engine.cluster_brightest(0, members, labels, off, 15)
+    for g in range(5):
+        mem, lab = members[off[g]:off[g + 1]], labels[off[g]:off[g + 1]]
+        for label in range(15):
+            idx = [i for i in range(len(mem)) if lab[i] == label]
+            # cbpm:241: ascending stable sort by brightness, reversed, first element
+            want = sorted(((i, bright[mem[i]]) for i in idx), key=lambda x: x[1])[::-1][0][0] if idx else None
+            assert got[g, label] == (mem[want] if idx else -1)
+
+
+def test_device_candidate_generation_yields_the_reference_candidate_set(engine, golden, tmp_path):
+    """Row N2 on the 4 real eisenberg frames: the candidate SET per image equals the one the unchanged
+    reference enumerated (recorded), hence the same polygon set; matches and DMatches agree as sets."""
+    c2 = golden("eisenberg_c2.npz")
+    kps, imgs = _c2_frames(c2)
+    n = len(kps)
+    store, counter = {}, []
+    dm_sets = []
+    for p, (a, b) in enumerate(c2["pairs"]):
+        a, b = int(a), int(b)
+        bf = ssp_b200.BFPolygonMatcher(str(tmp_path), f"f{a}", f"f{b}", a, b, imgs[a].shape, 1135, engine=engine,
+                                       write_debug_images=False, candidate_generation="device")
+        dms = bf.match(kps[a], kps[b], 0, 0, imgs[a], imgs[b], store, a, b, counter)
+        assert {(m.queryIdx, m.trainIdx) for m in dms} == {tuple(x) for x in c2[f"p{p}_dmatches"].tolist()}, (a, b)
+    for i in range(n):
+        want = {tuple(sorted(c)) for c in c2[f"i{i}_candidates"].tolist()}
+        got = {tuple(sorted(c)) for c in store[i]["all_possible_polygons_ftX"]}
+        assert got == want and len(store[i]["all_possible_polygons_ftX"]) == len(want), i
+        ref_polys = {tuple(r) for r in c2[f"i{i}_norm_idx"].tolist()}
+        assert {tuple(r) for r in store[i]["polygons_from_ftX"]["keypoint_indices_rotated_list"].tolist()} == ref_polys
