@@ -2,25 +2,33 @@
 """bench.py — image pairs matched/s and G descriptor-comparisons/s of the pairwise matching stage.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--workload c3|c5|c1] [--mode knn2_ratio|crosscheck] [--variant auto|popc|popc_csa|tensor]
+                    [--workload c3|c5|c1|c4|c4cap|c1real] [--mode knn2_ratio|crosscheck]
+                    [--variant auto|popc|popc_csa|tensor] [--no-sub]
 
 One step = one pass of the hot path over the whole pair list of the workload (default C3:
 synthetic 21 images x 50 000 ORB descriptors, all 210 pairs, kNN k=2 + ratio test — the
 configuration BASELINE.json quotes its metric and its >=100x target on).  Prints ONE JSON line.
 
-  value     pairs/s with the descriptor bank already resident in HBM (CUDA events, max over ranks)
+  value     pairs/s with the banks already resident in HBM (CUDA events, max over ranks); a 256 MiB
+            device memset between steps flushes the L2
   e2e       the same through the public API with HOST buffers: pinned host bank -> device (+ NCCL
-            broadcast at N>1), match, survivors gathered and copied back to the host, every step
-  roofline  dominant kernel against the integer-pipe roofline of SURVEY.md §8(d) plus HBM GB/s
-  cpu_baseline  cv2.BFMatcher (the reference's own CPU call) on a bounded sample, rank 0, N=1
+            broadcast at N>1), match, results gathered to rank 0 and copied back to the host, every
+            step, over the SAME number of steps and with the same L2 flush as `value`
+  roofline  dominant kernel against the measured int8 tensor-pipe ceiling (profiles/int8_ceiling_*.json)
+  cpu_baseline  cv2.BFMatcher (the reference's own CPU call) on a bounded sample, rank 0, N=1; its
+            matches are compared with the GPU's for the same pairs ("parity_in_run")
+  sub       (default invocation only) the other configurations the path is judged on, each with its
+            own value / e2e / kernel_ms / roofline: C3 cross-check (the reference's LIVE call), C5
+            (19 900 pairs x 20 k, the pair-sharding configuration), C4 and C4 at the 15 000 cap
+            (star polygons, kernels 2 + 3)
 
 --impl reference times the reference's CPU implementation of the path (cv2.BFMatcher with all
 host threads, custom_bruteforce_matcher.py:160-172 / :193-199) on a bounded sample per step.
 """
 import argparse
+import glob
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -40,7 +48,7 @@ WORKLOADS = {
     # whole matcher stage of example_01b through the reference-facing class; see run_stage
     "c1real": dict(stage=True, name="example_01b: ORB(1000) descriptors of the 21 forest JPEGs (frozen fixture), "
                                     "CustomBruteForceMatcher.match_n_features, all 210 pairs incl. RANSAC + MatchesInfo"),
-    # star-polygon path (kernels 2 + 3); see run_polygon_*
+    # star-polygon path (kernels 2 + 3); see polygon_record
     "c4": dict(n_images=21, n_stars=2_000, seed=2, polygon=True,
                name="synthetic star fields 21 images x 2k stars, f=1135 px, 894x1342, 5-gon polygon matching, all 210 pairs"),
     "c4cap": dict(n_images=21, n_polygons=15_000, seed=3, polygon=True,
@@ -52,6 +60,8 @@ POPC_PER_COMPARISON = 8          # algorithmic: 8 x (32-bit XOR + POPC) per 256-
 OPS_PER_COMPARISON = 512         # tensor variant: 256 int8 multiply-adds = 512 ops per distance
 I8_OPS_PER_CLK_PER_SM = 16384    # tcgen05 kind::i8: 8192 MAC/clk/SM (M128 N256 K32 issues every 128 clk)
 BYTES_PER_ROW = 32
+FLUSH_BYTES = 256 << 20          # > 126 MB L2
+L2_NOTE = "256 MiB device memset between steps (inside the timed region) flushes the 126 MB L2"
 
 
 def parse():
@@ -63,9 +73,14 @@ def parse():
     ap.add_argument("--workload", default="c3", choices=list(WORKLOADS))
     ap.add_argument("--mode", default="knn2_ratio", choices=["knn2_ratio", "crosscheck"])
     ap.add_argument("--variant", default="auto")
-    ap.add_argument("--cpu-sample-pairs", type=int, default=3)
+    ap.add_argument("--cpu-sample-pairs", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sub", action="store_true", help="default invocation: skip the sub-records")
+    ap.add_argument("--sub", default="crosscheck,c5,c4,c4cap", help="which sub-records the default invocation adds")
+    ap.add_argument("--sub-steps", type=int, default=3)
     ap.add_argument("--fp32", action="store_true", help="polygon workloads: non-parity fp32 compare")
+    ap.add_argument("--ransac", default="opencv", choices=["opencv", "device"],
+                    help="c1real: cv.findHomography per pair (reference, parity) or the batched device RANSAC (row N3)")
     return ap.parse_args()
 
 
@@ -122,32 +137,119 @@ class ClockSampler:
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+# ---- one process per GPU ----------------------------------------------------------------------------
+class Runtime:
+    """Rank / device / process-group state shared by every record of one bench invocation."""
+
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.dist = dist
+        self.stream = torch.cuda.current_stream(self.dev)
+        self.flush = torch.empty(FLUSH_BYTES, dtype=torch.uint8, device=self.dev)
+
+    def engine(self):
+        import ssp_b200
+        eng = ssp_b200.Engine(self.local_rank)
+        eng.set_stream(self.stream.cuda_stream)
+        return eng
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.dev)
+
+    def max_over_ranks(self, x):
+        if self.dist is None:
+            return float(x)
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(self, xs):
+        if self.dist is None:
+            return [int(x) for x in xs]
+        t = self.torch.tensor(list(xs), dtype=self.torch.int64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return [int(v) for v in t.tolist()]
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
+def timed_steps(rt, step, steps, warmup):
+    """W untimed steps, then EXACTLY `steps` steps between CUDA events on the engine's stream,
+    barrier + synchronize on both sides, max over ranks.  Returns (ms per step, clocks, last result)."""
+    out = None
+    for _ in range(warmup):
+        out = step()
+    rt.barrier()
+    with ClockSampler(rt.local_rank) as clocks:
+        ev0, ev1 = rt.torch.cuda.Event(enable_timing=True), rt.torch.cuda.Event(enable_timing=True)
+        ev0.record(rt.stream)
+        for _ in range(steps):
+            out = step()
+        ev1.record(rt.stream)
+        rt.barrier()
+    return rt.max_over_ranks(ev0.elapsed_time(ev1)) / steps, clocks.summary(), out
+
+
+def timed_e2e(rt, step, steps, warmup):
+    """The end-to-end leg: host buffers in, host buffers out, wall clock between barriers (host
+    work is part of it), max over ranks, same step count and L2 treatment as the resident leg."""
+    out = None
+    for _ in range(max(1, min(warmup, 2))):
+        out = step()
+    rt.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        out = step()
+    rt.barrier()
+    return rt.max_over_ranks(time.perf_counter() - t0) / steps, out
+
+
 # ---- CPU reference arm ----------------------------------------------------------------------------
-def cv_match_pair(cv, q, t, mode):
-    """The reference's own CPU call for one pair; returns the number of surviving matches."""
+def cv_match_pair(cv, q, t, mode, keep=False):
+    """The reference's own CPU call for one pair; returns the number of surviving matches (and, with
+    keep=True, the survivors as an int array (n, 3) {queryIdx, trainIdx, distance})."""
     if mode == "crosscheck":
-        return len(cv.BFMatcher(cv.NORM_HAMMING, crossCheck=True).match(cv.UMat(q), cv.UMat(t)))
-    good = 0
-    for m, n in cv.BFMatcher(cv.NORM_HAMMING).knnMatch(q, t, k=2):
-        if m.distance < 0.75 * n.distance:
-            good += 1
-    return good
+        ms = cv.BFMatcher(cv.NORM_HAMMING, crossCheck=True).match(cv.UMat(q), cv.UMat(t))
+    else:
+        ms = [m for m, n in cv.BFMatcher(cv.NORM_HAMMING).knnMatch(q, t, k=2) if m.distance < 0.75 * n.distance]
+    if not keep:
+        return len(ms)
+    return np.array([[m.queryIdx, m.trainIdx, int(m.distance)] for m in ms], dtype=np.int32).reshape(-1, 3)
 
 
 def cpu_sample(sets, pairs, mode, n_sample):
+    """cv2.BFMatcher on `n_sample` evenly spaced pairs of the workload; keeps the matches so that the
+    caller can compare them with the GPU's for the same pairs."""
     import cv2 as cv
     cv.setNumThreads(os.cpu_count() or 1)
     n_sample = max(1, min(n_sample, len(pairs)))
     stride = max(1, len(pairs) // n_sample)
     sample = [pairs[i * stride] for i in range(n_sample)]
-    t0 = time.perf_counter()
-    cmps = 0
+    matches, cmps, dt = [], 0, 0.0
     for a, b in sample:
-        cv_match_pair(cv, sets[a], sets[b], mode)
+        t0 = time.perf_counter()
+        n = cv_match_pair(cv, sets[a], sets[b], mode)           # timed: the call + the ratio loop only
+        dt += time.perf_counter() - t0
+        matches.append(cv_match_pair(cv, sets[a], sets[b], mode, keep=True))   # untimed: for the parity check
+        assert len(matches[-1]) == n
         cmps += sets[a].shape[0] * sets[b].shape[0]
-    dt = time.perf_counter() - t0
-    return {"pairs": len(sample), "seconds": dt, "pairs_per_s": len(sample) / dt, "gcmp_per_s": cmps / dt / 1e9,
-            "cores": cv.getNumThreads(), "cv2": cv.__version__}
+    return {"pairs": sample, "matches": matches, "seconds": dt, "pairs_per_s": len(sample) / dt,
+            "gcmp_per_s": cmps / dt / 1e9, "cores": cv.getNumThreads(), "cv2": cv.__version__}
 
 
 def run_reference(args, wl, sets, pairs):
@@ -180,7 +282,7 @@ def run_reference(args, wl, sets, pairs):
     return {
         "impl": "reference", "metric": "image_pairs_matched_per_sec", "value": value, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 (256-bit Hamming, OpenCV SIMD popcount)", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8 (256-bit Hamming, OpenCV SIMD popcount)", "data": "synthetic",
         "config": {"workload": wl["name"], "mode": args.mode, "pairs": len(pairs)},
         "gcmp_per_s": cmps / dt / 1e9,
         "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": cv.getNumThreads(), "kind": "reference",
@@ -189,35 +291,55 @@ def run_reference(args, wl, sets, pairs):
     }
 
 
-# ---- our arm --------------------------------------------------------------------------------------
+# ---- peaks ------------------------------------------------------------------------------------------
+def _latest_profile(pattern):
+    found = sorted(glob.glob(os.path.join(ROOT, "profiles", pattern)))
+    return found[-1] if found else None
+
+
 def popc_peak_per_clk_per_sm():
     """POPC issue rate measured on this pool's B200 by tools/pipe_microbench (committed summary),
     else the CUDA programming-guide planning figure."""
-    path = os.path.join(ROOT, "profiles", "pipe_microbench_r01.json")
     try:
-        with open(path) as f:
+        with open(_latest_profile("pipe_microbench_r*.json")) as f:
             return float(json.load(f)["popc"]), "measured (profiles/pipe_microbench_r01.json)"
     except Exception:
         return 16.0, "planning figure (CUDA programming guide, 16 POPC/clk/SM)"
 
 
-def measured_tensor_peak():
-    """Dense int8 peak in TOP/s.  MEASURED_PEAKS.json holds the cuBLAS bf16 figure of this pool's
-    B200s; kind::i8 runs at twice the bf16 rate per SM and clock on sm_100, so the int8 peak is
-    2 x that (burst figure: the kernel is timed alone)."""
+def measured_int8_ceiling(sm_count, sm_max_mhz):
+    """Dense int8 ceiling of THIS kernel's tensor path in TOP/s: the MMA-only probe (the product
+    kernel with the epilogue compiled out: TMA feed + tcgen05.mma issue, nothing else) timed on this
+    pool's B200 with its clock record, committed under profiles/ (tools/int8_ceiling.sh).  Fallback:
+    the physical issue rate of the pipe at the maximum SM clock."""
+    path = _latest_profile("int8_ceiling_r*.json")
+    try:
+        with open(path) as f:
+            j = json.load(f)
+        return float(j["tops"]), (f"measured: MMA-only probe of the same kernel, {j['kernel_ms']:.2f} ms per C3 launch at "
+                                  f"{j.get('sm_mhz')} MHz ({os.path.relpath(path, ROOT)})"), "measured"
+    except Exception:
+        peak = sm_count * I8_OPS_PER_CLK_PER_SM * sm_max_mhz * 1e6 / 1e12
+        return peak, f"fallback: {sm_count} SMs x {I8_OPS_PER_CLK_PER_SM} int8 ops/clk/SM x {sm_max_mhz:g} MHz (no committed probe)", "fallback"
+
+
+def bf16_proxy_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            bf16 = float(json.load(f)["bf16_tflops"])
-        return 2.0 * bf16, f"2 x measured cuBLAS bf16 burst ({bf16:g} TF/s, MEASURED_PEAKS.json): int8 runs at twice the bf16 rate"
+            j = json.load(f)
+        return {"two_x_cublas_bf16_burst": 2.0 * float(j["bf16_tflops"]),
+                "two_x_cublas_bf16_sustained": 2.0 * float(j.get("bf16_tflops_sustained", j["bf16_tflops"])),
+                "source": "MEASURED_PEAKS.json (cuBLAS bf16 is power-capped near 1.3 GHz on this pool: a proxy, not the ceiling)"}
     except Exception:
-        return 4500.0, "nominal dense int8 (B200_PROFILING.md fallback: 2 x 2250 bf16)"
+        return None
 
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel on this
-    workload, from the committed `ncu --set full` capture (profiles/traffic_r01.json)."""
+    workload, from the committed `ncu --set full` capture (profiles/traffic_r*.json)."""
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
+        path = _latest_profile("traffic_r*.json")
+        with open(path) as f:
             t = json.load(f)[kernel]
         return float(t["dram_bytes"]), t["source"]
     except Exception:
@@ -232,112 +354,72 @@ def measured_hbm_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def run_ours(args, wl, sets, pairs):
-    import torch
+# ---- kernel 1 workloads ---------------------------------------------------------------------------
+def hamming_record(rt, wl, sets, pairs, mode, variant, steps, warmup, cpu_pairs):
+    """value / e2e / roofline / cpu_baseline of one Hamming workload in one mode.  Returns the record
+    on rank 0 (None elsewhere)."""
     import ssp_b200
-    from ssp_b200.distributed import shard_pairs, broadcast_descriptor_bank, gather_matches_resident
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    dev = torch.device("cuda", local_rank)
-    torch.cuda.set_device(dev)
-
-    eng = ssp_b200.Engine(local_rank)
-    stream = torch.cuda.current_stream(dev)
-    eng.set_stream(stream.cuda_stream)
+    from ssp_b200.distributed import shard_pairs_contiguous, broadcast_descriptor_bank, gather_matches_resident
+    torch, world, rank = rt.torch, rt.world, rt.rank
+    eng = rt.engine()
 
     # host-side bank in pinned memory (rank 0 owns the input, like the reference's single process)
     bank = offs = pinned = None
+    offs_known = np.zeros(len(sets) + 1, dtype=np.int64)
+    np.cumsum([s.shape[0] for s in sets], out=offs_known[1:])
     if rank == 0:
         bank_np, offs = ssp_b200.Engine.pack_descriptors(sets)
         pinned = torch.from_numpy(bank_np).pin_memory()
         bank = pinned.numpy()
-    bank_bytes = int(sum(s.shape[0] for s in sets)) * BYTES_PER_ROW
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
+    bank_bytes = int(offs_known[-1]) * BYTES_PER_ROW
+    cost = [int(sets[a].shape[0]) * int(sets[b].shape[0]) for a, b in pairs]
+    local_pairs, lo, hi = shard_pairs_contiguous(pairs, rank, world, cost)
 
     # ---- resident bank for the `value` leg ----------------------------------------------------
     if world > 1:
-        bank_t, offs_all = broadcast_descriptor_bank(bank, offs, 0)
+        bank_view, offs_all = broadcast_descriptor_bank(bank, offs, 0)
+        bank_t = bank_view.clone()          # the receive buffer is reused by the e2e leg
     else:
-        bank_t, offs_all = pinned.to(dev), offs
+        bank_t, offs_all = pinned.to(rt.dev), offs
     eng.bind_descriptor_bank(bank_t.data_ptr(), offs_all, keepalive=bank_t)
-    local_pairs, local_pos = shard_pairs(pairs, rank, world)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    kernel_ms, launches = [], [0]
 
     def step_resident():
-        flush.zero_()
-        return eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant, fetch=False)
+        rt.flush.zero_()
+        res = eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, fetch=False)
+        st = eng.hamming_last_stats()
+        kernel_ms.append(st["main_kernel_ms"])
+        launches[0] += st["launches"]
+        return res
 
-    kernel_ms, launches = [], 0
-    for _ in range(args.warmup):
-        step_resident()
-    barrier()
-    with ClockSampler(local_rank) as clocks:
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record(stream)
-        for _ in range(args.steps):
-            res = step_resident()
-            st = eng.hamming_last_stats()
-            kernel_ms.append(st["main_kernel_ms"])
-            launches += st["launches"]
-        ev1.record(stream)
-        barrier()
-    elapsed_ms = ev0.elapsed_time(ev1)
-    comparisons_local = eng.hamming_last_stats()["comparisons"]
-    n_matches_local = int(res.offsets[-1])
-    if dist is not None:
-        t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms = float(t.item())
-        c = torch.tensor([comparisons_local, n_matches_local, launches], dtype=torch.int64, device=dev)
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        comparisons, n_matches, launches = int(c[0]), int(c[1]), int(c[2])
-    else:
-        comparisons, n_matches = comparisons_local, n_matches_local
-    ms_per_step = elapsed_ms / args.steps
+    ms_per_step, clk, res = timed_steps(rt, step_resident, steps, warmup)
+    kernel_ms = kernel_ms[warmup:]
+    st = eng.hamming_last_stats()
+    launches_timed = st["launches"] * steps      # the same launches every step (bank stays expanded)
+    comparisons_local = st["comparisons"]
+    comparisons, n_matches, launches_all = rt.sum_over_ranks([comparisons_local, int(res.offsets[-1]), launches_timed])
     value = len(pairs) / (ms_per_step / 1e3)
 
     # ---- e2e leg: host buffers in, host buffers out, every step -------------------------------
     def step_e2e():
+        rt.flush.zero_()
         if world > 1:
-            b_t, o_all = broadcast_descriptor_bank(bank, offs, 0)       # H2D on rank 0 + NCCL broadcast
+            b_t, o_all = broadcast_descriptor_bank(bank, offs, 0)       # H2D on rank 0 + ONE NCCL broadcast
             eng.bind_descriptor_bank(b_t.data_ptr(), o_all, keepalive=b_t)
-            local = eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant, fetch=False)
-            # survivors: device -> NCCL gather -> global pair order -> pinned host memory of rank 0
-            return gather_matches_resident(eng, local.offsets, local_pos, len(pairs), dst=0)
+            local = eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, fetch=False)
+            # survivors: device -> exact-length NCCL transfers into rank 0's arrays -> pinned host memory
+            return gather_matches_resident(eng, local.offsets, dst=0)
         eng.upload_descriptor_bank(bank, offs)                           # pinned host -> device
-        return eng.hamming_match_pairs(local_pairs, mode=args.mode, variant=args.variant, pinned=True)  # D2H of survivors
+        return eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, pinned=True)  # D2H of survivors
 
-    e2e_steps = max(1, min(args.steps, 3))
-    step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        out = step_e2e()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e_value = len(pairs) * e2e_steps / e2e_s
+    e2e_s, out = timed_e2e(rt, step_e2e, steps, warmup)
+    e2e_value = len(pairs) / e2e_s
     d2h = (int(out.offsets[-1]) * 12 + (len(pairs) + 1) * 8) if rank == 0 else 0
     if rank == 0:
         assert int(out.offsets[-1]) == n_matches, "e2e and resident legs disagree on the survivor count"
 
     # ---- roofline of the dominant kernel -------------------------------------------------------
     info = eng.device_info()
-    clk = clocks.summary()
     main_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
     gcmp = comparisons_local / (main_ms / 1e3) / 1e9 if main_ms > 0 else 0.0   # Gcmp/s, this rank
     sm_max_mhz = clk.get("sm_max_mhz") or info["sm_clock_khz"] / 1e3
@@ -345,29 +427,30 @@ def run_ours(args, wl, sets, pairs):
     hbm_peak, hbm_src = measured_hbm_peak()
     rows_q = sum(sets[a].shape[0] for a, _ in local_pairs)
     rows_t = sum(sets[b].shape[0] for _, b in local_pairs)
-    tensor = args.variant in ("auto", "tensor")
+    tensor = variant in ("auto", "tensor")
     if tensor:
-        # algorithmic work: one 256-term int8 dot product per comparison = 512 integer ops
+        # algorithmic work: one 256-term int8 dot product per comparison = 512 integer ops, counted
+        # ONCE per image pair also in cross-check mode (one distance serves both directions)
         achieved = gcmp * OPS_PER_COMPARISON / 1e3                      # TOP/s
-        peak, peak_src = measured_tensor_peak()
+        peak, peak_src, peak_kind = measured_int8_ceiling(info["sm_count"], sm_max_mhz)
         pipe_peak = info["sm_count"] * I8_OPS_PER_CLK_PER_SM * sm_max_mhz * 1e6 / 1e12
         algo_bytes = (rows_q + rows_t) * 256 + rows_q * 16              # expanded operands once + best-2 records
         roofline = {
             "bound": "tensor", "kernel": "hamming_tcgen05_kernel", "achieved": achieved, "peak": peak,
-            "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
-            "of": "measured" if "MEASURED_PEAKS" in peak_src else "fallback",
+            "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "of": peak_kind,
             "ops": "int8 multiply-add counted as 2 ops; s8 x s8 -> s32, exact",
             "peak_definition": peak_src,
             "pipe_peak_at_max_clock": pipe_peak,
             "pipe_peak_definition": f"{info['sm_count']} SMs x {I8_OPS_PER_CLK_PER_SM} int8 ops/clk/SM (tcgen05 kind::i8 "
-                                    f"M128 N256 K32 = 128 clk, measured by the MMA-only probe) x {sm_max_mhz:g} MHz",
+                                    f"M128 N256 K32 = 128 clk) x {sm_max_mhz:g} MHz",
             "frac_of_pipe_at_max_clock": achieved / pipe_peak,
             "frac_of_pipe_at_held_clock": achieved / (pipe_peak * held) if held else None,
+            "other_denominators": bf16_proxy_peak(),
             "gcmp_per_s": gcmp,
         }
     else:
         popc_rate, popc_src = popc_peak_per_clk_per_sm()
-        popc_per_cmp = 4 if args.variant == "popc_csa" else POPC_PER_COMPARISON
+        popc_per_cmp = 4 if variant == "popc_csa" else POPC_PER_COMPARISON
         peak = info["sm_count"] * popc_rate * sm_max_mhz * 1e6 / POPC_PER_COMPARISON / 1e9
         algo_bytes = (rows_q + rows_t) * BYTES_PER_ROW + rows_q * 16    # each operand once + best-2 records
         roofline = {
@@ -377,7 +460,7 @@ def run_ours(args, wl, sets, pairs):
                                f"{POPC_PER_COMPARISON} POPC per 256-bit comparison (the CSA variant issues {popc_per_cmp})",
             "frac_at_held_clock": gcmp / (peak * held) if held else None,
         }
-    traffic, traffic_src = ncu_traffic(roofline["kernel"])
+    traffic, traffic_src = ncu_traffic(roofline["kernel"] + ("_crosscheck" if mode == "crosscheck" else ""))
     roofline.update({
         "kernel_ms_per_launch": main_ms, "comparisons_per_launch": comparisons_local,
         "traffic": traffic, "traffic_source": traffic_src,
@@ -386,31 +469,40 @@ def run_ours(args, wl, sets, pairs):
                 "frac": (algo_bytes / (main_ms / 1e3) / 1e9) / hbm_peak if main_ms > 0 else None},
     })
 
-    line = None
+    rec = None
     if rank == 0:
-        line = {
-            "metric": "image_pairs_matched_per_sec", "value": value, "unit": "pairs/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+        rec = {
+            "value": value, "unit": "pairs/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms_per_step, "kernel_ms": main_ms,
             "dtype": "s8 x s8 -> s32 (exact)" if tensor else "u32 popcount",
-            "data": "synthetic",
-            "config": {"workload": wl["name"], "mode": args.mode, "variant": args.variant, "pairs": len(pairs),
-                       "descriptors_per_image": wl["n_desc"], "sharding": f"pairs round-robin over {world} rank(s)",
-                       "l2": "256 MiB device memset between steps (inside the timed region) flushes the 126 MB L2"},
+            "config": {"workload": wl["name"], "mode": mode, "variant": variant, "pairs": len(pairs),
+                       "descriptors_per_image": wl["n_desc"],
+                       "sharding": f"contiguous cost-balanced blocks of the pair list over {world} rank(s)", "l2": L2_NOTE},
             "gcmp_per_s": comparisons / (ms_per_step / 1e3) / 1e9,
             "matches_per_step": n_matches,
-            "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": bank_bytes + len(pairs) * 8,
-                    "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                    "gcmp_per_s": comparisons * e2e_steps / e2e_s / 1e9},
-            "gpu_launches": launches,
+            "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": bank_bytes + len(offs_known) * 8,
+                    "d2h_bytes_per_step": d2h, "steps": steps, "ms_per_step": e2e_s * 1e3,
+                    "gcmp_per_s": comparisons / e2e_s / 1e9},
+            "gpu_launches": launches_all,
             "clocks": clk,
             "roofline": roofline,
         }
+        if world == 1 and cpu_pairs > 0:
+            cpu = cpu_sample(sets, pairs, mode, cpu_pairs)
+            got = eng.hamming_match_pairs(cpu["pairs"], mode=mode, variant=variant)
+            same = all(np.array_equal(np.stack(got.pair(k), axis=1), cpu["matches"][k]) for k in range(len(cpu["pairs"])))
+            rec["parity_in_run"] = bool(same)
+            rec["parity_in_run_detail"] = (f"survivors (queryIdx, trainIdx, distance) of {len(cpu['pairs'])} pairs: GPU step vs "
+                                           f"cv2 {cpu['cv2']} BFMatcher, {sum(len(m) for m in cpu['matches'])} matches compared")
+            rec["cpu_baseline"] = {
+                "value": cpu["pairs_per_s"], "unit": "pairs/s", "cores": cpu["cores"], "kind": "reference",
+                "gcmp_per_s": cpu["gcmp_per_s"],
+                "sample": f"cv2 {cpu['cv2']} BFMatcher ({mode}) on {len(cpu['pairs'])} of {len(pairs)} pairs "
+                          f"({cpu['seconds']:.1f} s), {cpu['cores']} threads; the reference's own CPU call"}
     eng.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
-    return line
+    del bank_t
+    torch.cuda.empty_cache()
+    return rec
 
 
 # ---- star-polygon path (kernels 2 + 3) ------------------------------------------------------------
@@ -442,7 +534,7 @@ def polygon_cpu_pair(inp, oracle, k, pairs, state):
     a, b = pairs[k % len(pairs)]
     evals = 0
     if "cands" in inp:
-        share = len(inp["xy"]) / len(pairs)
+        share = len(inp["xy"]) / state["n_pairs_total"]
         c = inp["cands"][a]
         n = max(1, int(round(len(c) * share)))
         lo = (k * n) % max(1, len(c) - n)
@@ -456,22 +548,22 @@ def polygon_cpu_pair(inp, oracle, k, pairs, state):
     return evals
 
 
-def polygon_cpu_state(inp, oracle, pairs, steps):
+def polygon_cpu_state(inp, oracle, pairs, steps, n_pairs_total):
     """Untimed preparation of the CPU leg: the polygon rows the sampled pairs compare."""
     if "cands" not in inp:
-        return {"rows": 1500}     # 1500 x 15000 rows per step: numpy needs ~1.6 GB of temporaries
+        return {"rows": 1500, "n_pairs_total": n_pairs_total}     # 1500 x 15000 rows per step: numpy needs ~1.6 GB of temporaries
     need = sorted({i for k in range(steps) for i in pairs[k % len(pairs)]})
     feat = {}
     for i in need:
         feat[i] = np.ascontiguousarray(oracle.characteristics(inp["xy"][i], inp["br"][i], inp["cands"][i])["feat"])
-    return {"feat": feat}
+    return {"feat": feat, "n_pairs_total": n_pairs_total}
 
 
 def run_polygon_reference(args, wl, inp, pairs):
     from oracle.polygon_oracle import PolygonOracle
     oracle = PolygonOracle((IMG_H, IMG_W, 3), FOCAL)
     sample_pairs = [pairs[0], pairs[len(pairs) // 2]]
-    state = polygon_cpu_state(inp, oracle, sample_pairs, args.steps + args.warmup)
+    state = polygon_cpu_state(inp, oracle, sample_pairs, args.steps + args.warmup, len(pairs))
     k = 0
     for _ in range(args.warmup):
         polygon_cpu_pair(inp, oracle, k, sample_pairs, state)
@@ -493,167 +585,159 @@ def run_polygon_reference(args, wl, inp, pairs):
     return {
         "impl": "reference", "metric": "image_pairs_matched_per_sec", "value": value, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": wl["name"], "pairs": len(pairs)},
         "polygon_evals_per_s": evals / dt,
         "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": 1, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
 
+
 def fp_pipe_peaks():
     """FP64 / FP32 issue rates measured on this pool's B200 by tools/pipe_microbench (committed
     summary, thread-ops per clock per SM); None when the summary has no such entry."""
     try:
-        with open(os.path.join(ROOT, "profiles", "pipe_microbench_r01.json")) as f:
+        with open(_latest_profile("pipe_microbench_r*.json")) as f:
             j = json.load(f)
         return {k: float(j[k]) for k in ("dfma", "dsub_dmul_dadd_total", "ffma") if k in j}
     except Exception:
         return {}
 
 
-def run_polygon_ours(args, wl, inp, pairs):
-    import torch
-    import ssp_b200
-    from ssp_b200.distributed import shard_pairs
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    dev = torch.device("cuda", local_rank)
-    torch.cuda.set_device(dev)
-    eng = ssp_b200.Engine(local_rank)
-    stream = torch.cuda.current_stream(dev)
-    eng.set_stream(stream.cuda_stream)
+def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
+    from ssp_b200.distributed import (shard_pairs_contiguous, broadcast_star_bank, measure_polygons_sharded,
+                                      gather_polygon_matches_resident, _broadcaster)
+    torch, world, rank, dev, dist = rt.torch, rt.world, rt.rank, rt.dev, rt.dist
+    eng = rt.engine()
     n_img = wl["n_images"]
-    local_pairs, _ = shard_pairs(pairs, rank, world)
+    local_pairs, lo, hi = shard_pairs_contiguous(pairs, rank, world)
     measured = "cands" in inp
 
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    # every rank holds the full star / polygon bank (KBs..MBs) and measures all images itself:
-    # kernel 2 is microseconds per image, cheaper than any exchange (SURVEY §8(e))
+    # ---- resident inputs ------------------------------------------------------------------------
     if measured:
-        eng.upload_star_bank(inp["xy"], inp["br"], IMG_W, IMG_H, FOCAL)
-        cand_dev = [torch.from_numpy(c).to(dev) for c in inp["cands"]]
+        if world > 1:
+            src = (inp["xy"], inp["br"], inp["cands"]) if rank == 0 else (None, None, None)
+            so, co, xy_v, br_v, cand_v = broadcast_star_bank(*src, src=0)
+            xy_t, br_t, cand_t = xy_v.clone(), br_v.clone(), cand_v.clone()   # the receive buffer is reused by the e2e leg
+        else:
+            eng.upload_star_bank(inp["xy"], inp["br"], IMG_W, IMG_H, FOCAL)
+            co = np.zeros(n_img + 1, dtype=np.int64)
+            np.cumsum([len(c) for c in inp["cands"]], out=co[1:])
+            cand_host = torch.from_numpy(np.concatenate(inp["cands"])).pin_memory()
+            cand_t = cand_host.to(dev)
         h2d = sum(a.nbytes for a in inp["xy"]) + sum(b.nbytes for b in inp["br"]) + sum(c.nbytes for c in inp["cands"])
     else:
+        if rank == 0 or world == 1:
+            feat_host = torch.from_numpy(np.concatenate(inp["feat"])).pin_memory()
+        fo = np.zeros(n_img + 1, dtype=np.int64)
+        np.cumsum([len(f) for f in inp["feat"]], out=fo[1:])
         for i in range(n_img):
             eng.polygon_upload_features(i, inp["feat"][i])
         h2d = sum(f.nbytes for f in inp["feat"])
-    h2d += len(local_pairs) * 8
+    h2d += len(pairs) * 8
+
+    def measure_all_local():
+        for i in range(n_img):
+            eng.polygon_measure_resident(i, cand_t[int(co[i]):].data_ptr(), int(co[i + 1] - co[i]), wait=False)
+        return 2 * n_img   # measure + scatter per image
+
+    kernel_ms = []
 
     def step_resident():
         n = 0
         if measured:
-            for i in range(n_img):
-                eng.polygon_measure_resident(i, cand_dev[i].data_ptr(), cand_dev[i].shape[0], wait=False)
-                n += 3
-        res = eng.polygon_match_pairs(local_pairs, fp32=args.fp32, fetch=False)
-        return res, n + eng.polygon_last_stats()["launches"]
+            if world > 1:
+                measure_polygons_sharded(eng, so, co, xy_t, br_t, cand_t, IMG_W, IMG_H, FOCAL)
+                n += 2 * len(range(rank, n_img, world)) + 1
+            else:
+                n += measure_all_local()
+        res = eng.polygon_match_pairs(local_pairs, fp32=fp32, fetch=False)
+        st = eng.polygon_last_stats()
+        kernel_ms.append(st["main_kernel_ms"])
+        return res, n + st["launches"]
 
     def step_e2e():
         if measured:
-            eng.upload_star_bank(inp["xy"], inp["br"], IMG_W, IMG_H, FOCAL)
-            for i in range(n_img):
-                eng.polygon_measure(i, inp["cands"][i])
+            if world > 1:
+                src = (inp["xy"], inp["br"], inp["cands"]) if rank == 0 else (None, None, None)
+                so2, co2, xy2, br2, cand2 = broadcast_star_bank(*src, src=0)       # H2D on rank 0 + ONE broadcast
+                measure_polygons_sharded(eng, so2, co2, xy2, br2, cand2, IMG_W, IMG_H, FOCAL)
+            else:
+                eng.upload_star_bank(inp["xy"], inp["br"], IMG_W, IMG_H, FOCAL)
+                cand_t.copy_(cand_host, non_blocking=True)                           # one H2D for all candidate tables
+                measure_all_local()
         else:
-            for i in range(n_img):
-                eng.polygon_upload_features(i, inp["feat"][i])
-        return eng.polygon_match_pairs(local_pairs, fp32=args.fp32)
+            if world > 1:
+                arrays = [fo, feat_host.numpy()] if rank == 0 else None
+                _, feat_v = _broadcaster("polyfeat", 0).broadcast(arrays, to_host=(0,))
+                for i in range(n_img):
+                    eng.polygon_upload_features_resident(i, feat_v[int(fo[i]):].data_ptr(), 0, int(fo[i + 1] - fo[i]))
+            else:
+                for i in range(n_img):
+                    eng.polygon_upload_features(i, inp["feat"][i])
+        if world > 1:
+            local = eng.polygon_match_pairs(local_pairs, fp32=fp32, fetch=False)
+            return gather_polygon_matches_resident(eng, local.offsets, dst=0)
+        return eng.polygon_match_pairs(local_pairs, fp32=fp32)
 
-    kernel_ms, launches = [], 0
-    for _ in range(args.warmup):
-        step_resident()
-    barrier()
-    with ClockSampler(local_rank) as clocks:
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record(stream)
-        for _ in range(args.steps):
-            res, n = step_resident()
-            launches += n
-            kernel_ms.append(eng.polygon_last_stats()["main_kernel_ms"])
-        ev1.record(stream)
-        barrier()
-    elapsed_ms = ev0.elapsed_time(ev1)
-    evals_local = eng.polygon_last_stats()["evaluations"]
-    n_matches_local = int(res.offsets[-1])
+    ms_per_step, clk, (res, launches_step) = timed_steps(rt, step_resident, steps, warmup)
+    kernel_ms = kernel_ms[warmup:]
+    st = eng.polygon_last_stats()
+    evals_local = st["evaluations"]
+    executed_local = st.get("executed_flops")
     n_polys = [eng.polygon_count(i) for i in range(n_img)]
-    if dist is not None:
-        t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms = float(t.item())
-        c = torch.tensor([evals_local, n_matches_local, launches], dtype=torch.int64, device=dev)
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        evals, n_matches, launches = int(c[0]), int(c[1]), int(c[2])
-    else:
-        evals, n_matches = evals_local, n_matches_local
-    ms_per_step = elapsed_ms / args.steps
-
-    e2e_steps = max(1, min(args.steps, 3))
-    step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        out = step_e2e()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    d2h = int(out.offsets[-1]) * 16 + (len(local_pairs) + 1) * 8
+    evals, n_matches, launches = rt.sum_over_ranks([evals_local, int(res.offsets[-1]), launches_step * steps])
+    e2e_s, out = timed_e2e(rt, step_e2e, steps, warmup)
+    d2h = (int(out.offsets[-1]) * 16 + (len(pairs) + 1) * 8) if rank == 0 else 0
+    if rank == 0:
+        assert int(out.offsets[-1]) == n_matches, "e2e and resident legs disagree on the polygon match count"
 
     info = eng.device_info()
-    clk = clocks.summary()
     sm_max_mhz = clk.get("sm_max_mhz") or info["sm_clock_khz"] / 1e3
     main_ms = float(np.mean(kernel_ms))
     rates = fp_pipe_peaks()
-    key, what = ("ffma", "FFMA") if args.fp32 else ("dsub_dmul_dadd_total", "unfused DSUB+DMUL+DADD (numpy's rounding)")
+    key, what = ("ffma", "FFMA") if fp32 else ("dsub_dmul_dadd_total", "unfused DSUB+DMUL+DADD (numpy's rounding)")
     flop_per_clk_sm = rates.get(key)
-    if flop_per_clk_sm is not None and args.fp32:
+    if flop_per_clk_sm is not None and fp32:
         flop_per_clk_sm *= 2.0          # an FFMA is 2 flop; the fp32 mode needs 15 FSUB + 15 FFMA = 45 flop in 30 issues
         flop_per_clk_sm *= 45.0 / 60.0  # 30 issue slots carry 45 flop, not 60
     peak = info["sm_count"] * flop_per_clk_sm * sm_max_mhz * 1e6 / 1e12 if flop_per_clk_sm else None
-    achieved = evals_local * FLOP_PER_EVALUATION / (main_ms / 1e3) / 1e12 if main_ms > 0 else None
+    # the kernel prunes exactly (a column whose partial sum already reaches the row's best is dropped):
+    # the roofline counts the flops it EXECUTED (counted on the device), never the 45 per evaluation it skipped
+    algorithmic = evals_local * FLOP_PER_EVALUATION / (main_ms / 1e3) / 1e12 if main_ms > 0 else None
+    achieved = executed_local / (main_ms / 1e3) / 1e12 if (executed_local and main_ms > 0) else None
     roofline = {
-        "bound": "fp32-pipe" if args.fp32 else "fp64-pipe", "kernel": "poly_compare_f32_kernel" if args.fp32 else "poly_compare_f64_kernel",
+        "bound": "fp32-pipe" if fp32 else "fp64-pipe", "kernel": "poly_compare_f32_kernel" if fp32 else "poly_compare_f64_kernel",
         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak and achieved else None,
+        "achieved_counts": "flops executed by the kernel (device counter); pruned terms are not counted",
+        "executed_fraction_of_algorithmic_flops": (executed_local / (evals_local * FLOP_PER_EVALUATION)) if executed_local and evals_local else None,
+        "algorithmic_tflops_equivalent": algorithmic,
         "peak_definition": (f"{info['sm_count']} SMs x {flop_per_clk_sm:.1f} flop/clk/SM ({what}, measured: "
                             f"profiles/pipe_microbench_r01.json) x {sm_max_mhz:g} MHz") if peak else "not measured",
         "flop_per_evaluation": FLOP_PER_EVALUATION, "kernel_ms_per_launch": main_ms,
-        "evaluations_per_launch": evals_local, "traffic": None,
+        "evaluations_per_launch": evals_local, "evaluations_per_s": evals_local / (main_ms / 1e3) if main_ms > 0 else None,
+        "traffic": None,
     }
-    if not measured and not args.fp32 and world == 1:   # the committed ncu capture is of exactly this launch
+    if not measured and not fp32 and world == 1:   # the committed ncu capture is of exactly this launch
         roofline["traffic"], roofline["traffic_source"] = ncu_traffic("poly_compare_f64_kernel")
-    line = None
+    rec = None
     if rank == 0:
-        line = {
-            "metric": "image_pairs_matched_per_sec", "value": len(pairs) / (ms_per_step / 1e3), "unit": "pairs/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
-            "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
-            "dtype": "f32" if args.fp32 else "f64", "data": "synthetic",
+        rec = {
+            "value": len(pairs) / (ms_per_step / 1e3), "unit": "pairs/s", "n_gpus": world, "steps": steps,
+            "warmup": warmup, "ms_per_step": ms_per_step, "kernel_ms": main_ms,
+            "dtype": "f32" if fp32 else "f64",
             "config": {"workload": wl["name"], "pairs": len(pairs), "polygons_per_image": [min(n_polys), max(n_polys)],
                        "candidates_per_image": [min(map(len, inp["cands"])), max(map(len, inp["cands"]))] if measured else None,
-                       "threshold": 0.1566, "sharding": f"pairs round-robin over {world} rank(s)",
+                       "threshold": 0.1566,
+                       "sharding": f"kernel 2 by image, kernel 3 by contiguous blocks of the pair list over {world} rank(s)",
                        "l2": "inputs are far below L2 size by nature of the path (<= 38 MB polygon bank); no flush"},
             "polygon_evals_per_s": evals / (ms_per_step / 1e3), "matches_per_step": n_matches,
-            "e2e": {"value": len(pairs) * e2e_steps / e2e_s, "unit": "pairs/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+            "e2e": {"value": len(pairs) / e2e_s, "unit": "pairs/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "steps": steps, "ms_per_step": e2e_s * 1e3},
             "gpu_launches": launches, "clocks": clk, "roofline": roofline,
         }
     eng.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
-    return line
+    return rec
 
 
 # ---- whole matcher stage at BASELINE config 1 (real ORB descriptors) -------------------------------
@@ -715,7 +799,8 @@ def run_stage(args, wl):
             imgs_features_orb_and_stars=feats, imgs_features_len_orb=[len(f.keypoints) for f in feats],
             conf_thresh=0.2, img_names=names, work_scale_imgs=imgs, pairwise_matches_output_dir=tmp,
             disable_prompts=True, output_dir_polygon_matching=tmp, predefined_overlaps=[],
-            focal_length_pinhole=1135, engine=engine, write_debug_images=False, verbose=False)
+            focal_length_pinhole=1135, engine=engine, write_debug_images=False, verbose=False,
+            ransac="opencv" if reference else args.ransac)
         return m.match_n_features()
 
     for _ in range(args.warmup):
@@ -729,8 +814,9 @@ def run_stage(args, wl):
     line = {
         "metric": "image_pairs_matched_per_sec", "value": n_pairs / dt, "unit": "pairs/s", "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8 Hamming + f64 RANSAC (OpenCV)", "data": "real (frozen ORB fixture)",
+        "scaling": "strong", "vs_baseline": None, "dtype": "u8 Hamming + f64 RANSAC (OpenCV)", "data": "real (frozen ORB fixture)",
         "config": {"workload": wl["name"], "pairs": n_pairs, "mode": "crosscheck", "kept_directed_entries": kept,
+                   "ransac": "opencv" if reference else args.ransac,
                    "note": "whole stage incl. cv.findHomography per pair and MatchesInfo construction on the host; "
                            "the matching itself is one engine call in front of the pair loop"},
         "e2e": {"value": n_pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": 0 if reference else bytes_in,
@@ -760,6 +846,16 @@ def emit(line):
         os.write(_JSON_FD, data)
 
 
+def top_level(rec, args):
+    """A record as the ONE line of the bench contract."""
+    line = {"metric": "image_pairs_matched_per_sec", "value": rec["value"], "unit": rec["unit"], "n_gpus": rec["n_gpus"],
+            "steps": rec["steps"], "warmup": rec["warmup"], "ms_per_step": rec["ms_per_step"], "higher_is_better": True,
+            # the pair list of a workload is fixed and divided over the ranks at every N
+            "scaling": "strong", "vs_baseline": None, "dtype": rec["dtype"], "data": "synthetic"}
+    line.update({k: v for k, v in rec.items() if k not in line})
+    return line
+
+
 def main():
     global _JSON_FD
     sys.stdout.flush()
@@ -768,6 +864,7 @@ def main():
     args = parse()
     wl = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference" and rank != 0:
         return 0  # rank 0 alone runs the CPU arm
     from ssp_b200 import synthetic as synth
@@ -775,18 +872,21 @@ def main():
         if rank == 0:
             emit(run_stage(args, wl))
         return 0
+    cpu_pairs = 0 if (args.no_cpu_baseline or world > 1) else args.cpu_sample_pairs
     if wl.get("polygon"):
         inp = polygon_inputs(wl)
         pairs = synth.all_pairs(wl["n_images"])
         if args.impl == "reference":
             emit(run_polygon_reference(args, wl, inp, pairs))
             return 0
-        line = run_polygon_ours(args, wl, inp, pairs)
+        rt = Runtime()
+        rec = polygon_record(rt, wl, inp, pairs, args.steps, args.warmup, args.fp32)
         if rank == 0:
-            if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not args.no_cpu_baseline:
+            if cpu_pairs:
                 ref_args = argparse.Namespace(**{**vars(args), "steps": 2, "warmup": 0})
-                line["cpu_baseline"] = run_polygon_reference(ref_args, wl, inp, pairs)["cpu_baseline"]
-            emit(line)
+                rec["cpu_baseline"] = run_polygon_reference(ref_args, wl, inp, pairs)["cpu_baseline"]
+            emit(top_level(rec, args))
+        rt.close()
         return 0
     # every rank generates the same seeded input (cheap next to shipping it); rank 0's copy is
     # the "host input" of the e2e leg
@@ -795,16 +895,52 @@ def main():
     if args.impl == "reference":
         emit(run_reference(args, wl, sets, pairs))
         return 0
-    line = run_ours(args, wl, sets, pairs)
+    rt = Runtime()
+    rec = hamming_record(rt, wl, sets, pairs, args.mode, args.variant, args.steps, args.warmup, cpu_pairs)
+    default_invocation = (args.workload == "c3" and args.mode == "knn2_ratio" and args.variant == "auto" and not args.no_sub)
+    sub = {}
+    if default_invocation:
+        want = [s for s in args.sub.split(",") if s]
+        k, w = max(1, min(args.steps, args.sub_steps)), max(3, min(args.warmup, 3))
+
+        def guarded(name, fn):
+            # a sub-record must never take the headline line down with it
+            try:
+                r = fn()
+            except Exception as e:                                         # noqa: BLE001
+                r = {"error": f"{type(e).__name__}: {e}"[:400]} if rank == 0 else None
+            if rank == 0:
+                sub[name] = r
+
+        if "crosscheck" in want:
+            # the call the reference's pipelines actually make (custom_bruteforce_matcher.py:193-199)
+            guarded("crosscheck", lambda: hamming_record(rt, wl, sets, pairs, "crosscheck", "auto", k, w, min(cpu_pairs, 6)))
+        del sets
+        if "c5" in want:
+            w5 = WORKLOADS["c5"]
+            sets5 = synth.descriptor_bank(w5["n_images"], w5["n_desc"], seed=w5["seed"])
+            pairs5 = synth.all_pairs(w5["n_images"])
+            guarded("c5", lambda: hamming_record(rt, w5, sets5, pairs5, "knn2_ratio", "auto", k, w, min(cpu_pairs * 3, 32)))
+            del sets5
+        for name in ("c4", "c4cap"):
+            if name in want:
+                wp = WORKLOADS[name]
+                inp = polygon_inputs(wp)
+                pp = synth.all_pairs(wp["n_images"])
+
+                def poly(wp=wp, inp=inp, pp=pp):
+                    r = polygon_record(rt, wp, inp, pp, k, w, False)
+                    if rank == 0 and cpu_pairs:
+                        ref_args = argparse.Namespace(**{**vars(args), "steps": 2, "warmup": 0})
+                        r["cpu_baseline"] = run_polygon_reference(ref_args, wp, inp, pp)["cpu_baseline"]
+                    return r
+                guarded(name, poly)
     if rank == 0:
-        if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not args.no_cpu_baseline:
-            cpu = cpu_sample(sets, pairs, args.mode, args.cpu_sample_pairs)
-            line["cpu_baseline"] = {
-                "value": cpu["pairs_per_s"], "unit": "pairs/s", "cores": cpu["cores"], "kind": "reference",
-                "gcmp_per_s": cpu["gcmp_per_s"],
-                "sample": f"cv2 {cpu['cv2']} BFMatcher ({args.mode}) on {cpu['pairs']} of {len(pairs)} pairs "
-                          f"({cpu['seconds']:.1f} s), {cpu['cores']} threads; the reference's own CPU call"}
+        line = top_level(rec, args)
+        if sub:
+            line["sub"] = sub
         emit(line)
+    rt.close()
     return 0
 
 

@@ -214,6 +214,29 @@ int ssp_polygon_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
  * kernel that ran does not count (fp32 / min-over-shifts / legacy). */
 int ssp_polygon_last_executed_flops(ssp_ctx* ctx, int64_t* executed_flops);
 
+/* ---- row N3: batched RANSAC homography (opt-in, NOT bit-compatible with OpenCV) -----------
+ * Stands in for the per-pair cv.findHomography(src_pts, dst_pts, cv.RANSAC, 5) of
+ * custom_bruteforce_matcher.py:215-246 for ALL pairs of the last ssp_hamming_match_pairs call at
+ * once; the point pairs are gathered on the device from that call's survivors (query row ->
+ * keypoint of the query image, train row -> keypoint of the train image).
+ *   keypoint_xy       float32 (K, 2) pixel coordinates of all images' keypoints back to back (host)
+ *   keypoint_offsets  int64 (n_images + 1) (host); image i must list at least as many keypoints as
+ *                     it has descriptor rows
+ *   pairs / n_pairs   the pair list of the last Hamming call
+ *   reproj_threshold  inlier bound in pixels (reference: 5); n_hypotheses 4-point samples per pair
+ *   min_matches       pairs with fewer matches get no model (reference: 6, :215): H = NaN, n_inliers = -1
+ *   H                 float64 (n_pairs, 9) row-major, h33 = 1: least-squares refit on the inliers of
+ *                     the best hypothesis (NaN if no model)
+ *   inlier_mask       uint8 per survivor, in the order of ssp_hamming_fetch_matches
+ *   n_inliers         int32 per pair
+ * Same model as cv::findHomography (4-point hypotheses, reprojection error, best count wins, refit on
+ * the inliers, mask of the best hypothesis) with a fixed seed and hypothesis count; OpenCV's RNG,
+ * adaptive termination and Levenberg-Marquardt polish are not reproduced. */
+int ssp_ransac_homography_pairs(ssp_ctx* ctx, const float* keypoint_xy, const int64_t* keypoint_offsets,
+                                int n_images, const int32_t* pairs, int n_pairs, double reproj_threshold,
+                                int n_hypotheses, uint32_t seed, int min_matches, double* H,
+                                uint8_t* inlier_mask, int64_t mask_capacity, int32_t* n_inliers);
+
 /* ---- row N2: candidate generation ------------------------------------------------------
  * The data-parallel parts of reduce_amount_of_keypoints_and_create_polygon_spanning_tuples_of_keypoints
  * (cbpm:261-443) and reduce_amount_of_keypoints_by_clustering (cbpm:137-259); the Ward clustering

@@ -83,7 +83,8 @@ int ssp_destroy(ssp_ctx* ctx) {
                          &ctx->p_tmp_feat, &ctx->p_pairs,     &ctx->p_argmin,    &ctx->p_mindist,
                          &ctx->p_counts,   &ctx->p_offsets,   &ctx->p_m1,        &ctx->p_m2,
                          &ctx->p_md,       &ctx->p_flops,     &ctx->b_img,       &ctx->b_xy,        &ctx->b_disc,
-                         &ctx->b_out,      &ctx->c_mask,      &ctx->c_work,      &ctx->c_blocks,    &ctx->c_cand};
+                         &ctx->b_out,      &ctx->c_mask,      &ctx->c_work,      &ctx->c_blocks,    &ctx->c_cand,
+                         &ctx->r_pairs,    &ctx->r_kp,        &ctx->r_out};
   for (ssp::DevBuf* b : bufs) b->release();
   for (ssp::PolyImage& pi : ctx->poly) {
     pi.feat.release();

@@ -169,6 +169,9 @@ struct ssp_ctx {
 
   // candidate generation (row N2)
   ssp::DevBuf c_mask, c_work, c_blocks, c_cand;
+
+  // batched RANSAC (row N3)
+  ssp::DevBuf r_pairs, r_kp, r_out;
 };
 
 namespace ssp {

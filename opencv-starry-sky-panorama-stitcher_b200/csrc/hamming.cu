@@ -329,17 +329,18 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
 namespace ssp {
 
 // How the tensor variant does the cross-check (environment variable SSP_B200_CROSSCHECK):
-//   fused  (default) one launch: the column direction comes out of the forward accumulators
-//   sparse           round 1's form: forward launch, then a reverse launch over the claimed rows
+//   sparse (default) forward launch, then a reverse launch over the claimed rows only (1.64 passes)
+//   fused            one launch: the column direction comes out of the forward accumulators (exact, but
+//                    ~1.5 column events per warp and tile make it slower than two passes: DESIGN.md)
 //   dense            both directions as dense work items of one launch (what the POPC variants do)
 enum CrossForm { CC_FUSED, CC_SPARSE, CC_DENSE };
 static CrossForm cross_form() {   // read per call: tests and A/B runs switch it between calls
   const char* d = getenv("SSP_B200_CROSSCHECK_DENSE");
   if (d && d[0] == '1') return CC_DENSE;
   const char* e = getenv("SSP_B200_CROSSCHECK");
-  if (e && e[0] == 's') return CC_SPARSE;
+  if (e && e[0] == 'f') return CC_FUSED;
   if (e && e[0] == 'd') return CC_DENSE;
-  return CC_FUSED;
+  return CC_SPARSE;
 }
 
 static int hamming_match_impl(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, int mode, double ratio,

@@ -394,14 +394,20 @@ poly_compare_f64_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ ar
 // that owns the row (shuffle broadcast, ascending lane = ascending column order per row, rare:
 // O(log P2) per row), which applies the sequential rule of the reference unchanged.  Thresholds
 // used for pruning are the row's own, possibly a few entries stale, i.e. never too small: exact.
-constexpr int PQ_TILE = 256;                 // columns per shared-memory tile
+#ifndef PQ_TILE_COLS
+#define PQ_TILE_COLS 128
+#endif
+#ifndef PQ_UNROLL
+#define PQ_UNROLL 4      // columns whose first-group sums are in flight together (independent FP64 chains)
+#endif
+constexpr int PQ_TILE = PQ_TILE_COLS;        // columns per shared-memory tile (shared memory bounds the occupancy)
 constexpr int PQ_QUEUE = 64;                 // queue entries per warp (a batch runs as soon as 32 wait)
 constexpr int PQ_G2 = 3 - POLY_G0 - POLY_G1; // the third property group
 
 __global__ void __launch_bounds__(PC_THREADS)
 poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ argmin,
                               double* __restrict__ mindist, unsigned long long* __restrict__ executed_flops) {
-  __shared__ __align__(16) double tile[PQ_TILE * 15];
+  __shared__ __align__(16) double tile[(PQ_TILE + PQ_UNROLL) * 15];
   __shared__ __align__(16) double rows_s[PC_THREADS * 10];     // groups POLY_G1 and PQ_G2 of every row of the CTA
   __shared__ double thr_s[PC_THREADS];
   __shared__ double q_g0[PC_THREADS / 32][PQ_QUEUE];
@@ -496,42 +502,52 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
     for (int i = threadIdx.x; i < ncol * 15; i += PC_THREADS)
       tile[i] = pp.f2[(long long)c0 * 15 + i];
     __syncthreads();
-    for (int j = 0; j < ncol; ++j) {
-      const double* b = tile + j * 15;
-      double g0 = 0.0;
+    for (int j0 = 0; j0 < ncol; j0 += PQ_UNROLL) {
+      double g0[PQ_UNROLL];
 #pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        const double d = __dsub_rn(a[POLY_G0 * 5 + k], b[POLY_G0 * 5 + k]);
-        const double sq = __dmul_rn(d, d);
-        g0 = (k == 0) ? sq : __dadd_rn(g0, sq);
-      }
-      const bool pass = g0 < thr;
-      const unsigned m = __ballot_sync(0xffffffffu, pass);
-      if (m) {
-        if (pass) {
-          const int pos = q_n + __popc(m & ((1u << lane) - 1u));
-          my_g0[pos] = g0;
-          my_rc[pos] = (lane << 16) | j;
+      for (int u = 0; u < PQ_UNROLL; ++u) {
+        // columns past the end of a ragged tile read stale shared memory; they never pass (j < ncol below)
+        const double* b = tile + (j0 + u) * 15;
+        double acc = 0.0;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const double d = __dsub_rn(a[POLY_G0 * 5 + k], b[POLY_G0 * 5 + k]);
+          const double sq = __dmul_rn(d, d);
+          acc = (k == 0) ? sq : __dadd_rn(acc, sq);
         }
-        q_n += __popc(m);
-        __syncwarp();
-        if (q_n >= 32) {
-          run_batch(0, 32, c0);
-          // the (at most 31) entries behind the batch move to the front
-          const int rest = q_n - 32;
-          double mg = 0.0;
-          int mr = 0;
-          if (lane < rest) {
-            mg = my_g0[32 + lane];
-            mr = my_rc[32 + lane];
+        g0[u] = acc;
+      }
+#pragma unroll
+      for (int u = 0; u < PQ_UNROLL; ++u) {
+        const int j = j0 + u;
+        const bool pass = j < ncol && g0[u] < thr;
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (m) {
+          if (pass) {
+            const int pos = q_n + __popc(m & ((1u << lane) - 1u));
+            my_g0[pos] = g0[u];
+            my_rc[pos] = (lane << 16) | j;
           }
+          q_n += __popc(m);
           __syncwarp();
-          if (lane < rest) {
-            my_g0[lane] = mg;
-            my_rc[lane] = mr;
+          if (q_n >= 32) {
+            run_batch(0, 32, c0);
+            // the (at most 31) entries behind the batch move to the front
+            const int rest = q_n - 32;
+            double mg = 0.0;
+            int mr = 0;
+            if (lane < rest) {
+              mg = my_g0[32 + lane];
+              mr = my_rc[32 + lane];
+            }
+            __syncwarp();
+            if (lane < rest) {
+              my_g0[lane] = mg;
+              my_rc[lane] = mr;
+            }
+            q_n = rest;
+            __syncwarp();
           }
-          q_n = rest;
-          __syncwarp();
         }
       }
     }
@@ -999,8 +1015,9 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
     int* am = ctx->p_argmin.as<int>();
     double* md = ctx->p_mindist.as<double>();
     const bool ms = (shift_mode == SSP_SHIFT_MIN_OVER_SHIFTS);
-    const char* env = getenv("SSP_B200_POLY_COMPARE");   // "legacy": round 1's per-lane pruning (A/B)
-    const bool legacy = env && env[0] == 'l';
+    // "queue": the compacted-pruning kernel (round 2; slower so far), default: per-lane pruning
+    const char* env = getenv("SSP_B200_POLY_COMPARE");
+    const bool legacy = !(env && env[0] == 'q');
     if (precision == SSP_PRECISION_FP64) {
       if (ms) poly_compare_f64_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
       else if (legacy) poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);

@@ -49,7 +49,8 @@ class CustomBruteForceMatcher:
                  disable_prompts=False, enforce_star_polygon_matcher=False,
                  output_dir_polygon_matching, predefined_overlaps, focal_length_pinhole,
                  engine: Engine = None, hamming_mode="crosscheck", hamming_variant="auto",
-                 write_debug_images=None, verbose=True, polygon_candidate_generation="host"):
+                 write_debug_images=None, verbose=True, polygon_candidate_generation="host",
+                 ransac="opencv", ransac_hypotheses=2048, ransac_seed=0):
         self.imgs_features_orb_and_stars = imgs_features_orb_and_stars
         self.imgs_features_len_orb = imgs_features_len_orb
         self.conf_thresh = conf_thresh
@@ -77,6 +78,15 @@ class CustomBruteForceMatcher:
         self.write_debug_images = _debug_images_enabled(write_debug_images)
         self.verbose = verbose
         self.polygon_candidate_generation = polygon_candidate_generation  # "device": row N2 (BFPolygonMatcher)
+        # "opencv": cv.findHomography per pair exactly as the reference (parity).  "device": row N3,
+        # one batched RANSAC launch for all ORB pairs right behind kernel 1 (same model, not OpenCV's
+        # random numbers: inlier sets agree closely, bits do not); the star path stays on OpenCV.
+        if ransac not in ("opencv", "device"):
+            raise ValueError("ransac must be 'opencv' or 'device'")
+        self.ransac = ransac
+        self.ransac_hypotheses = ransac_hypotheses
+        self.ransac_seed = ransac_seed
+        self._orb_models = dict()   # (src, dst) -> (H or None, inlier mask list) from the batched RANSAC
         self._bank_generation = None  # Engine.bank_generation of MY upload
         self._orb_matches = dict()  # (src, dst) -> tuple of cv2.DMatch, filled by prefetch
 
@@ -128,6 +138,19 @@ class CustomBruteForceMatcher:
                                               variant=self.hamming_variant)
         for k, p in enumerate(pairs):
             self._orb_matches[p] = dmatches_from_arrays(*res.pair(k))
+        if self.ransac == "device":
+            kp_xy = [np.array([kp.pt for kp in ft.keypoints[0:n_orb]], dtype=np.float32).reshape(-1, 2)
+                     for ft, n_orb in zip(self.imgs_features_orb_and_stars, self.imgs_features_len_orb)]
+            H, mask, inl = self.engine.ransac_homography_pairs(
+                kp_xy, pairs, int(res.offsets[-1]), reproj_threshold=self.RANSAC_REPROJ_THRESHOLD_PX,
+                n_hypotheses=self.ransac_hypotheses, seed=self.ransac_seed,
+                min_matches=self.MIN_MATCHES_FOR_HOMOGRAPHY)
+            for k, p in enumerate(pairs):
+                lo, hi = int(res.offsets[k]), int(res.offsets[k + 1])
+                if inl[k] < 0:
+                    continue                       # fewer than 6 matches: the host branch handles it (Q2)
+                model = None if np.isnan(H[k]).any() else H[k].copy()
+                self._orb_models[p] = (model, mask[lo:hi].astype(np.int64).tolist())
 
     def _hamming_matches(self, src_idx, dst_idx):
         key = (src_idx, dst_idx)
@@ -136,11 +159,14 @@ class CustomBruteForceMatcher:
         return self._orb_matches[key]
 
     # ---- MatchesInfo assembly (host, OpenCV) ------------------------------------------------
-    def _forward_info(self, matches, ft1, ft2, src_idx, dst_idx):
-        """RANSAC homography + confidence for one direction (:210-266 / :437-495)."""
-        src_pts = np.float32([ft1.keypoints[m.queryIdx].pt for m in matches]).reshape(-1, 1, 2)
-        dst_pts = np.float32([ft2.keypoints[m.trainIdx].pt for m in matches]).reshape(-1, 1, 2)
-        if len(matches) >= self.MIN_MATCHES_FOR_HOMOGRAPHY:
+    def _forward_info(self, matches, ft1, ft2, src_idx, dst_idx, model=None):
+        """RANSAC homography + confidence for one direction (:210-266 / :437-495).  `model` = (H, mask)
+        of the batched device RANSAC for these very matches, when that mode is on."""
+        if model is not None and len(matches) >= self.MIN_MATCHES_FOR_HOMOGRAPHY:
+            H, mask_list = model
+        elif len(matches) >= self.MIN_MATCHES_FOR_HOMOGRAPHY:
+            src_pts = np.float32([ft1.keypoints[m.queryIdx].pt for m in matches]).reshape(-1, 1, 2)
+            dst_pts = np.float32([ft2.keypoints[m.trainIdx].pt for m in matches]).reshape(-1, 1, 2)
             H, mask = cv.findHomography(src_pts, dst_pts, method=cv.RANSAC,
                                         ransacReprojThreshold=self.RANSAC_REPROJ_THRESHOLD_PX)
             mask_list = mask.ravel().tolist()
@@ -188,7 +214,8 @@ class CustomBruteForceMatcher:
         matches = self._hamming_matches(src_idx, dst_idx)
         self._log(f"\n[{src_idx:>3}] {self.img_names[src_idx][:24]:>25} <-> [{dst_idx:>3}] "
                   f"{self.img_names[dst_idx][:24]:>25}: {len(matches):>4} ORB matches ({self.hamming_mode})")
-        fwd, mask_list = self._forward_info(matches, ft1, ft2, src_idx, dst_idx)
+        fwd, mask_list = self._forward_info(matches, ft1, ft2, src_idx, dst_idx,
+                                            model=self._orb_models.get((src_idx, dst_idx)))
         back = self._mirrored_info(fwd, matches, mask_list, src_idx, dst_idx)
         pair = [fwd, back]
 

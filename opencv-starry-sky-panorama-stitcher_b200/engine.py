@@ -414,6 +414,29 @@ class Engine:
         return {"launches": n.value, "main_kernel_ms": ms.value, "evaluations": ev.value,
                 "executed_flops": fl.value if fl.value >= 0 else None}
 
+    # -- row N3 ---------------------------------------------------------------------------
+    def ransac_homography_pairs(self, keypoint_xy: Sequence[np.ndarray], pairs, n_matches: int,
+                                reproj_threshold: float = 5.0, n_hypotheses: int = 2048, seed: int = 0,
+                                min_matches: int = 6):
+        """Batched RANSAC homographies for the pairs of the LAST `hamming_match_pairs` call (same pair
+        list), point pairs gathered on the device from its survivors.  keypoint_xy[i]: (n_i, 2) pixel
+        coordinates of image i's keypoints.  Returns (H float64 (n_pairs, 3, 3) with NaN where no
+        model exists, inlier mask uint8 (n_matches,), n_inliers int32 (n_pairs,), -1 = fewer than
+        min_matches matches).  Opt-in stand-in for cv.findHomography(..., cv.RANSAC, 5)
+        (custom_bruteforce_matcher.py:215-246); same model, not OpenCV's random numbers."""
+        p = _as_pairs(pairs)
+        offs = np.zeros(len(keypoint_xy) + 1, dtype=np.int64)
+        np.cumsum([len(a) for a in keypoint_xy], out=offs[1:])
+        xy = np.ascontiguousarray(np.concatenate([np.asarray(a, dtype=np.float32).reshape(-1, 2) for a in keypoint_xy])
+                                  if offs[-1] else np.zeros((0, 2), np.float32))
+        H = np.empty((p.shape[0], 9), dtype=np.float64)
+        mask = np.empty(max(int(n_matches), 1), dtype=np.uint8)
+        inl = np.empty(p.shape[0], dtype=np.int32)
+        self._check(self._lib.ssp_ransac_homography_pairs(
+            self._ctx, _ptr(xy), _ptr(offs), len(offs) - 1, _ptr(p), p.shape[0], float(reproj_threshold),
+            int(n_hypotheses), int(seed) & 0xFFFFFFFF, int(min_matches), _ptr(H), _ptr(mask), mask.shape[0], _ptr(inl)))
+        return H.reshape(-1, 3, 3), mask[:int(n_matches)], inl
+
     # -- row N2 ---------------------------------------------------------------------------
     def star_regions(self, image: int) -> np.ndarray:
         """uint16 bit mask per star of `image`: membership in the 12 border regions of cbpm:328-375."""

@@ -226,7 +226,10 @@ def run_c2_stage(engine, st, feats, imgs, names, n_orb, tmp, tag, **kw):
         assert_info_equals_recording(mi, st, f"{tag}_m{k}")
     kinds = sorted(m.kind_of_pairwise_matches.items())
     assert [[s, d, 1 if v == "stars" else 0] for (s, d), v in kinds] == st[f"{tag}_kinds"].tolist()
-    assert m.fts_calculated_counter == st[f"{tag}_counter"].tolist()
+    if tag == "overlaps":
+        # only the first recording started from an empty polygon cache (make_golden.py hands the
+        # dict on to the other two so that the reference's brightness loop runs once per image)
+        assert m.fts_calculated_counter == st[f"{tag}_counter"].tolist()
     return m, raw, infos
 
 
