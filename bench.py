@@ -418,6 +418,30 @@ def hamming_record(rt, wl, sets, pairs, mode, variant, steps, warmup, cpu_pairs)
     if rank == 0:
         assert int(out.offsets[-1]) == n_matches, "e2e and resident legs disagree on the survivor count"
 
+    # one more end-to-end step with a device synchronisation after every piece: where its time goes
+    # (max over ranks per piece; the pieces overlap a little less than in the timed steps)
+    timeline = {}
+
+    def piece(name, fn):
+        rt.barrier()
+        t0 = time.perf_counter()
+        r = fn()
+        torch.cuda.synchronize(rt.dev)
+        timeline[name] = rt.max_over_ranks((time.perf_counter() - t0) * 1e3)
+        return r
+
+    if world > 1:
+        b_t, o_all = piece("h2d_on_rank0+broadcast", lambda: broadcast_descriptor_bank(bank, offs, 0))
+        piece("bind", lambda: eng.bind_descriptor_bank(b_t.data_ptr(), o_all, keepalive=b_t))
+        local = piece("expand+kernel1+finalize", lambda: eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, fetch=False))
+        piece("gather_to_rank0+d2h", lambda: gather_matches_resident(eng, local.offsets, dst=0))
+    else:
+        piece("h2d", lambda: eng.upload_descriptor_bank(bank, offs))
+        local = piece("expand+kernel1+finalize", lambda: eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, fetch=False))
+        n_loc = int(local.offsets[-1])
+        bufs = [eng.pinned_array(k, n_loc, np.int32) for k in ("hq", "ht", "hd")]
+        piece("d2h", lambda: eng.hamming_fetch_into(*(b.ctypes.data for b in bufs), n_loc, device=False))
+
     # ---- roofline of the dominant kernel -------------------------------------------------------
     info = eng.device_info()
     main_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
@@ -482,7 +506,7 @@ def hamming_record(rt, wl, sets, pairs, mode, variant, steps, warmup, cpu_pairs)
             "matches_per_step": n_matches,
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": bank_bytes + len(offs_known) * 8,
                     "d2h_bytes_per_step": d2h, "steps": steps, "ms_per_step": e2e_s * 1e3,
-                    "gcmp_per_s": comparisons / e2e_s / 1e9},
+                    "gcmp_per_s": comparisons / e2e_s / 1e9, "timeline_ms": timeline},
             "gpu_launches": launches_all,
             "clocks": clk,
             "roofline": roofline,

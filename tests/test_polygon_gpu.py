@@ -343,3 +343,31 @@ def test_device_candidate_generation_yields_the_reference_candidate_set(engine, 
         assert got == want and len(store[i]["all_possible_polygons_ftX"]) == len(want), i
         ref_polys = {tuple(r) for r in c2[f"i{i}_norm_idx"].tolist()}
         assert {tuple(r) for r in store[i]["polygons_from_ftX"]["keypoint_indices_rotated_list"].tolist()} == ref_polys
+
+
+# ---- kernel 3: the compacted-pruning variant is the same function -----------------------------------
+
+@pytest.mark.parametrize("rows,cols", [(1, 1), (33, 257), (700, 4100), (3000, 3000)])
+def test_queue_compare_kernel_equals_per_lane_pruning_and_numpy(engine, monkeypatch, rows, cols):
+    """SSP_B200_POLY_COMPARE=queue (survivors of the first property group are queued per warp and
+    evaluated as dense batches) must return the per-lane kernel's argmin / mindist bit for bit, also
+    with duplicate columns (ties keep the first) and ragged tile ends."""
+    feat = synth.polygon_feature_bank(2, max(rows, cols), seed=41)
+    f1, f2 = feat[0][:rows].copy(), feat[1][:cols].copy()
+    if cols > 40:
+        f2[cols // 2] = f2[7]            # duplicate columns: equal distances, the earlier one must win
+        f2[cols - 1] = f2[3]
+    if rows > 5 and cols > 9:
+        f1[5] = f2[9]                    # an exact match: distance 0
+    engine.polygon_upload_features(0, f1)
+    engine.polygon_upload_features(1, f2)
+    out = {}
+    for kind in ("legacy", "queue"):
+        monkeypatch.setenv("SSP_B200_POLY_COMPARE", kind)
+        out[kind] = engine.polygon_match_pairs([(0, 1)], threshold=10.0, return_rowmin=True)
+    np.testing.assert_array_equal(out["queue"].argmin, out["legacy"].argmin)
+    np.testing.assert_array_equal(out["queue"].mindist, out["legacy"].mindist)
+    m = PolygonOracle.compare(f1, f2)
+    np.testing.assert_array_equal(out["queue"].argmin, np.argmin(m, axis=1))
+    np.testing.assert_array_equal(out["queue"].mindist, m.min(axis=1))
+    assert engine.polygon_last_stats()["executed_flops"] > 0
