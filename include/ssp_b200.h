@@ -254,15 +254,18 @@ int ssp_star_regions(ssp_ctx* ctx, int image, uint16_t* region_mask, int64_t cap
 int ssp_cluster_brightest(ssp_ctx* ctx, int image, const int32_t* members, const int32_t* labels,
                           const int32_t* region_offsets, int n_regions, int max_labels,
                           int32_t* survivors);
-/* cbpm:407-413: the union over the 12 regions of all 5-combinations of each region's stars
- * (region_members: the regions' ascending star ids back to back, region_counts[12]).  *n_unique =
- * size of the union.  If 0 < *n_unique <= max_candidates and device_candidates != NULL the tuples
- * are written to an engine-owned int32 (n, 5) table on the device -- region-major, lexicographic
- * inside a region; a set listed by several regions belongs to the first -- and its address is
+/* cbpm:407-413: set(itertools.combinations(region list, 5) for each of the 12 regions).
+ * region_members: the regions' star ids back to back IN LIST ORDER (the order decides which tuples
+ * are equal), region_counts[12].  *n_tuples = number of distinct tuples, i.e. len() of the reference's
+ * set, the number its reduction loop compares with the maximum (five stars listed by two regions in a
+ * different relative order count twice); *n_unique = number of distinct star SETS.  If
+ * 0 < *n_tuples <= max_candidates and device_candidates != NULL, one tuple per distinct star set is
+ * written to an engine-owned int32 (n_unique, 5) table on the device -- region-major, combination
+ * order inside a region; a set listed by several regions belongs to the first -- and its address is
  * returned for ssp_polygon_measure(..., SSP_MEM_DEVICE); otherwise *device_candidates = NULL (the
  * host retries with fewer stars per region, as the reference's while loop does). */
 int ssp_polygon_candidates(ssp_ctx* ctx, const int32_t* region_members, const int32_t* region_counts,
-                           int n_regions, int64_t max_candidates, int64_t* n_unique,
+                           int n_regions, int64_t max_candidates, int64_t* n_tuples, int64_t* n_unique,
                            const int32_t** device_candidates);
 
 /* ---- row N1: star brightness ----------------------------------------------------------

@@ -73,7 +73,7 @@ PROTOTYPES = {
     "ssp_star_regions": (_c.c_int, [_ctx_p, _c.c_int, _vp, _c.c_int64]),
     "ssp_cluster_brightest": (_c.c_int, [_ctx_p, _c.c_int, _i32p, _i32p, _i32p, _c.c_int, _c.c_int, _i32p]),
     "ssp_polygon_candidates": (_c.c_int, [_ctx_p, _i32p, _i32p, _c.c_int, _c.c_int64, _c.POINTER(_c.c_int64),
-                                          _c.POINTER(_c.c_void_p)]),
+                                          _c.POINTER(_c.c_int64), _c.POINTER(_c.c_void_p)]),
     "ssp_star_brightness": (_c.c_int, [_ctx_p, _u8p, _c.c_int, _c.c_int, _i32p, _c.c_int64, _i32p,
                                        _c.c_int, _c.c_int, _i32p, _c.c_int]),
 }

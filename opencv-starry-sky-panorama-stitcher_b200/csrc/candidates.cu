@@ -8,9 +8,10 @@
 //                              comparisons in float64, exactly the reference's expressions);
 //   * cluster_brightest_kernel per cluster of a region keep the brightest star, the LAST of
 //                              equally bright ones (cbpm:230-245: ascending stable sort, reversed);
-//   * cand_count / cand_write  all C(n_r, 5) combinations of every region's member list, the union
-//                              over the regions without duplicates, in a deterministic order
-//                              (itertools.combinations + set() in the reference, cbpm:407-413).
+//   * cand_kernel              all C(n_r, 5) combinations of every region's member list: the number of
+//                              distinct TUPLES (what the reference's loop counts, cbpm:383, 407-413:
+//                              itertools.combinations + set()) and the table of distinct star SETS
+//                              (what gets measured), in a deterministic order.
 // The Ward clustering itself (sklearn.cluster.AgglomerativeClustering, cbpm:175-181) stays on the
 // host: its labels are an input here.  The candidate SET equals the reference's; the ORDER is
 // region-major / lexicographic instead of CPython's set iteration order, which is why this path is
@@ -22,7 +23,7 @@ namespace ssp {
 constexpr int CG_REGIONS = 12;
 constexpr int CG_MAX_MEMBERS = 32;   // members per region the enumeration accepts (reference: <= 15)
 constexpr int CG_THREADS = 256;
-constexpr int CG_MAX_STARS = 4096;   // star ids the duplicate test can index
+constexpr int CG_MAX_STARS = 2048;   // star ids the duplicate test can index (reference: the 1000 brightest)
 
 // cbpm:319-375.  Bit r of mask[i] = star i lies in region r, regions in the reference's dict order:
 // left_top, left_bot, left_mid, right_top, right_bot, right_mid, top_left, top_right, top_mid,
@@ -101,7 +102,7 @@ cluster_brightest_kernel(const int* __restrict__ members, const int* __restrict_
 }
 
 struct CandRegions {
-  int count[CG_REGIONS];                       // members of every region (ascending star ids)
+  int count[CG_REGIONS];                       // members of every region, in the region's LIST order
   int member[CG_REGIONS][CG_MAX_MEMBERS];
   int combos[CG_REGIONS];                      // C(count, 5)
   int block_off[CG_REGIONS + 1];               // prefix of ceil(combos / CG_THREADS)
@@ -129,13 +130,18 @@ __device__ __forceinline__ void unrank5(int rank, int n, int (&c)[5]) {
   }
 }
 
-// A 5-set listed by region r is a duplicate iff all five stars are ALSO members of an earlier
-// region: then that region lists the same set (members are ascending, so as the same tuple).
+// The reference builds set(itertools.combinations(region list, 5) for every region) (cbpm:407-413): a
+// set of TUPLES, so five stars listed by two regions in a different relative order count twice -- and
+// that count is what its reduction loop compares with the maximum.  Measured, both tuples are the
+// same polygon (its dict is keyed by hull order, cbpm:593).  Hence two answers per combination:
+//   tuple duplicate: an EARLIER region lists all five stars in the same relative order  -> not counted
+//   set duplicate:   an earlier region lists all five stars at all                      -> not written
 template <bool WRITE>
 __global__ void __launch_bounds__(CG_THREADS)
-cand_kernel(CandRegions cr, int* __restrict__ block_count, int* __restrict__ out) {
-  __shared__ unsigned short member_mask[CG_MAX_STARS];   // star id -> regions that currently list it
-  __shared__ int warp_cnt[CG_THREADS / 32];
+cand_kernel(CandRegions cr, int* __restrict__ block_tuples, int* __restrict__ block_sets, int* __restrict__ out) {
+  __shared__ unsigned short member_mask[CG_MAX_STARS];        // star id -> regions that currently list it
+  __shared__ unsigned char pos_in[CG_REGIONS][CG_MAX_STARS];  // position of the star in that region's list
+  __shared__ int warp_cnt[2][CG_THREADS / 32];
   __shared__ int base_s;
   int region = 0;
   while (region + 1 < CG_REGIONS && (int)blockIdx.x >= cr.block_off[region + 1]) ++region;
@@ -143,11 +149,13 @@ cand_kernel(CandRegions cr, int* __restrict__ block_count, int* __restrict__ out
   for (int i = threadIdx.x; i < CG_MAX_STARS; i += CG_THREADS) member_mask[i] = 0;
   __syncthreads();
   if (threadIdx.x < CG_REGIONS)
-    for (int k = 0; k < cr.count[threadIdx.x]; ++k)
-      atomicOr(reinterpret_cast<unsigned*>(member_mask) + (cr.member[threadIdx.x][k] >> 1),
-               (1u << threadIdx.x) << (16 * (cr.member[threadIdx.x][k] & 1)));
+    for (int k = 0; k < cr.count[threadIdx.x]; ++k) {
+      const int id = cr.member[threadIdx.x][k];
+      atomicOr(reinterpret_cast<unsigned*>(member_mask) + (id >> 1), (1u << threadIdx.x) << (16 * (id & 1)));
+      pos_in[threadIdx.x][id] = (unsigned char)k;
+    }
   __syncthreads();
-  bool keep = false;
+  bool new_tuple = false, new_set = false;
   int id[5] = {0, 0, 0, 0, 0};
   if (rank < cr.combos[region]) {
     int c[5];
@@ -158,41 +166,70 @@ cand_kernel(CandRegions cr, int* __restrict__ block_count, int* __restrict__ out
       id[k] = cr.member[region][c[k]];
       common &= member_mask[id[k]];
     }
-    keep = (common & ((1u << region) - 1u)) == 0;
+    unsigned earlier = common & ((1u << region) - 1u);
+    new_set = earlier == 0;
+    new_tuple = true;
+    while (earlier) {
+      const int a = __ffs((int)earlier) - 1;
+      earlier &= earlier - 1;
+      bool same_order = true;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) same_order = same_order && pos_in[a][id[k]] < pos_in[a][id[k + 1]];
+      if (same_order) new_tuple = false;
+    }
   }
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const unsigned ballot = __ballot_sync(0xffffffffu, keep);
-  if (lane == 0) warp_cnt[wid] = __popc(ballot);
+  const unsigned ballot_t = __ballot_sync(0xffffffffu, new_tuple);
+  const unsigned ballot_s = __ballot_sync(0xffffffffu, new_set);
+  if (lane == 0) {
+    warp_cnt[0][wid] = __popc(ballot_t);
+    warp_cnt[1][wid] = __popc(ballot_s);
+  }
   __syncthreads();
-  int before = 0, total = 0;
+  int before = 0, total_t = 0, total_s = 0;
 #pragma unroll
   for (int w = 0; w < CG_THREADS / 32; ++w) {
-    before += (w < wid) ? warp_cnt[w] : 0;
-    total += warp_cnt[w];
+    before += (w < wid) ? warp_cnt[1][w] : 0;
+    total_t += warp_cnt[0][w];
+    total_s += warp_cnt[1][w];
   }
   if (!WRITE) {
-    if (threadIdx.x == 0) block_count[blockIdx.x] = total;
+    if (threadIdx.x == 0) {
+      block_tuples[blockIdx.x] = total_t;
+      block_sets[blockIdx.x] = total_s;
+    }
     return;
   }
   if (threadIdx.x == 0) {
     int b = 0;
-    for (int k = 0; k < (int)blockIdx.x; ++k) b += block_count[k];   // <= a few hundred blocks
+    for (int k = 0; k < (int)blockIdx.x; ++k) b += block_sets[k];   // <= a few hundred blocks
     base_s = b;
   }
   __syncthreads();
-  if (keep) {
-    const int pos = base_s + before + __popc(ballot & ((1u << lane) - 1u));
+  if (new_set) {
+    const int pos = base_s + before + __popc(ballot_s & ((1u << lane) - 1u));
 #pragma unroll
     for (int k = 0; k < 5; ++k) out[pos * 5 + k] = id[k];
   }
 }
 
-__global__ void cand_total_kernel(const int* __restrict__ block_count, int n_blocks, long long* __restrict__ total) {
-  long long t = 0;
-  for (int k = threadIdx.x; k < n_blocks; k += 32) t += block_count[k];
+// totals[0] = distinct tuples (the reference's len(set)), totals[1] = distinct star sets (table rows)
+__global__ void cand_total_kernel(const int* __restrict__ block_tuples, const int* __restrict__ block_sets,
+                                  int n_blocks, long long* __restrict__ totals) {
+  long long t = 0, u = 0;
+  for (int k = threadIdx.x; k < n_blocks; k += 32) {
+    t += block_tuples[k];
+    u += block_sets[k];
+  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-  if (threadIdx.x == 0) *total = t;
+  for (int o = 16; o > 0; o >>= 1) {
+    t += __shfl_xor_sync(0xffffffffu, t, o);
+    u += __shfl_xor_sync(0xffffffffu, u, o);
+  }
+  if (threadIdx.x == 0) {
+    totals[0] = t;
+    totals[1] = u;
+  }
 }
 
 }  // namespace ssp
@@ -264,14 +301,14 @@ int ssp_cluster_brightest(ssp_ctx* ctx, int image, const int32_t* members, const
 }
 
 int ssp_polygon_candidates(ssp_ctx* ctx, const int32_t* region_members, const int32_t* region_counts,
-                           int n_regions, int64_t max_candidates, int64_t* n_unique,
+                           int n_regions, int64_t max_candidates, int64_t* n_tuples, int64_t* n_unique,
                            const int32_t** device_candidates) {
   using namespace ssp;
   if (!ctx) return SSP_ERR_INVALID;
   if (int rc = use_device(ctx)) return rc;
   SSP_REQUIRE(ctx, n_regions == CG_REGIONS, SSP_ERR_INVALID,
               "ssp_polygon_candidates: the reference has %d regions (cbpm:328-375), got %d", CG_REGIONS, n_regions);
-  SSP_REQUIRE(ctx, region_members != nullptr && region_counts != nullptr && n_unique != nullptr,
+  SSP_REQUIRE(ctx, region_members != nullptr && region_counts != nullptr && n_tuples != nullptr && n_unique != nullptr,
               SSP_ERR_INVALID, "ssp_polygon_candidates: NULL argument");
   CandRegions cr;
   int cursor = 0, blocks = 0;
@@ -282,9 +319,11 @@ int ssp_polygon_candidates(ssp_ctx* ctx, const int32_t* region_members, const in
     cr.count[r] = n;
     for (int k = 0; k < n; ++k) {
       const int id = region_members[cursor + k];
-      SSP_REQUIRE(ctx, id >= 0 && id < CG_MAX_STARS && (k == 0 || id > region_members[cursor + k - 1]),
-                  SSP_ERR_INVALID, "ssp_polygon_candidates: region %d: star ids must be ascending and < %d", r,
-                  CG_MAX_STARS);
+      SSP_REQUIRE(ctx, id >= 0 && id < CG_MAX_STARS, SSP_ERR_INVALID,
+                  "ssp_polygon_candidates: region %d: star id %d outside [0, %d)", r, id, CG_MAX_STARS);
+      for (int j = 0; j < k; ++j)
+        SSP_REQUIRE(ctx, region_members[cursor + j] != id, SSP_ERR_INVALID,
+                    "ssp_polygon_candidates: region %d lists star %d twice", r, id);
       cr.member[r][k] = id;
     }
     for (int k = n; k < CG_MAX_MEMBERS; ++k) cr.member[r][k] = 0;
@@ -296,24 +335,28 @@ int ssp_polygon_candidates(ssp_ctx* ctx, const int32_t* region_members, const in
     blocks += (cr.combos[r] + CG_THREADS - 1) / CG_THREADS;
   }
   cr.block_off[CG_REGIONS] = blocks;
+  *n_tuples = 0;
   *n_unique = 0;
   if (device_candidates) *device_candidates = nullptr;
   if (blocks == 0) return SSP_OK;
   NvtxRange range("candidate enumeration");
-  SSP_CUDA_TRY(ctx, ctx->c_blocks.ensure((size_t)blocks * 4 + 16));
-  int* d_counts = ctx->c_blocks.as<int>();
-  long long* d_total = reinterpret_cast<long long*>(ctx->c_blocks.as<char>() + ((size_t)blocks * 4 + 7) / 8 * 8);
-  cand_kernel<false><<<(unsigned)blocks, CG_THREADS, 0, ctx->stream>>>(cr, d_counts, nullptr);
+  SSP_CUDA_TRY(ctx, ctx->c_blocks.ensure((size_t)blocks * 8 + 32));
+  int* d_tuples = ctx->c_blocks.as<int>();
+  int* d_sets = d_tuples + blocks;
+  long long* d_totals = reinterpret_cast<long long*>(ctx->c_blocks.as<char>() + ((size_t)blocks * 8 + 15) / 16 * 16);
+  cand_kernel<false><<<(unsigned)blocks, CG_THREADS, 0, ctx->stream>>>(cr, d_tuples, d_sets, nullptr);
   SSP_CUDA_TRY(ctx, cudaGetLastError());
-  cand_total_kernel<<<1, 32, 0, ctx->stream>>>(d_counts, blocks, d_total);
+  cand_total_kernel<<<1, 32, 0, ctx->stream>>>(d_tuples, d_sets, blocks, d_totals);
   SSP_CUDA_TRY(ctx, cudaGetLastError());
-  long long total = 0;
-  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&total, d_total, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  long long totals[2] = {0, 0};
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(totals, d_totals, 16, cudaMemcpyDeviceToHost, ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  *n_unique = total;
-  if (total == 0 || total > max_candidates || !device_candidates) return SSP_OK;   // the host tries the next k
-  SSP_CUDA_TRY(ctx, ctx->c_cand.ensure((size_t)total * 20 + 16));
-  cand_kernel<true><<<(unsigned)blocks, CG_THREADS, 0, ctx->stream>>>(cr, d_counts, ctx->c_cand.as<int>());
+  *n_tuples = totals[0];
+  *n_unique = totals[1];
+  // the reference's loop condition looks at the TUPLE count (cbpm:383); the host retries with fewer stars
+  if (totals[0] == 0 || totals[0] > max_candidates || !device_candidates) return SSP_OK;
+  SSP_CUDA_TRY(ctx, ctx->c_cand.ensure((size_t)totals[1] * 20 + 16));
+  cand_kernel<true><<<(unsigned)blocks, CG_THREADS, 0, ctx->stream>>>(cr, d_tuples, d_sets, ctx->c_cand.as<int>());
   SSP_CUDA_TRY(ctx, cudaGetLastError());
   *device_candidates = ctx->c_cand.as<int>();
   return SSP_OK;

@@ -401,7 +401,7 @@ poly_compare_f64_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ ar
 #define PQ_UNROLL 4      // columns whose first-group sums are in flight together (independent FP64 chains)
 #endif
 constexpr int PQ_TILE = PQ_TILE_COLS;        // columns per shared-memory tile (shared memory bounds the occupancy)
-constexpr int PQ_QUEUE = 64;                 // queue entries per warp (a batch runs as soon as 32 wait)
+constexpr int PQ_QUEUE = 32 * (PQ_UNROLL + 1);   // queue entries per warp: 31 left over + one column step of PQ_UNROLL x 32
 constexpr int PQ_G2 = 3 - POLY_G0 - POLY_G1; // the third property group
 
 __global__ void __launch_bounds__(PC_THREADS)
@@ -522,33 +522,34 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
         const int j = j0 + u;
         const bool pass = j < ncol && g0[u] < thr;
         const unsigned m = __ballot_sync(0xffffffffu, pass);
-        if (m) {
-          if (pass) {
-            const int pos = q_n + __popc(m & ((1u << lane) - 1u));
-            my_g0[pos] = g0[u];
-            my_rc[pos] = (lane << 16) | j;
-          }
-          q_n += __popc(m);
-          __syncwarp();
-          if (q_n >= 32) {
-            run_batch(0, 32, c0);
-            // the (at most 31) entries behind the batch move to the front
-            const int rest = q_n - 32;
-            double mg = 0.0;
-            int mr = 0;
-            if (lane < rest) {
-              mg = my_g0[32 + lane];
-              mr = my_rc[32 + lane];
-            }
-            __syncwarp();
-            if (lane < rest) {
-              my_g0[lane] = mg;
-              my_rc[lane] = mr;
-            }
-            q_n = rest;
-            __syncwarp();
-          }
+        if (pass) {
+          const int pos = q_n + __popc(m & ((1u << lane) - 1u));
+          my_g0[pos] = g0[u];
+          my_rc[pos] = (lane << 16) | j;
         }
+        q_n += __popc(m);
+      }
+      if (q_n >= 32) {   // one call site: dense batches from the front, the (< 32) rest moves up
+        __syncwarp();
+        int first = 0;
+        while (q_n - first >= 32) {
+          run_batch(first, 32, c0);
+          first += 32;
+        }
+        const int rest = q_n - first;
+        double mg = 0.0;
+        int mr = 0;
+        if (lane < rest) {
+          mg = my_g0[first + lane];
+          mr = my_rc[first + lane];
+        }
+        __syncwarp();
+        if (lane < rest) {
+          my_g0[lane] = mg;
+          my_rc[lane] = mr;
+        }
+        q_n = rest;
+        __syncwarp();
       }
     }
     flops += live ? 14u * (unsigned)ncol : 0u;

@@ -9,9 +9,8 @@
 //
 // NOT bit-compatible with OpenCV by nature (OpenCV's RNG, adaptive iteration count and final
 // Levenberg-Marquardt polish are its own): same model (4-point DLT hypotheses, reprojection
-// error <= threshold counts as inlier, best hypothesis wins, least-squares refit on its inliers,
-// mask = inliers of the best hypothesis as in cv::findHomography), fixed seed, fixed hypothesis
-// count.  tests/ and bench.py report inlier-count agreement with cv.findHomography.
+// error <= threshold counts as inlier, best hypothesis wins, then least-squares refits on the inliers
+// that are accepted while they gain inliers), fixed seed, fixed hypothesis count.  tests/ and bench.py report inlier-count agreement with cv.findHomography.
 //
 // One CTA per pair.  Points are Hartley-normalised per pair; every thread owns hypotheses
 // tid, tid + 256, ...: counter-based sampling of 4 distinct matches, degeneracy test (collinear
@@ -241,94 +240,128 @@ ransac_homography_kernel(const RansacPair* __restrict__ pairs, const int* __rest
     if (tid == 0) n_inliers_out[blockIdx.x] = 0;
     return;
   }
-  // ---- mask of the best hypothesis + least-squares refit (h33 = 1) on its inliers, normalised ----
-  float hb[9];
-#pragma unroll
-  for (int k = 0; k < 9; ++k) hb[k] = best_h[k];
-  double acc[44];
-#pragma unroll
-  for (int k = 0; k < 44; ++k) acc[k] = 0.0;
-  int inl = 0;
-  for (int i = tid; i < n; i += RS_THREADS) {
-    const float4 p = load_pt(i);
-    const float w = hb[6] * p.x + hb[7] * p.y + hb[8];
+  // ---- local optimisation: least-squares refit (h33 = 1, normalised) on the inliers of the current
+  // model, accepted while it gains inliers (a 4-point model through noisy points rarely holds all
+  // of them; cv::findHomography polishes with Levenberg-Marquardt instead) ----------------------------
+  __shared__ float cur_h[9];
+  __shared__ double refit_h[9];
+  __shared__ int refit_ok;
+  if (tid < 9) cur_h[tid] = best_h[tid];
+  __syncthreads();
+  auto is_inlier = [&](const float (&h)[9], const float4 p) {
+    const float w = h[6] * p.x + h[7] * p.y + h[8];
     const float iw = 1.f / w;
-    const float dx = (hb[0] * p.x + hb[1] * p.y + hb[2]) * iw - p.z;
-    const float dy = (hb[3] * p.x + hb[4] * p.y + hb[5]) * iw - p.w;
-    const bool in = dx * dx + dy * dy <= thresh_sq;
-    mask_out[pr.match_off + i] = in ? 1 : 0;
-    if (!in) continue;
-    ++inl;
-    const double x = (p.x - cs_x) * ss, y = (p.y - cs_y) * ss, u = (p.z - cd_x) * sd, v = (p.w - cd_y) * sd;
-    const double r0[9] = {x, y, 1.0, 0.0, 0.0, 0.0, -x * u, -y * u, u};
-    const double r1[9] = {0.0, 0.0, 0.0, x, y, 1.0, -x * v, -y * v, v};
-    // upper triangle of A^T A (8 x 8: 36 entries) and A^T b (8 entries)
-    int e = 0;
+    const float dx = (h[0] * p.x + h[1] * p.y + h[2]) * iw - p.z;
+    const float dy = (h[3] * p.x + h[4] * p.y + h[5]) * iw - p.w;
+    return dx * dx + dy * dy <= thresh_sq;
+  };
+  // least squares over the inliers of cur_h -> refit_h (pixel space, h33 = 1), refit_ok
+  auto refit = [&]() {
+    float hb[9];
 #pragma unroll
-    for (int a = 0; a < 8; ++a)
+    for (int k = 0; k < 9; ++k) hb[k] = cur_h[k];
+    double acc[44];
 #pragma unroll
-      for (int b = a; b < 8; ++b) acc[e++] += r0[a] * r0[b] + r1[a] * r1[b];
+    for (int k = 0; k < 44; ++k) acc[k] = 0.0;
+    for (int i = tid; i < n; i += RS_THREADS) {
+      const float4 p = load_pt(i);
+      if (!is_inlier(hb, p)) continue;
+      const double x = (p.x - cs_x) * ss, y = (p.y - cs_y) * ss, u = (p.z - cd_x) * sd, v = (p.w - cd_y) * sd;
+      const double r0[9] = {x, y, 1.0, 0.0, 0.0, 0.0, -x * u, -y * u, u};
+      const double r1[9] = {0.0, 0.0, 0.0, x, y, 1.0, -x * v, -y * v, v};
+      // upper triangle of A^T A (8 x 8: 36 entries) and A^T b (8 entries)
+      int e = 0;
 #pragma unroll
-    for (int a = 0; a < 8; ++a) acc[36 + a] += r0[a] * r0[8] + r1[a] * r1[8];
-  }
-  // reduce the 44 sums: warp shuffles, then one pass over the warps
+      for (int a = 0; a < 8; ++a)
 #pragma unroll
-  for (int k = 0; k < 44; ++k) {
-    double v = acc[k];
+        for (int b = a; b < 8; ++b) acc[e++] += r0[a] * r0[b] + r1[a] * r1[b];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((tid & 31) == 0) ata[tid >> 5][k] = v;
-  }
-  const int total_inl = (int)(block_sum((double)inl) + 0.5);
-  if (tid == 0) {
-    double M[8][9];
-    int e = 0;
-    for (int a = 0; a < 8; ++a)
-      for (int b = a; b < 8; ++b) {
+      for (int a = 0; a < 8; ++a) acc[36 + a] += r0[a] * r0[8] + r1[a] * r1[8];
+    }
+#pragma unroll
+    for (int k = 0; k < 44; ++k) {
+      double v = acc[k];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if ((tid & 31) == 0) ata[tid >> 5][k] = v;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      double M[8][9];
+      int e = 0;
+      for (int a = 0; a < 8; ++a)
+        for (int b = a; b < 8; ++b) {
+          double s = 0.0;
+          for (int w = 0; w < RS_THREADS / 32; ++w) s += ata[w][e];
+          M[a][b] = s;
+          M[b][a] = s;
+          ++e;
+        }
+      for (int a = 0; a < 8; ++a) {
         double s = 0.0;
-        for (int w = 0; w < RS_THREADS / 32; ++w) s += ata[w][e];
-        M[a][b] = s;
-        M[b][a] = s;
-        ++e;
+        for (int w = 0; w < RS_THREADS / 32; ++w) s += ata[w][36 + a];
+        M[a][8] = s;
       }
-    for (int a = 0; a < 8; ++a) {
-      double s = 0.0;
-      for (int w = 0; w < RS_THREADS / 32; ++w) s += ata[w][36 + a];
-      M[a][8] = s;
-    }
-    double hn[9];
-    bool ok = true;
-    for (int c = 0; c < 8 && ok; ++c) {
-      int piv = c;
-      double best = fabs(M[c][c]);
-      for (int r = c + 1; r < 8; ++r)
-        if (fabs(M[r][c]) > best) { best = fabs(M[r][c]); piv = r; }
-      ok = best > 1e-14;
-      if (!ok) break;
-      if (piv != c)
-        for (int k = c; k < 9; ++k) { const double t = M[c][k]; M[c][k] = M[piv][k]; M[piv][k] = t; }
-      for (int r = c + 1; r < 8; ++r) {
-        const double f = M[r][c] / M[c][c];
-        for (int k = c; k < 9; ++k) M[r][k] -= f * M[c][k];
+      double hn[9];
+      bool ok = true;
+      for (int c = 0; c < 8 && ok; ++c) {
+        int piv = c;
+        double best = fabs(M[c][c]);
+        for (int r = c + 1; r < 8; ++r)
+          if (fabs(M[r][c]) > best) { best = fabs(M[r][c]); piv = r; }
+        ok = best > 1e-14;
+        if (!ok) break;
+        if (piv != c)
+          for (int k = c; k < 9; ++k) { const double t = M[c][k]; M[c][k] = M[piv][k]; M[piv][k] = t; }
+        for (int r = c + 1; r < 8; ++r) {
+          const double f = M[r][c] / M[c][c];
+          for (int k = c; k < 9; ++k) M[r][k] -= f * M[c][k];
+        }
       }
-    }
-    if (ok) {
-      for (int c = 7; c >= 0; --c) {
-        double s = M[c][8];
-        for (int k = c + 1; k < 8; ++k) s -= M[c][k] * hn[k];
-        hn[c] = s / M[c][c];
+      if (ok) {
+        for (int c = 7; c >= 0; --c) {
+          double s = M[c][8];
+          for (int k = c + 1; k < 8; ++k) s -= M[c][k] * hn[k];
+          hn[c] = s / M[c][c];
+        }
+        hn[8] = 1.0;
+        double hp[9];
+        rs_denormalise(hn, norm_s[0], norm_s[1], norm_s[2], norm_s[3], norm_s[4], norm_s[5], hp);
+        ok = fabs(hp[8]) > 1e-12;
+        if (ok)
+          for (int k = 0; k < 9; ++k) refit_h[k] = hp[k] / hp[8];
       }
-      hn[8] = 1.0;
-      double hp[9];
-      rs_denormalise(hn, norm_s[0], norm_s[1], norm_s[2], norm_s[3], norm_s[4], norm_s[5], hp);
-      ok = fabs(hp[8]) > 1e-12 && total_inl >= 4;
-      if (ok)
-        for (int k = 0; k < 9; ++k) Hp[k] = hp[k] / hp[8];
+      refit_ok = ok ? 1 : 0;
     }
-    if (!ok)   // keep the RANSAC model itself
-      for (int k = 0; k < 9; ++k) Hp[k] = (double)hb[k];
-    n_inliers_out[blockIdx.x] = total_inl;
+    __syncthreads();
+  };
+  auto count_inliers = [&](const float (&h)[9]) {
+    int c = 0;
+    for (int i = tid; i < n; i += RS_THREADS) c += is_inlier(h, load_pt(i)) ? 1 : 0;
+    return (int)(block_sum((double)c) + 0.5);
+  };
+  int cur_count = best_count;
+  for (int round = 0; round < 4; ++round) {
+    refit();
+    if (!refit_ok) break;
+    float hr[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) hr[k] = (float)refit_h[k];
+    const int c = count_inliers(hr);          // uniform over the block
+    if (c <= cur_count) break;
+    __syncthreads();
+    if (tid < 9) cur_h[tid] = hr[tid];
+    cur_count = c;
+    __syncthreads();
   }
+  // the answer: mask = inliers of the accepted model, H = least squares over exactly those inliers
+  refit();
+  float hc[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) hc[k] = cur_h[k];
+  for (int i = tid; i < n; i += RS_THREADS) mask_out[pr.match_off + i] = is_inlier(hc, load_pt(i)) ? 1 : 0;
+  if (tid < 9) Hp[tid] = refit_ok ? refit_h[tid] : (double)hc[tid];
+  if (tid == 0) n_inliers_out[blockIdx.x] = cur_count;
 }
 
 }  // namespace ssp

@@ -247,7 +247,9 @@ class BFPolygonMatcher:
                 for g, r in enumerate(todo):
                     used = sorted(set(labels[off[g]:off[g + 1]]))        # `for cluster_id in unique_labels`
                     regions[r] = [int(surv[g, lab]) for lab in used]
-            n, ptr = eng.polygon_candidates(regions, maximum_number_of_polygons_per_image_region)
+            # the loop condition is on len(set of TUPLES) as in the reference (cbpm:383); the table holds
+            # one tuple per distinct star set
+            n_tuples, n, ptr = eng.polygon_candidates(regions, maximum_number_of_polygons_per_image_region)
             if ptr:
                 return n, ptr, regions
             k -= 1

@@ -50,7 +50,7 @@ class CustomBruteForceMatcher:
                  output_dir_polygon_matching, predefined_overlaps, focal_length_pinhole,
                  engine: Engine = None, hamming_mode="crosscheck", hamming_variant="auto",
                  write_debug_images=None, verbose=True, polygon_candidate_generation="host",
-                 ransac="opencv", ransac_hypotheses=2048, ransac_seed=0):
+                 ransac="opencv", ransac_hypotheses=4096, ransac_seed=0):
         self.imgs_features_orb_and_stars = imgs_features_orb_and_stars
         self.imgs_features_len_orb = imgs_features_len_orb
         self.conf_thresh = conf_thresh

