@@ -1016,9 +1016,10 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
     int* am = ctx->p_argmin.as<int>();
     double* md = ctx->p_mindist.as<double>();
     const bool ms = (shift_mode == SSP_SHIFT_MIN_OVER_SHIFTS);
-    // "queue": the compacted-pruning kernel (round 2; slower so far), default: per-lane pruning
+    // default: the compacted-pruning kernel (round 2: 85 ms against 108 ms at the 15 000 cap, bit-equal);
+    // SSP_B200_POLY_COMPARE=legacy selects round 1's per-lane pruning for A/B runs
     const char* env = getenv("SSP_B200_POLY_COMPARE");
-    const bool legacy = !(env && env[0] == 'q');
+    const bool legacy = env && env[0] == 'l';
     if (precision == SSP_PRECISION_FP64) {
       if (ms) poly_compare_f64_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
       else if (legacy) poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
