@@ -661,9 +661,8 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
     h2d += len(pairs) * 8
 
     def measure_all_local():
-        for i in range(n_img):
-            eng.polygon_measure_resident(i, cand_t[int(co[i]):].data_ptr(), int(co[i + 1] - co[i]), wait=False)
-        return 2 * n_img   # measure + scatter per image
+        eng.polygon_measure_batch_resident(list(range(n_img)), cand_t.data_ptr(), co)   # ONE launch pair for all images
+        return 2
 
     kernel_ms = []
 
@@ -672,7 +671,7 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
         if measured:
             if world > 1:
                 measure_polygons_sharded(eng, so, co, xy_t, br_t, cand_t, IMG_W, IMG_H, FOCAL)
-                n += 2 * len(range(rank, n_img, world)) + 1
+                n += 2 + 1   # star rays + measure batch + compaction
             else:
                 n += measure_all_local()
         res = eng.polygon_match_pairs(local_pairs, fp32=fp32, fetch=False)

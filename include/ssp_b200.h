@@ -179,6 +179,13 @@ int ssp_fetch_star_rays(ssp_ctx* ctx, double* rays, int64_t capacity_stars, int 
  * by the next ssp_polygon_count / _fetch / _match_pairs call. */
 int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int64_t n_candidates,
                         double min_side_px, int mem_kind, uint8_t* status, int64_t* n_valid);
+/* The same for several images in ONE launch pair (measure + compaction): images[k] owns the
+ * candidates [cand_offsets[k], cand_offsets[k+1]) of the concatenated int32 (n, 5) table.  Always the
+ * no-wait form: counts and domain errors are delivered by the next ssp_polygon_count / _fetch /
+ * _match_pairs call.  A step of the star path measures every image of the panorama this way
+ * (the reference: once per image, cached in polygon_data_store, cbpm:744-748). */
+int ssp_polygon_measure_batch(ssp_ctx* ctx, const int32_t* images, int n_images, const int32_t* candidates,
+                              const int64_t* cand_offsets, double min_side_px, int mem_kind);
 /* Reads back the stored polygons of `image`, any pointer may be NULL.  All arrays are
  * (P, 5) row-major in the canonical vertex order (hull order, orientation of cbpm:537-543,
  * rotated so the smallest vertex angle is element 0, cbpm:578-591):

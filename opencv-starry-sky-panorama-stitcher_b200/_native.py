@@ -56,6 +56,7 @@ PROTOTYPES = {
     "ssp_fetch_star_rays": (_c.c_int, [_ctx_p, _f64p, _c.c_int64, _c.c_int]),
     "ssp_polygon_measure": (_c.c_int, [_ctx_p, _c.c_int, _i32p, _c.c_int64, _c.c_double, _c.c_int,
                                        _u8p, _c.POINTER(_c.c_int64)]),
+    "ssp_polygon_measure_batch": (_c.c_int, [_ctx_p, _i32p, _c.c_int, _i32p, _i64p, _c.c_double, _c.c_int]),
     "ssp_polygon_fetch": (_c.c_int, [_ctx_p, _c.c_int, _i32p, _f64p, _f64p, _f64p, _f64p,
                                      _c.c_int64, _c.c_int]),
     "ssp_polygon_count": (_c.c_int, [_ctx_p, _c.c_int, _c.POINTER(_c.c_int64)]),

@@ -47,14 +47,12 @@ __device__ __forceinline__ double orient2d(double ax, double ay, double bx, doub
 // One thread per candidate polygon: the body of get_polygons_characteristics (cbpm:500-600)
 // plus the normalisation of cbpm:722-740.  Results go to per-candidate slots; a stable
 // compaction keeps the valid ones afterwards.
-__global__ void __launch_bounds__(128)
-poly_measure_kernel(StarView sv, const int* __restrict__ cand, long long n_cand, double min_side,
-                    unsigned char* __restrict__ status, int* __restrict__ flags,
-                    int* __restrict__ n_domain, int* __restrict__ o_idx,
-                    double* __restrict__ o_angle, double* __restrict__ o_side,
-                    double* __restrict__ o_bright, double* __restrict__ o_feat) {
-  const long long pidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (pidx >= n_cand) return;
+__device__ __forceinline__ void
+poly_measure_one(const StarView& sv, const int* __restrict__ cand, long long pidx, double min_side,
+                 unsigned char* __restrict__ status, int* __restrict__ flags,
+                 int* __restrict__ n_domain, int* __restrict__ o_idx,
+                 double* __restrict__ o_angle, double* __restrict__ o_side,
+                 double* __restrict__ o_bright, double* __restrict__ o_feat) {
   int id[5];
   double x[5], y[5];
   bool bad = false;
@@ -205,6 +203,52 @@ poly_measure_kernel(StarView sv, const int* __restrict__ cand, long long n_cand,
   flags[pidx] = 1;
 }
 
+__global__ void __launch_bounds__(128)
+poly_measure_kernel(StarView sv, const int* __restrict__ cand, long long n_cand, double min_side,
+                    unsigned char* __restrict__ status, int* __restrict__ flags,
+                    int* __restrict__ n_domain, int* __restrict__ o_idx,
+                    double* __restrict__ o_angle, double* __restrict__ o_side,
+                    double* __restrict__ o_bright, double* __restrict__ o_feat) {
+  const long long pidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pidx >= n_cand) return;
+  poly_measure_one(sv, cand, pidx, min_side, status, flags, n_domain, o_idx, o_angle, o_side, o_bright, o_feat);
+}
+
+// Several images in ONE launch (ssp_polygon_measure_batch): the candidate tables sit back to back,
+// every image owns whole 128-thread blocks.  A C4 step measured 21 images with 21 launches of ~118
+// blocks each, ~25 us apiece and latency-bound on 148 SMs; together they are one grid of ~2 500 blocks.
+struct MeasureImage {
+  StarView sv;
+  long long cand_off;    // first candidate of the image in the concatenated table (= scratch index)
+  int n;                 // candidates of the image
+  int block_off;         // first block of the image
+  int* o_idx;            // the image's polygon bank
+  double *o_angle, *o_side, *o_bright, *o_feat;
+  long long* slot;       // {count, n_domain} of the image (device memory, copied to the pinned slot afterwards)
+};
+
+__device__ __forceinline__ int measure_image_of_block(const MeasureImage* __restrict__ imgs, int n_images, int block) {
+  int lo = 0, hi = n_images - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (imgs[mid].block_off <= block) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(128)
+poly_measure_batch_kernel(const MeasureImage* __restrict__ imgs, int n_images, const int* __restrict__ cand,
+                          double min_side, unsigned char* __restrict__ status, int* __restrict__ flags,
+                          int* __restrict__ o_idx, double* __restrict__ o_angle, double* __restrict__ o_side,
+                          double* __restrict__ o_bright, double* __restrict__ o_feat) {
+  const MeasureImage im = imgs[measure_image_of_block(imgs, n_images, (int)blockIdx.x)];
+  const int local = ((int)blockIdx.x - im.block_off) * 128 + (int)threadIdx.x;
+  if (local >= im.n) return;
+  // the domain-error counter of the image is the second word of its slot
+  poly_measure_one(im.sv, cand, im.cand_off + local, min_side, status, flags,
+                   reinterpret_cast<int*>(im.slot + 1), o_idx, o_angle, o_side, o_bright, o_feat);
+}
+
 // Stable compaction of the valid candidates.  Every block derives its own output base from the
 // flags in front of it (at most 15 000 ints, L2-resident) -- round 1 ran a separate single-CTA scan
 // kernel between measure and scatter, 12 us per image, as much as half a measure launch.  The last
@@ -254,6 +298,52 @@ poly_scatter_kernel(const int* __restrict__ flags, long long* __restrict__ total
   }
 #pragma unroll
   for (int k = 0; k < 15; ++k) o_feat[d * 15 + k] = t_feat[i * 15 + k];
+}
+
+__global__ void __launch_bounds__(128)
+poly_scatter_batch_kernel(const MeasureImage* __restrict__ imgs, int n_images, const int* __restrict__ flags,
+                          const int* __restrict__ t_idx, const double* __restrict__ t_angle,
+                          const double* __restrict__ t_side, const double* __restrict__ t_bright,
+                          const double* __restrict__ t_feat) {
+  __shared__ int wsum[4];
+  __shared__ int wcnt[4];
+  const MeasureImage im = imgs[measure_image_of_block(imgs, n_images, (int)blockIdx.x)];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int first = ((int)blockIdx.x - im.block_off) * 128;     // inside the image
+  const int* f = flags + im.cand_off;
+  int before = 0;
+  for (int k = threadIdx.x; k < first; k += 128) before += f[k];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(0xffffffffu, before, o);
+  const int local = first + (int)threadIdx.x;
+  const bool keep = local < im.n && f[local] != 0;
+  const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+  if (lane == 0) {
+    wsum[wid] = before;
+    wcnt[wid] = __popc(ballot);
+  }
+  __syncthreads();
+  long long d = (long long)wsum[0] + wsum[1] + wsum[2] + wsum[3];
+  int block_total = 0;
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    d += (w < wid) ? wcnt[w] : 0;
+    block_total += wcnt[w];
+  }
+  const bool last_block = first + 128 >= im.n;
+  if (last_block && threadIdx.x == 0) im.slot[0] = (long long)wsum[0] + wsum[1] + wsum[2] + wsum[3] + block_total;
+  if (!keep) return;
+  d += __popc(ballot & ((1u << lane) - 1u));
+  const long long i = im.cand_off + local;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    im.o_idx[d * 5 + k] = t_idx[i * 5 + k];
+    im.o_angle[d * 5 + k] = t_angle[i * 5 + k];
+    im.o_side[d * 5 + k] = t_side[i * 5 + k];
+    im.o_bright[d * 5 + k] = t_bright[i * 5 + k];
+  }
+#pragma unroll
+  for (int k = 0; k < 15; ++k) im.o_feat[d * 15 + k] = t_feat[i * 15 + k];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -872,6 +962,109 @@ int ssp_polygon_measure(ssp_ctx* ctx, int image, const int32_t* candidates, int6
                 "ssp_polygon_measure: %d candidate(s) of image %d gave |acos argument| > 1 "
                 "(the reference raises ValueError at custom_bf_polygon_matcher.py:134)",
                 n_domain, image);
+  return SSP_OK;
+}
+
+int ssp_polygon_measure_batch(ssp_ctx* ctx, const int32_t* images, int n_images, const int32_t* candidates,
+                              const int64_t* cand_offsets, double min_side_px, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, !ctx->star_off.empty(), SSP_ERR_STATE, "ssp_polygon_measure_batch: no star bank");
+  SSP_REQUIRE(ctx, n_images >= 0 && (n_images == 0 || (images != nullptr && cand_offsets != nullptr)) &&
+                       (n_images == 0 || cand_offsets[0] == 0),
+              SSP_ERR_INVALID, "ssp_polygon_measure_batch: bad arguments");
+  if (n_images == 0) return SSP_OK;
+  constexpr int SLOT_IMAGES = 4096;
+  const long long n = cand_offsets[n_images];
+  SSP_REQUIRE(ctx, n >= 0 && n < (1LL << 31) - 1024 && (n == 0 || candidates != nullptr), SSP_ERR_INVALID,
+              "ssp_polygon_measure_batch: bad candidate table");
+  std::vector<MeasureImage> tab;
+  int blocks = 0;
+  for (int k = 0; k < n_images; ++k) {
+    const int image = images[k];
+    if (int rc = ensure_poly_image(ctx, image, "ssp_polygon_measure_batch", true)) return rc;
+    SSP_REQUIRE(ctx, image < SLOT_IMAGES, SSP_ERR_INVALID, "ssp_polygon_measure_batch: image id %d >= %d", image, SLOT_IMAGES);
+    for (int j = 0; j < k; ++j)
+      SSP_REQUIRE(ctx, images[j] != image, SSP_ERR_INVALID, "ssp_polygon_measure_batch: image %d listed twice", image);
+    const long long ni = cand_offsets[k + 1] - cand_offsets[k];
+    SSP_REQUIRE(ctx, ni >= 0, SSP_ERR_INVALID, "ssp_polygon_measure_batch: offsets must be non-decreasing");
+  }
+  if (!ctx->p_slots) {
+    SSP_CUDA_TRY(ctx, cudaHostAlloc(reinterpret_cast<void**>(&ctx->p_slots), (size_t)SLOT_IMAGES * 16,
+                                    cudaHostAllocPortable));
+    ctx->p_slot_capacity = SLOT_IMAGES;
+  }
+  ctx->p_n_matches = -1;
+  NvtxRange range("kernel 2 (polygon measure, batch)");
+  // scratch: as ssp_polygon_measure, sized for all images together
+  const long long ns = n > 0 ? n : 1;
+  SSP_CUDA_TRY(ctx, ctx->p_cand.ensure((size_t)ns * 20));
+  SSP_CUDA_TRY(ctx, ctx->p_status.ensure((size_t)ns + 16));
+  const size_t head = ((size_t)n_images * (16 + sizeof(MeasureImage)) + 63) / 64 * 64;
+  SSP_CUDA_TRY(ctx, ctx->p_scan.ensure(head + (size_t)ns * 4 + 64));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_idx.ensure((size_t)ns * 20));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_angle.ensure((size_t)ns * 40));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_side.ensure((size_t)ns * 40));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_bright.ensure((size_t)ns * 40));
+  SSP_CUDA_TRY(ctx, ctx->p_tmp_feat.ensure((size_t)ns * 120));
+  // p_scan layout here: [slots n_images x 2 int64][table n_images x MeasureImage][flags n int]
+  long long* d_slots = ctx->p_scan.as<long long>();
+  MeasureImage* d_tab = reinterpret_cast<MeasureImage*>(ctx->p_scan.as<char>() + (size_t)n_images * 16);
+  int* d_flags = reinterpret_cast<int*>(ctx->p_scan.as<char>() + head);
+  for (int k = 0; k < n_images; ++k) {
+    const int image = images[k];
+    PolyImage& pi = ctx->poly[(size_t)image];
+    const long long ni = cand_offsets[k + 1] - cand_offsets[k];
+    const long long cap = ni > 0 ? ni : 1;
+    SSP_CUDA_TRY(ctx, pi.star_idx.ensure((size_t)cap * 20));
+    SSP_CUDA_TRY(ctx, pi.angle.ensure((size_t)cap * 40));
+    SSP_CUDA_TRY(ctx, pi.side.ensure((size_t)cap * 40));
+    SSP_CUDA_TRY(ctx, pi.bright.ensure((size_t)cap * 40));
+    SSP_CUDA_TRY(ctx, pi.feat.ensure((size_t)cap * 120));
+    const long long s0 = ctx->star_off[(size_t)image];
+    MeasureImage m;
+    m.sv.xy = ctx->s_xy.as<double>() + 2 * s0;
+    m.sv.bright = ctx->s_bright.as<double>() + s0;
+    m.sv.rays = ctx->s_rays.as<double>() + 3 * s0;
+    m.sv.n = (int)(ctx->star_off[(size_t)image + 1] - s0);
+    m.cand_off = cand_offsets[k];
+    m.n = (int)ni;
+    m.block_off = blocks;
+    m.o_idx = pi.star_idx.as<int>();
+    m.o_angle = pi.angle.as<double>();
+    m.o_side = pi.side.as<double>();
+    m.o_bright = pi.bright.as<double>();
+    m.o_feat = pi.feat.as<double>();
+    m.slot = d_slots + 2 * k;
+    blocks += (int)((ni + 127) / 128);
+    tab.push_back(m);
+  }
+  SSP_CUDA_TRY(ctx, cudaMemsetAsync(d_slots, 0, (size_t)n_images * 16, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(d_tab, tab.data(), tab.size() * sizeof(MeasureImage), cudaMemcpyHostToDevice,
+                                    ctx->stream));   // pageable source: staged before the call returns
+  if (n > 0) {
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_cand.p, candidates, (size_t)n * 20, to_device_kind(mem_kind), ctx->stream));
+    poly_measure_batch_kernel<<<(unsigned)blocks, 128, 0, ctx->stream>>>(
+        d_tab, n_images, ctx->p_cand.as<int>(), min_side_px, ctx->p_status.as<unsigned char>(), d_flags,
+        ctx->p_tmp_idx.as<int>(), ctx->p_tmp_angle.as<double>(), ctx->p_tmp_side.as<double>(),
+        ctx->p_tmp_bright.as<double>(), ctx->p_tmp_feat.as<double>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+    poly_scatter_batch_kernel<<<(unsigned)blocks, 128, 0, ctx->stream>>>(
+        d_tab, n_images, d_flags, ctx->p_tmp_idx.as<int>(), ctx->p_tmp_angle.as<double>(),
+        ctx->p_tmp_side.as<double>(), ctx->p_tmp_bright.as<double>(), ctx->p_tmp_feat.as<double>());
+    SSP_CUDA_TRY(ctx, cudaGetLastError());
+  }
+  // counts and domain flags travel to the pinned slots; the next consumer reads them (no wait here)
+  for (int k = 0; k < n_images; ++k) {
+    const int image = images[k];
+    PolyImage& pi = ctx->poly[(size_t)image];
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&ctx->p_slots[2 * image], d_slots + 2 * k, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    pi.count = 0;
+    pi.pending = true;
+    pi.has_raw = true;
+  }
+  ctx->p_any_pending = true;
   return SSP_OK;
 }
 

@@ -312,24 +312,26 @@ def broadcast_star_bank(xy: Optional[Sequence[np.ndarray]], brightness: Optional
 def measure_polygons_sharded(engine, star_off, cand_off, xy_t, br_t, cand_t, img_w, img_h, focal,
                              min_side_px: float = 5.0):
     """Kernel 2 split by image (the reference's per-image cache, custom_bruteforce_matcher.py:57-59 /
-    cbpm:744-748: measure once per image, compare per pair): rank r measures images r, r + world, ...,
-    then the polygon banks are all-gathered so that every rank can compare any pair.  Returns the
-    polygon count of every image."""
+    cbpm:744-748: measure once per image, compare per pair): every rank measures ONE contiguous block
+    of images (balanced by candidate count) in one launch pair, then the polygon banks are all-gathered
+    so that every rank can compare any pair.  Returns the polygon count of every image."""
     dev = _device_for_backend()
     rank, world = dist.get_rank(), dist.get_world_size()
     n_img = len(star_off) - 1
     engine.upload_star_bank_resident(xy_t.data_ptr(), br_t.data_ptr(), star_off, img_w, img_h, focal)
-    mine = list(range(rank, n_img, world))
-    for i in mine:
-        engine.polygon_measure_resident(i, cand_t[int(cand_off[i]):].data_ptr(), int(cand_off[i + 1] - cand_off[i]),
-                                        min_side_px=min_side_px, wait=False)
+    bounds = shard_bounds(n_img, world, cost=np.diff(cand_off).astype(np.float64) + 1.0)
+    lo, hi = bounds[rank], bounds[rank + 1]
+    mine = list(range(lo, hi))
+    if mine:
+        engine.polygon_measure_batch_resident(mine, cand_t[int(cand_off[lo]):].data_ptr(),
+                                              np.asarray(cand_off[lo:hi + 1]) - int(cand_off[lo]), min_side_px)
     counts = torch.zeros(n_img, dtype=torch.int64, device=dev)
     if mine:
-        counts[rank::world] = torch.tensor([engine.polygon_count(i) for i in mine], dtype=torch.int64).to(dev)
+        counts[lo:hi] = torch.tensor([engine.polygon_count(i) for i in mine], dtype=torch.int64).to(dev)
     dist.all_reduce(counts, op=dist.ReduceOp.SUM)
     counts = counts.cpu().numpy()
     # every rank's banks back to back, padded to the longest rank, one all-gather per array
-    rows_of = [int(counts[r::world].sum()) for r in range(world)]
+    rows_of = [int(counts[bounds[r]:bounds[r + 1]].sum()) for r in range(world)]
     width = max(max(rows_of), 1)
     feat = _devbuf("pg_feat", width * 15, torch.float64, dev).view(width, 15)
     idx = _devbuf("pg_idx", width * 5, torch.int32, dev).view(width, 5)
@@ -347,7 +349,7 @@ def measure_polygons_sharded(engine, star_off, cand_off, xy_t, br_t, cand_t, img
         if r == rank:
             continue
         cursor = 0
-        for i in range(r, n_img, world):
+        for i in range(bounds[r], bounds[r + 1]):
             n = int(counts[i])
             engine.polygon_upload_features_resident(i, all_feat[r, cursor:].data_ptr(), all_idx[r, cursor:].data_ptr(), n)
             cursor += n

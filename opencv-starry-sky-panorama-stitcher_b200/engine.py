@@ -324,6 +324,18 @@ class Engine:
                                                   None, ctypes.byref(n_valid) if wait else None))
         return n_valid.value if wait else None
 
+    def polygon_measure_batch_resident(self, images: Sequence[int], device_ptr: int, cand_offsets,
+                                       min_side_px: float = 5.0):
+        """Measures several images in one launch pair: images[k] owns rows [cand_offsets[k],
+        cand_offsets[k+1]) of the int32 (n, 5) candidate table at `device_ptr`.  Does not wait; counts
+        come from `polygon_count`."""
+        ids = np.ascontiguousarray(images, dtype=np.int32)
+        offs = np.ascontiguousarray(cand_offsets, dtype=np.int64)
+        for i in ids.tolist():
+            self.poly_owner[int(i)] = None
+        self._check(self._lib.ssp_polygon_measure_batch(self._ctx, _ptr(ids), len(ids), ctypes.c_void_p(device_ptr),
+                                                        _ptr(offs), float(min_side_px), N.MEM_DEVICE))
+
     def polygon_count(self, image: int) -> int:
         n = ctypes.c_int64()
         self._check(self._lib.ssp_polygon_count(self._ctx, int(image), ctypes.byref(n)))

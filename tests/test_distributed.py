@@ -201,6 +201,11 @@ class _PolygonOracleEngine:
         self.bank[image] = (np.ascontiguousarray(got["feat"], dtype=np.float64).reshape(-1, 15),
                             np.ascontiguousarray(got["star_idx"], dtype=np.int32).reshape(-1, 5))
 
+    def polygon_measure_batch_resident(self, images, device_ptr, cand_offsets, min_side_px=5.0):
+        for k, image in enumerate(images):
+            lo, n = int(cand_offsets[k]), int(cand_offsets[k + 1] - cand_offsets[k])
+            self.polygon_measure_resident(image, device_ptr + lo * 20 if n else 0, n, min_side_px)
+
     def polygon_count(self, image):
         return len(self.bank[image][0])
 

@@ -371,3 +371,36 @@ def test_queue_compare_kernel_equals_per_lane_pruning_and_numpy(engine, monkeypa
     np.testing.assert_array_equal(out["queue"].argmin, np.argmin(m, axis=1))
     np.testing.assert_array_equal(out["queue"].mindist, m.min(axis=1))
     assert engine.polygon_last_stats()["executed_flops"] > 0
+
+
+def test_batch_measure_of_all_images_equals_the_per_image_form(engine):
+    """ssp_polygon_measure_batch: several images, ONE measure + ONE compaction launch; banks, counts and
+    the matches that follow equal those of the per-image calls -- also with an image without
+    candidates and with invalid candidates in the mix."""
+    import torch
+    xy_l, b_l, _ = synth.star_fields(4, 300, seed=12)
+    engine.upload_star_bank(xy_l, b_l, 1342, 894, 1135.0)
+    cands = [synth.random_candidates(len(xy_l[i]), 900 + 333 * i, seed=50 + i) for i in range(4)]
+    cands[2] = cands[2][:0]
+    want = []
+    for i in range(4):
+        n = engine.polygon_measure(i, cands[i])
+        want.append((n, engine.polygon_fetch(i)))
+    ref = engine.polygon_match_pairs([(0, 1), (1, 3), (0, 3), (2, 3)], threshold=10.0, return_rowmin=True)
+    offs = np.zeros(5, dtype=np.int64)
+    np.cumsum([len(c) for c in cands], out=offs[1:])
+    table = torch.from_numpy(np.concatenate(cands).astype(np.int32)).cuda()
+    order = [3, 0, 2, 1]                         # any order of images, offsets follow the order
+    perm_offs = np.zeros(5, dtype=np.int64)
+    np.cumsum([len(cands[i]) for i in order], out=perm_offs[1:])
+    perm_table = torch.from_numpy(np.concatenate([cands[i] for i in order]).astype(np.int32)).cuda()
+    for ids, tab, o in (([0, 1, 2, 3], table, offs), (order, perm_table, perm_offs)):
+        engine.polygon_measure_batch_resident(ids, tab.data_ptr(), o)
+        for i in range(4):
+            assert engine.polygon_count(i) == want[i][0]
+            got = engine.polygon_fetch(i)
+            for k in ("star_idx", "angle", "side", "brightness", "feat"):
+                np.testing.assert_array_equal(got[k], want[i][1][k], err_msg=f"image {i} {k}")
+        res = engine.polygon_match_pairs([(0, 1), (1, 3), (0, 3), (2, 3)], threshold=10.0, return_rowmin=True)
+        np.testing.assert_array_equal(res.argmin, ref.argmin)
+        np.testing.assert_array_equal(res.mindist, ref.mindist)
