@@ -488,79 +488,89 @@ poly_compare_f64_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ ar
 #define PQ_TILE_COLS 64
 #endif
 #ifndef PQ_UNROLL
-#define PQ_UNROLL 2      // columns whose first-group sums are in flight together (independent FP64 chains)
-#endif
-#ifndef PQ_ROWS
-#define PQ_ROWS 2        // rows per thread: column loads, ballots and loop overhead are shared between them
+#define PQ_UNROLL 4      // columns whose first-group sums are in flight together (independent FP64 chains)
 #endif
 constexpr int PQ_TILE = PQ_TILE_COLS;        // columns per shared-memory tile (shared memory bounds the occupancy)
-constexpr int PQ_CTA_ROWS = PC_THREADS * PQ_ROWS;
-constexpr int PQ_QUEUE = 32 * (PQ_UNROLL * PQ_ROWS + 1);   // entries per warp: 31 left over + one step of the unrolled loop
+constexpr int PQ_QUEUE = 32 * (PQ_UNROLL + 1);   // queue entries per warp: 31 left over + one column step of PQ_UNROLL x 32
 constexpr int PQ_G2 = 3 - POLY_G0 - POLY_G1; // the third property group
+#ifndef PQ_FMA_BOUND
+#define PQ_FMA_BOUND 1   // first-group FILTER with fused multiply-adds (10 instead of 14 FP64 instructions per column)
+#endif
+// The filter only has to be SAFE, not bit-equal: with the same rounded differences d_k, the fused sum
+// Gf = fl(d4^2 + fl(d3^2 + ...)) and numpy's G = fl(fl(d4^2) + fl(fl(d3^2) + ...)) both lie within
+// (1 +- u)^5 of the real sum, so G >= Gf * (1 - 10 u).  A column is dropped only if Gf >= thr * (1 + 2^-40),
+// which implies G >= thr -- exactly the columns the reference's evaluation order would drop, minus a
+// sliver that is kept.  Every survivor is re-evaluated from scratch in numpy's order inside its batch.
+constexpr double PQ_LOOSE = 1.0 + 9.094947017729282e-13;   // 1 + 2^-40
 
-struct __align__(16) PqEntry {   // one survivor of the first property group
-  double g0;                     // its first-group sum
-  int rc;                        // row slot of the warp (which << 5 | lane) << 16 | column in the tile
-  int pad;
-};
-
-// ncu of the first version of this kernel (one row per thread) showed it ISSUE-bound, not FP64-bound:
-// 47 instructions per column and warp of which 14 are FP64.  Two rows per thread share the column's
-// shared-memory loads, the loop and the vote bookkeeping, and only the FIRST property group of a row
-// lives in registers (10 registers per row); the other two groups are read from shared memory by
-// whichever lane evaluates a queued entry.
 __global__ void __launch_bounds__(PC_THREADS)
 poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ argmin,
                               double* __restrict__ mindist, unsigned long long* __restrict__ executed_flops) {
   __shared__ __align__(16) double tile[(PQ_TILE + PQ_UNROLL) * 15];
-  __shared__ __align__(16) double rows_s[PQ_CTA_ROWS * 10];   // groups POLY_G1 and PQ_G2 of every row of the CTA
-  __shared__ double thr_s[PQ_CTA_ROWS];
-  __shared__ PqEntry queue_s[PC_THREADS / 32][PQ_QUEUE];
+#if PQ_FMA_BOUND
+  constexpr int RS = 15;   // the batch re-evaluates all three groups of a row
+#else
+  constexpr int RS = 10;   // groups POLY_G1 and PQ_G2; the first-group sum travels in the queue
+  __shared__ double q_g0[PC_THREADS / 32][PQ_QUEUE];
+#endif
+  __shared__ __align__(16) double rows_s[PC_THREADS * RS];
+  __shared__ double thr_s[PC_THREADS];
+  __shared__ int q_rc[PC_THREADS / 32][PQ_QUEUE];             // row lane << 16 | column in tile
   const PolyPair pp = pairs[blockIdx.x];
-  const int row0 = blockIdx.y * PQ_CTA_ROWS;
+  const int row0 = blockIdx.y * PC_THREADS;
   if (row0 >= pp.p1) return;
+  const int r = row0 + threadIdx.x;
+  const bool live = r < pp.p1;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  // row slot s of warp w (s = which * 32 + lane) is row  row0 + w * 32 * PQ_ROWS + s
-  const int warp_row0 = row0 + wid * 32 * PQ_ROWS;
-  double a0[PQ_ROWS][5];
-  double thr[PQ_ROWS], best[PQ_ROWS];
-  int best_c[PQ_ROWS];
-  bool live[PQ_ROWS];
-  double* my_rows = rows_s + wid * 32 * PQ_ROWS * 10;
-  double* my_thr = thr_s + wid * 32 * PQ_ROWS;
-  PqEntry* my_q = queue_s[wid];
+  double a[15];
 #pragma unroll
-  for (int w = 0; w < PQ_ROWS; ++w) {
-    const int slot = w * 32 + lane;
-    const int r = warp_row0 + slot;
-    live[w] = r < pp.p1;
+  for (int k = 0; k < 15; ++k) a[k] = live ? pp.f1[(long long)r * 15 + k] : 0.0;
 #pragma unroll
-    for (int k = 0; k < 5; ++k) {
-      a0[w][k] = live[w] ? pp.f1[(long long)r * 15 + POLY_G0 * 5 + k] : 0.0;
-      my_rows[slot * 10 + k] = live[w] ? pp.f1[(long long)r * 15 + POLY_G1 * 5 + k] : 0.0;
-      my_rows[slot * 10 + 5 + k] = live[w] ? pp.f1[(long long)r * 15 + PQ_G2 * 5 + k] : 0.0;
-    }
-    thr[w] = live[w] ? INFINITY : -1.0;     // a dead row never passes the first test
-    best[w] = INFINITY;
-    best_c[w] = 0;
-    my_thr[slot] = thr[w];
+  for (int k = 0; k < 5; ++k) {
+    rows_s[threadIdx.x * RS + k] = a[POLY_G1 * 5 + k];
+    rows_s[threadIdx.x * RS + 5 + k] = a[PQ_G2 * 5 + k];
+#if PQ_FMA_BOUND
+    rows_s[threadIdx.x * RS + 10 + k] = a[POLY_G0 * 5 + k];
+#endif
   }
+  // a dead lane (row beyond p1) never passes the first test
+  double thr = live ? INFINITY : -1.0, best = INFINITY;
+  double thr_filter = thr;                       // what the first-group filter compares with (thr, loosened)
+  int best_c = 0;
+  thr_s[threadIdx.x] = thr;
   unsigned flops = 0;
   int q_n = 0;                                   // entries waiting in this warp's queue (warp-uniform)
+#if !PQ_FMA_BOUND
+  double* my_g0 = q_g0[wid];
+#endif
+  int* my_rc = q_rc[wid];
+  const double* my_rows = rows_s + wid * 32 * RS;
+  double* my_thr = thr_s + wid * 32;
 
   // evaluates up to 32 queued entries [first, first + n) as one dense batch
   auto run_batch = [&](int first, int n, int c0) {
     double v = 0.0;
-    int slot = 0, col = 0;
+    int rl = 0, col = 0;
     bool cand = false;
     if (lane < n) {
-      const PqEntry e = my_q[first + lane];
-      slot = e.rc >> 16;
-      col = e.rc & 0xFFFF;
-      const double g0 = e.g0;
+      const int rc = my_rc[first + lane];
+      rl = rc >> 16;
+      col = rc & 0xFFFF;
       const double* b = tile + col * 15;
-      const double* ar = my_rows + slot * 10;
-      const double t = my_thr[slot];
+      const double* ar = my_rows + rl * RS;
+      const double t = my_thr[rl];
+#if PQ_FMA_BOUND
+      double g0 = 0.0;     // the filter's fused sum was only a bound: the real first group, numpy's order
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const double d = __dsub_rn(ar[10 + k], b[POLY_G0 * 5 + k]);
+        const double sq = __dmul_rn(d, d);
+        g0 = (k == 0) ? sq : __dadd_rn(g0, sq);
+      }
+      flops += 14;
+#else
+      const double g0 = my_g0[first + lane];
+#endif
       double g1 = 0.0;
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
@@ -569,7 +579,7 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
         g1 = (k == 0) ? sq : __dadd_rn(g1, sq);
       }
       flops += 15;
-      if (__dadd_rn(g0, g1) < t) {
+      if (g0 < t && __dadd_rn(g0, g1) < t) {
         double g2 = 0.0;
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
@@ -591,21 +601,18 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
     while (todo) {
       const int src = __ffs((int)todo) - 1;
       todo &= todo - 1;
-      const int o_slot = __shfl_sync(0xffffffffu, slot, src);
+      const int o_rl = __shfl_sync(0xffffffffu, rl, src);
       const int o_col = __shfl_sync(0xffffffffu, col, src);
       const double o_v = __shfl_sync(0xffffffffu, v, src);
-      if (lane == (o_slot & 31)) {
-#pragma unroll
-        for (int w = 0; w < PQ_ROWS; ++w)
-          if ((o_slot >> 5) == w && o_v < thr[w]) {
-            const double sv = sqrt(o_v);
-            if (sv < best[w]) {
-              best[w] = sv;
-              best_c[w] = c0 + o_col;
-            }
-            thr[w] = o_v;
-            my_thr[o_slot] = o_v;
-          }
+      if (lane == o_rl && o_v < thr) {
+        const double sv = sqrt(o_v);
+        if (sv < best) {
+          best = sv;
+          best_c = c0 + o_col;
+        }
+        thr = o_v;
+        thr_filter = PQ_FMA_BOUND ? o_v * PQ_LOOSE : o_v;
+        my_thr[lane] = o_v;
       }
       __syncwarp();
     }
@@ -618,45 +625,37 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
       tile[i] = pp.f2[(long long)c0 * 15 + i];
     __syncthreads();
     for (int j0 = 0; j0 < ncol; j0 += PQ_UNROLL) {
-      double g0[PQ_UNROLL][PQ_ROWS];
+      double g0[PQ_UNROLL];
 #pragma unroll
       for (int u = 0; u < PQ_UNROLL; ++u) {
         // columns past the end of a ragged tile read stale shared memory; they never pass (j < ncol below)
-        const double* b = tile + (j0 + u) * 15 + POLY_G0 * 5;
-        double bv[5];
+        const double* b = tile + (j0 + u) * 15;
+        double acc = 0.0;
 #pragma unroll
-        for (int k = 0; k < 5; ++k) bv[k] = b[k];
-#pragma unroll
-        for (int w = 0; w < PQ_ROWS; ++w) {
-          double acc = 0.0;
-#pragma unroll
-          for (int k = 0; k < 5; ++k) {
-            const double d = __dsub_rn(a0[w][k], bv[k]);
-            const double sq = __dmul_rn(d, d);
-            acc = (k == 0) ? sq : __dadd_rn(acc, sq);
-          }
-          g0[u][w] = acc;
+        for (int k = 0; k < 5; ++k) {
+          const double d = __dsub_rn(a[POLY_G0 * 5 + k], b[POLY_G0 * 5 + k]);
+#if PQ_FMA_BOUND
+          acc = (k == 0) ? __dmul_rn(d, d) : __fma_rn(d, d, acc);
+#else
+          const double sq = __dmul_rn(d, d);
+          acc = (k == 0) ? sq : __dadd_rn(acc, sq);
+#endif
         }
+        g0[u] = acc;
       }
 #pragma unroll
       for (int u = 0; u < PQ_UNROLL; ++u) {
         const int j = j0 + u;
-#pragma unroll
-        for (int w = 0; w < PQ_ROWS; ++w) {
-          // row order inside a column does not matter: entries of ONE row stay in ascending column order
-          const bool pass = j < ncol && g0[u][w] < thr[w];
-          const unsigned m = __ballot_sync(0xffffffffu, pass);
-          if (m) {   // warp-uniform
-            if (pass) {
-              PqEntry e;
-              e.g0 = g0[u][w];
-              e.rc = ((w * 32 + lane) << 16) | j;
-              e.pad = 0;
-              my_q[q_n + __popc(m & ((1u << lane) - 1u))] = e;
-            }
-            q_n += __popc(m);
-          }
+        const bool pass = j < ncol && g0[u] < thr_filter;
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (pass) {
+          const int pos = q_n + __popc(m & ((1u << lane) - 1u));
+#if !PQ_FMA_BOUND
+          my_g0[pos] = g0[u];
+#endif
+          my_rc[pos] = (lane << 16) | j;
         }
+        q_n += __popc(m);
       }
       if (q_n >= 32) {   // one call site: dense batches from the front, the (< 32) rest moves up
         __syncwarp();
@@ -666,32 +665,35 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
           first += 32;
         }
         const int rest = q_n - first;
-        PqEntry mv;
-        mv.g0 = 0.0; mv.rc = 0; mv.pad = 0;
-        if (lane < rest) mv = my_q[first + lane];
+        int mr = 0;
+#if !PQ_FMA_BOUND
+        double mg = 0.0;
+        if (lane < rest) mg = my_g0[first + lane];
+#endif
+        if (lane < rest) mr = my_rc[first + lane];
         __syncwarp();
-        if (lane < rest) my_q[lane] = mv;
+        if (lane < rest) {
+#if !PQ_FMA_BOUND
+          my_g0[lane] = mg;
+#endif
+          my_rc[lane] = mr;
+        }
         q_n = rest;
         __syncwarp();
       }
     }
-#pragma unroll
-    for (int w = 0; w < PQ_ROWS; ++w) flops += live[w] ? 14u * (unsigned)ncol : 0u;
+    flops += live ? 14u * (unsigned)ncol : 0u;
     // the tile is about to be overwritten: drain what is left
     if (q_n > 0) {
-      __syncwarp();
       run_batch(0, q_n, c0);
       q_n = 0;
       __syncwarp();
     }
   }
-#pragma unroll
-  for (int w = 0; w < PQ_ROWS; ++w)
-    if (live[w]) {
-      const int r = warp_row0 + w * 32 + lane;
-      argmin[pp.out_row + r] = best_c[w];
-      mindist[pp.out_row + r] = best[w];
-    }
+  if (live) {
+    argmin[pp.out_row + r] = best_c;
+    mindist[pp.out_row + r] = best;
+  }
   // flops executed by this warp (lane-level: pruned terms are not counted)
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) flops += __shfl_xor_sync(0xffffffffu, flops, o);
@@ -1255,8 +1257,7 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
       if (ms) poly_compare_f64_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
       else if (legacy) poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
       else {
-        dim3 qgrid((unsigned)n_pairs, (unsigned)((max_p1 + PQ_CTA_ROWS - 1) / PQ_CTA_ROWS));
-        poly_compare_f64_queue_kernel<<<qgrid, PC_THREADS, 0, ctx->stream>>>(
+        poly_compare_f64_queue_kernel<<<grid, PC_THREADS, 0, ctx->stream>>>(
             dp, am, md, ctx->p_flops.as<unsigned long long>());
         counted = true;
       }
