@@ -154,7 +154,10 @@ class Runtime:
             import torch.distributed as dist
             dist.init_process_group("nccl", device_id=self.dev)
             self.dist = dist
-        self.stream = torch.cuda.current_stream(self.dev)
+        # ONE stream for everything: torch ops, NCCL's stream waits and the engine's kernels (a dedicated
+        # stream has a non-zero handle; torch's default stream reads as 0 = "engine's own stream" in the C ABI)
+        self.stream = torch.cuda.Stream(self.dev)
+        torch.cuda.set_stream(self.stream)
         self.flush = torch.empty(FLUSH_BYTES, dtype=torch.uint8, device=self.dev)
 
     def engine(self):

@@ -149,9 +149,20 @@ class Engine:
         raw = (ctypes.c_char * need).from_address(addr)
         return np.frombuffer(raw, dtype=dt, count=int(n))
 
+    CUDA_STREAM_LEGACY = 0x1   # cudaStreamLegacy: the handle that NAMES the default stream
+
     def set_stream(self, cuda_stream_handle: Optional[int]):
-        """Run subsequent work on this cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
-        self._check(self._lib.ssp_set_stream(self._ctx, ctypes.c_void_p(cuda_stream_handle or 0)))
+        """Run subsequent work on this cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream).
+        None = the context's own (non-blocking) stream.  torch reports its DEFAULT stream as handle 0,
+        which the C ABI reads as "own stream" too: 0 is therefore passed on as cudaStreamLegacy, so
+        that the engine's kernels really are ordered with the caller's torch / NCCL work (round 1 and
+        the first round-2 bench silently ran on the own stream: an NCCL broadcast enqueued before
+        kernel 1 then sat behind the persistent kernel that holds every SM)."""
+        if cuda_stream_handle is None:
+            handle = 0
+        else:
+            handle = int(cuda_stream_handle) or self.CUDA_STREAM_LEGACY
+        self._check(self._lib.ssp_set_stream(self._ctx, ctypes.c_void_p(handle)))
 
     def synchronize(self):
         self._check(self._lib.ssp_synchronize(self._ctx))

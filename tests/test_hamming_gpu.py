@@ -286,3 +286,30 @@ def test_ratio_is_pythons_float64_comparison_for_any_ratio(engine):
     res = engine.hamming_match_pairs([(0, 1)], mode="knn2_ratio", ratio=(7, 10), return_best2=True)
     keep = [i for i in range(len(res.best2)) if res.best2[i, 2] >= 0 and float(res.best2[i, 1]) < 0.7 * float(res.best2[i, 3])]
     np.testing.assert_array_equal(res.query_idx, np.array(keep, dtype=np.int32))
+
+
+@pytest.mark.parametrize("default_stream", [False, True])
+def test_engine_work_is_ordered_with_the_callers_torch_stream(default_stream):
+    """The bank is produced on the caller's stream by an asynchronous copy that sits behind 100 ms of
+    other work; the engine, told to use that stream, must see the copied bytes.  torch names its
+    default stream 0, which the C ABI reads as "own stream": Engine.set_stream maps it to
+    cudaStreamLegacy (round 1 ran kernel 1 on the own stream without anybody noticing)."""
+    import torch
+    sets = synth.descriptor_bank(2, 3000, seed=77, world=4000)
+    bank, offs = ssp_b200.Engine.pack_descriptors(sets)
+    pinned = torch.from_numpy(bank).pin_memory()
+    eng = ssp_b200.Engine(0)
+    stream = torch.cuda.default_stream() if default_stream else torch.cuda.Stream()
+    eng.set_stream(stream.cuda_stream)
+    with torch.cuda.stream(stream):
+        dev = torch.zeros_like(pinned, device="cuda")
+        torch.cuda.synchronize()
+        torch.cuda._sleep(200_000_000)                 # ~0.1 s of work in front of the copy
+        dev.copy_(pinned, non_blocking=True)
+        eng.bind_descriptor_bank(dev.data_ptr(), offs, keepalive=dev)
+        res = eng.hamming_match_pairs([(0, 1)], mode="crosscheck")
+    mq, mt, md = ho.crosscheck(sets[0], sets[1])
+    np.testing.assert_array_equal(res.query_idx, mq)
+    np.testing.assert_array_equal(res.train_idx, mt)
+    assert len(mq) > 500
+    eng.close()
