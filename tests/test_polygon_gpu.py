@@ -404,3 +404,25 @@ def test_batch_measure_of_all_images_equals_the_per_image_form(engine):
         res = engine.polygon_match_pairs([(0, 1), (1, 3), (0, 3), (2, 3)], threshold=10.0, return_rowmin=True)
         np.testing.assert_array_equal(res.argmin, ref.argmin)
         np.testing.assert_array_equal(res.mindist, ref.mindist)
+
+
+def test_compute_star_features_mirror_reproduces_the_reference_star_finder(engine, golden, tmp_path):
+    """image_processors.compute_star_features (Canny -> contours -> brightness -> the n brightest -> ORB)
+    with the per-star brightness loop replaced by ONE launch of the brightness kernel: keypoints, their
+    order and the descriptors equal what the UNCHANGED reference produced on the 4 eisenberg frames
+    (eisenberg_c2.npz: keypoints; eisenberg_c2_stage.npz: the star rows of the merged descriptors)."""
+    from ssp_b200.image_processors import compute_star_features, get_star_brightness
+    c2 = golden("eisenberg_c2.npz")
+    st = golden("eisenberg_c2_stage.npz")
+    for i in range(len(c2["names"])):
+        img = cv2.cvtColor(c2[f"i{i}_gray"], cv2.COLOR_GRAY2BGR)
+        feats = compute_star_features(img, str(c2["names"][i]), str(tmp_path), n_brightest_stars=1000, engine=engine,
+                                      write_debug_images=False)
+        xy = np.array([kp.pt for kp in feats.keypoints], dtype=np.float32).reshape(-1, 2)
+        np.testing.assert_array_equal(xy, c2[f"i{i}_xy"], err_msg=f"frame {i} keypoint positions / order")
+        np.testing.assert_array_equal(np.array([kp.size for kp in feats.keypoints], dtype=np.float32), c2[f"i{i}_size"])
+        n_orb = int(st["n_orb"][i])
+        np.testing.assert_array_equal(feats.descriptors.get(), st[f"i{i}_descriptors"][n_orb:])
+        assert feats.img_size == (img.shape[1], img.shape[0])
+    kp = feats.keypoints[0]
+    assert get_star_brightness(kp, img, engine) == star_brightness(c2[f"i{len(c2['names']) - 1}_gray"], kp.pt)
