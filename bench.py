@@ -362,7 +362,8 @@ def hamming_record(rt, wl, sets, pairs, mode, variant, steps, warmup, cpu_pairs)
     """value / e2e / roofline / cpu_baseline of one Hamming workload in one mode.  Returns the record
     on rank 0 (None elsewhere)."""
     import ssp_b200
-    from ssp_b200.distributed import shard_pairs_contiguous, broadcast_descriptor_bank, gather_matches_resident
+    from ssp_b200.distributed import (shard_pairs_contiguous, shard_bounds, broadcast_descriptor_bank,
+                                      gather_matches_resident)
     torch, world, rank = rt.torch, rt.world, rt.rank
     eng = rt.engine()
 
@@ -377,6 +378,7 @@ def hamming_record(rt, wl, sets, pairs, mode, variant, steps, warmup, cpu_pairs)
     bank_bytes = int(offs_known[-1]) * BYTES_PER_ROW
     cost = [int(sets[a].shape[0]) * int(sets[b].shape[0]) for a, b in pairs]
     local_pairs, lo, hi = shard_pairs_contiguous(pairs, rank, world, cost)
+    max_block = int(np.diff(shard_bounds(len(pairs), world, cost)).max())   # every rank can compute it
 
     # ---- resident bank for the `value` leg ----------------------------------------------------
     if world > 1:
@@ -411,7 +413,7 @@ def hamming_record(rt, wl, sets, pairs, mode, variant, steps, warmup, cpu_pairs)
             eng.bind_descriptor_bank(b_t.data_ptr(), o_all, keepalive=b_t)
             local = eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, fetch=False)
             # survivors: device -> exact-length NCCL transfers into rank 0's arrays -> pinned host memory
-            return gather_matches_resident(eng, local.offsets, dst=0)
+            return gather_matches_resident(eng, local.offsets, dst=0, max_block=max_block)
         eng.upload_descriptor_bank(bank, offs)                           # pinned host -> device
         return eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, pinned=True)  # D2H of survivors
 
@@ -437,7 +439,7 @@ def hamming_record(rt, wl, sets, pairs, mode, variant, steps, warmup, cpu_pairs)
         b_t, o_all = piece("h2d_on_rank0+broadcast", lambda: broadcast_descriptor_bank(bank, offs, 0))
         piece("bind", lambda: eng.bind_descriptor_bank(b_t.data_ptr(), o_all, keepalive=b_t))
         local = piece("expand+kernel1+finalize", lambda: eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, fetch=False))
-        piece("gather_to_rank0+d2h", lambda: gather_matches_resident(eng, local.offsets, dst=0))
+        piece("gather_to_rank0+d2h", lambda: gather_matches_resident(eng, local.offsets, dst=0, max_block=max_block))
     else:
         piece("h2d", lambda: eng.upload_descriptor_bank(bank, offs))
         local = piece("expand+kernel1+finalize", lambda: eng.hamming_match_pairs(local_pairs, mode=mode, variant=variant, fetch=False))

@@ -201,7 +201,7 @@ def _devbuf(tag: str, n: int, dtype: torch.dtype, dev) -> torch.Tensor:
 
 
 def gather_segments(tag: str, fetch_into: Callable, dtypes: Sequence[torch.dtype], local_counts: np.ndarray,
-                    dst: int = 0):
+                    dst: int = 0, max_block: Optional[int] = None):
     """Every rank holds, for its CONTIGUOUS block of pairs, `len(dtypes)` result arrays with
     local_counts[p] entries for its p-th pair.  Brings them to rank `dst` in global pair order:
 
@@ -218,10 +218,16 @@ def gather_segments(tag: str, fetch_into: Callable, dtypes: Sequence[torch.dtype
     rank, world = dist.get_rank(), dist.get_world_size()
     local_counts = np.asarray(local_counts, dtype=np.int64)
     n_local = int(local_counts.sum())
-    # (1) counts: [n_pairs_of_rank, counts..., 0 padding]; block lengths differ by the cost balance
-    width = torch.tensor([len(local_counts)], dtype=torch.int64, device=dev)
-    dist.all_reduce(width, op=dist.ReduceOp.MAX)
-    w = int(width.item())
+    # (1) counts: [n_pairs_of_rank, counts..., 0 padding]; block lengths differ by the cost balance.
+    # max_block = the longest block of any rank, when the caller knows it (every rank can compute the
+    # shard bounds itself): saves one collective and one host synchronisation per step
+    if max_block is None:
+        width = torch.tensor([len(local_counts)], dtype=torch.int64, device=dev)
+        dist.all_reduce(width, op=dist.ReduceOp.MAX)
+        w = int(width.item())
+    else:
+        w = int(max_block)
+        assert w >= len(local_counts)
     mine = torch.zeros(w + 1, dtype=torch.int64)
     mine[0] = len(local_counts)
     mine[1:1 + len(local_counts)] = torch.from_numpy(local_counts)
@@ -250,8 +256,10 @@ def gather_segments(tag: str, fetch_into: Callable, dtypes: Sequence[torch.dtype
         host = []
         for k, dt in enumerate(dtypes):
             h = _pinned(f"{tag}{k}", total, dt)
-            h.copy_(final[k], non_blocking=False)
+            h.copy_(final[k], non_blocking=True)     # all arrays in flight, one synchronisation below
             host.append(h.numpy())
+        if dev.type == "cuda":
+            torch.cuda.current_stream(dev).synchronize()
         offsets = np.zeros(sum(len(c) for c in per_rank) + 1, dtype=np.int64)
         np.cumsum(np.concatenate(per_rank) if per_rank else np.zeros(0, np.int64), out=offsets[1:])
         return offsets, host
@@ -263,26 +271,26 @@ def gather_segments(tag: str, fetch_into: Callable, dtypes: Sequence[torch.dtype
     return None
 
 
-def gather_matches_resident(engine, local_offsets: np.ndarray, dst: int = 0):
+def gather_matches_resident(engine, local_offsets: np.ndarray, dst: int = 0, max_block: Optional[int] = None):
     """Hamming survivors of the last `hamming_match_pairs(local block, fetch=False)` of every rank
     -> HammingResult in global pair order on rank `dst` (None elsewhere), without a host round
     trip on the sending side."""
     def fetch(bufs):
         engine.hamming_fetch_into(bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[2].data_ptr(), bufs[0].numel(),
                                   device=bufs[0].is_cuda)
-    out = gather_segments("ham", fetch, (torch.int32, torch.int32, torch.int32), np.diff(local_offsets), dst)
+    out = gather_segments("ham", fetch, (torch.int32, torch.int32, torch.int32), np.diff(local_offsets), dst, max_block)
     if out is None:
         return None
     offsets, (q, t, d) = out
     return HammingResult(offsets, q, t, d)
 
 
-def gather_polygon_matches_resident(engine, local_offsets: np.ndarray, dst: int = 0):
+def gather_polygon_matches_resident(engine, local_offsets: np.ndarray, dst: int = 0, max_block: Optional[int] = None):
     """Polygon matches (poly1, poly2, dist) of every rank's block -> PolygonMatchResult on `dst`."""
     def fetch(bufs):
         engine.polygon_fetch_into(bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[2].data_ptr(), bufs[0].numel(),
                                   device=bufs[0].is_cuda)
-    out = gather_segments("poly", fetch, (torch.int32, torch.int32, torch.float64), np.diff(local_offsets), dst)
+    out = gather_segments("poly", fetch, (torch.int32, torch.int32, torch.float64), np.diff(local_offsets), dst, max_block)
     if out is None:
         return None
     offsets, (p1, p2, d) = out
