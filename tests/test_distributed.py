@@ -109,12 +109,14 @@ def _worker_resident(rank, world, port, out_path):
                                       _broadcaster)
     pairs, bank, offs = _hamming_inputs()
     collectives = []
-    for step in range(3):     # the steady state is one collective per broadcast
+    _broadcaster("descriptors", 0).CHUNK = 4096     # several pieces even for this small bank
+    for step in range(3):     # the steady state is one pass over the buffer
         bank_t, off = broadcast_descriptor_bank(bank if rank == 0 else None, offs if rank == 0 else None, 0)
         collectives.append(_broadcaster("descriptors", 0).collectives)
         np.testing.assert_array_equal(off, offs)
         np.testing.assert_array_equal(bank_t.numpy(), bank)
-    assert collectives[1] - collectives[0] == 1 and collectives[2] - collectives[1] == 1
+    pieces = -(-_broadcaster("descriptors", 0).capacity // 4096)
+    assert pieces > 2 and collectives[1] - collectives[0] == pieces and collectives[2] - collectives[1] == pieces
     cost = [(offs[a + 1] - offs[a]) * (offs[b + 1] - offs[b]) for a, b in pairs]
     local_pairs, lo, hi = shard_pairs_contiguous(pairs, rank, world, cost)
     local = _oracle_match_fn({"bank": bank_t.numpy(), "offs": off}, "knn2_ratio")(local_pairs)
@@ -254,7 +256,9 @@ def _worker_polygons(rank, world, port, out_path):
     src = (xy, br, cands) if rank == 0 else (None, None, None)
     so, co, xy_t, br_t, cand_t = broadcast_star_bank(*src, src=0)
     eng = _PolygonOracleEngine()
-    counts = measure_polygons_sharded(eng, so, co, xy_t, br_t, cand_t, 1342, 894, 1135.0)
+    # world 2: the exchange (split by image + all-gather); world 3: every rank measures everything
+    counts = measure_polygons_sharded(eng, so, co, xy_t, br_t, cand_t, 1342, 894, 1135.0,
+                                      replicate_below=0 if world == 2 else 1 << 20)
     assert [eng.polygon_count(i) for i in range(5)] == counts.tolist()   # every rank holds every bank now
     cost = [int(counts[a]) * int(counts[b]) for a, b in pairs]
     local_pairs, lo, hi = shard_pairs_contiguous(pairs, rank, world, cost)
