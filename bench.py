@@ -152,7 +152,9 @@ class Runtime:
         self.dev = torch.device("cuda", self.local_rank)
         if self.world > 1:
             import torch.distributed as dist
-            dist.init_process_group("nccl", device_id=self.dev)
+            import datetime
+            # a rank that dies inside a sub-record must not leave the others waiting for ten minutes
+            dist.init_process_group("nccl", device_id=self.dev, timeout=datetime.timedelta(seconds=240))
             self.dist = dist
         # ONE stream for everything: torch ops, NCCL's stream waits and the engine's kernels (a dedicated
         # stream has a non-zero handle; torch's default stream reads as 0 = "engine's own stream" in the C ABI)
@@ -931,12 +933,19 @@ def main():
         want = [s for s in args.sub.split(",") if s]
         k, w = max(1, min(args.steps, args.sub_steps)), max(3, min(args.warmup, 3))
 
+        broken = []
+
         def guarded(name, fn):
-            # a sub-record must never take the headline line down with it
-            try:
-                r = fn()
-            except Exception as e:                                         # noqa: BLE001
-                r = {"error": f"{type(e).__name__}: {e}"[:400]} if rank == 0 else None
+            # a sub-record must never take the headline line down with it; after a failure the process
+            # group may be out of step, so the remaining sub-records are skipped rather than risked
+            if broken:
+                r = {"error": f"skipped after the failure of sub-record {broken[0]!r}"} if rank == 0 else None
+            else:
+                try:
+                    r = fn()
+                except Exception as e:                                     # noqa: BLE001
+                    broken.append(name)
+                    r = {"error": f"{type(e).__name__}: {e}"[:400]} if rank == 0 else None
             if rank == 0:
                 sub[name] = r
 
