@@ -1,5 +1,5 @@
 #!/bin/bash
-# Under `gpurun --gpus N` (N=$N): the default bench line (all sub-records) at N GPUs + the stage-by-stage e2e diagnosis
+# Run under `gpurun --gpus N` with N=... in the environment: the default bench line (all sub-records) at N GPUs + the stage-by-stage e2e diagnosis
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 N=${N:-8}
