@@ -101,6 +101,13 @@ struct TcWork {              // one directed image pair
   // the row direction, and the 16-bit filter thresholds derived from it.  NULL = row direction only.
   uint32_t* col_key;
   int16_t* col_thr;
+  // kNN-2: distance of every query row's 2nd neighbour in the LAST train image it was matched against
+  // (uint16 per row of the query image, 0xFFFF = none yet) -- a prediction of where the k-th best of
+  // this item will settle.  prior_mode bit 0: start the rows at that distance + TC_PRIOR_MARGIN instead
+  // of unfiltered; bit 1: leave this item's 2nd-neighbour distances behind for the next item.
+  uint16_t* prior;
+  int prior_mode;
+  int pad2_;
 };
 
 // ---- bank expansion ---------------------------------------------------------------------------
@@ -238,6 +245,9 @@ struct TcRow {
   TC_PROF(long long p_wait; long long p_pass1; long long p_pass2; long long p_nflag;)
 };
 
+#ifndef TC_PRIOR_MARGIN
+#define TC_PRIOR_MARGIN 2   // a row starts at (predicted 2nd-neighbour distance + this many bits); a row that ends an
+#endif                      // item with fewer than two neighbours inside that radius is redone unfiltered (exact)
 #ifndef TC_PEER_AGED
 #define TC_PEER_AGED 1   // a peer value seen two tiles ago needs no tie margin
 #endif
@@ -605,6 +615,19 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   r.tag = (item & 63u) << 10;
   r.heavy = (w.slot_src == nullptr);
   r.slack = 0;
+  if (K == 2 && w.prior != nullptr && (w.prior_mode & 1) && w.slot_src == nullptr) {
+    // Predicted thresholds: the 2nd-neighbour distance is set by the bulk of unrelated descriptors and
+    // barely moves from one train image to the next, so a row may start FILTERED at the distance it
+    // ended the previous image with, plus a margin -- no unfiltered start-up tiles, a third of the
+    // exact updates.  Exactness: a row that finds two neighbours inside the radius has found its
+    // true two nearest (anything outside is farther than both); one that does not is written out
+    // incomplete and redone from scratch by the sparse pass behind this launch (hamming.cu).
+    const unsigned p = (row >= 0) ? (unsigned)__ldcg(w.prior + row) : 0u;   // L2: written by other SMs a moment ago
+    const bool has = row < 0 || p != 0xFFFFu;
+    if (row < 0) r.thr = 511;                                   // no row: never flagged
+    else if (p != 0xFFFFu) r.thr = r.pq - (int)p - TC_PRIOR_MARGIN - 1;
+    r.heavy = !__all_sync(0xffffffffu, has);                    // a row without a prediction keeps the warp unfiltered
+  }
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
   *r.my_slot = 0;
   uint32_t pv1 = 0xFFFFFFFFu, pv2 = 0xFFFFFFFFu;   // peer values read one and two tiles ago (none yet)
@@ -686,6 +709,8 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
       out.z = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi & TC_KEY_IDX_MASK);
       out.w = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi >> TC_KEY_SHIFT);
       best2[w.out_row + row] = out;
+      if (K == 2 && w.prior != nullptr && (w.prior_mode & 2) && hi != TC_KEY_NONE)
+        w.prior[row] = (uint16_t)(hi >> TC_KEY_SHIFT);
     }
   }
 }
@@ -989,6 +1014,9 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
     t.pad_ = 0;
     t.col_key = w.col_key;
     t.col_thr = w.col_thr;
+    t.prior = w.prior;
+    t.prior_mode = w.prior_mode;
+    t.pad2_ = 0;
     cols = cols || (w.col_key != nullptr);
     const int tiles = w.slot_src ? w.q_tiles : (w.nq + TC_M - 1) / TC_M;
     if (tiles <= 0) continue;

@@ -13,7 +13,7 @@ for n in ${EXPERIMENTS:-1 2 3 0}; do
   rm -f build/hamming_tensor.o
   make EXTRA=-DTC_EXPERIMENT=$n -j8 > /dev/null
   for v in ${VARIANTS:-tensor}; do
-    (cd ../.. && python bench.py --steps 3 --warmup 2 --variant $v --no-cpu-baseline 2>/dev/null |
+    (cd ../.. && python bench.py --steps 3 --warmup 2 --variant $v --no-cpu-baseline --no-sub 2>/dev/null |
       python -c "
 import json,sys
 d=json.loads(sys.stdin.read())

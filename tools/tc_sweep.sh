@@ -11,11 +11,11 @@ for flags in "$@"; do
   rm -f build/hamming_tensor.o
   make EXTRA="$flags" -j8 > /dev/null 2>&1
   for wl in c3 ${C5:+c5}; do
-    (cd ../.. && python bench.py --steps 3 --warmup 2 --workload $wl --no-cpu-baseline 2>/dev/null |
+    (cd ../.. && python bench.py --steps 3 --warmup 2 --workload $wl --no-cpu-baseline --no-sub 2>/dev/null |
       python -c "
 import json,sys
 d=json.loads(sys.stdin.read())
-print('flags [$flags] $wl kernel_ms', round(d['roofline']['kernel_ms_per_launch'],2), 'sm_mhz', d['clocks']['sm_mhz'], d['clocks']['reasons'], 'matches', d['matches_per_step'])") | tee -a "$OUT"
+print('flags [$flags] $wl kernel_ms', round(d['roofline']['kernel_ms_per_launch'],2), 'sm_mhz', d['clocks']['sm_mhz'], d['clocks']['reasons'], 'matches', d['matches_per_step'], 'redone', d.get('redone_rows_per_step'))") | tee -a "$OUT"
   done
 done
 rm -f build/hamming_tensor.o
