@@ -615,17 +615,20 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   r.tag = (item & 63u) << 10;
   r.heavy = (w.slot_src == nullptr);
   r.slack = 0;
+  int thr0 = TC_THR_NONE;   // D the row was started at (predicted threshold), TC_THR_NONE = started unfiltered
   if (K == 2 && w.prior != nullptr && (w.prior_mode & 1) && w.slot_src == nullptr) {
     // Predicted thresholds: the 2nd-neighbour distance is set by the bulk of unrelated descriptors and
     // barely moves from one train image to the next, so a row may start FILTERED at the distance it
     // ended the previous image with, plus a margin -- no unfiltered start-up tiles, a third of the
-    // exact updates.  Exactness: a row that finds two neighbours inside the radius has found its
-    // true two nearest (anything outside is farther than both); one that does not is written out
-    // incomplete and redone from scratch by the sparse pass behind this launch (hamming.cu).
+    // exact updates.  Exactness: only columns with D > thr0 are guaranteed to be examined, so the row
+    // is complete iff its final 2nd best itself lies inside that radius (D > thr0: then everything
+    // outside is farther than both; a warp-uniform update may also pick up columns outside the
+    // radius, which prove nothing).  Any other row is written out incomplete and redone from scratch
+    // by the sparse pass behind this launch (hamming.cu).
     const unsigned p = (row >= 0) ? (unsigned)__ldcg(w.prior + row) : 0u;   // L2: written by other SMs a moment ago
     const bool has = row < 0 || p != 0xFFFFu;
     if (row < 0) r.thr = 511;                                   // no row: never flagged
-    else if (p != 0xFFFFu) r.thr = r.pq - (int)p - TC_PRIOR_MARGIN - 1;
+    else if (p != 0xFFFFu) r.thr = thr0 = r.pq - (int)p - TC_PRIOR_MARGIN - 1;
     r.heavy = !__all_sync(0xffffffffu, has);                    // a row without a prediction keeps the warp unfiltered
   }
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
@@ -701,7 +704,9 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   if (wg == 0) {
     const uint2 o = slot[row_in_tile];
     const uint32_t lo = min(r.m1, o.x);
-    const uint32_t hi = min(max(r.m1, o.x), min(r.m2, o.y));
+    uint32_t hi = min(max(r.m1, o.x), min(r.m2, o.y));
+    // started at a predicted threshold: complete only if the 2nd best lies strictly inside the radius
+    if (K == 2 && thr0 != TC_THR_NONE && hi != TC_KEY_NONE && r.pq - (int)(hi >> TC_KEY_SHIFT) <= thr0) hi = TC_KEY_NONE;
     if (row >= 0) {
       int4 out;
       out.x = (lo == TC_KEY_NONE) ? -1 : (int)(lo & TC_KEY_IDX_MASK);
