@@ -699,9 +699,18 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
                    warp, item, clock64() - p_t0, r.p_wait, r.p_pass1, r.p_pass2, r.p_nflag, n_t * (TC_HALF / 8));)
   // merge the two warpgroups' top-2 (disjoint train subsets) and write the row record
   uint2* slot = merge + (item & 1u) * TC_M;
-  if (wg == 1) slot[row_in_tile] = make_uint2(r.m1, r.m2);
+  if (wg == 1) {
+    slot[row_in_tile] = make_uint2(r.m1, r.m2);
+    // the two warpgroups read the row's prediction at slightly different moments and another item may
+    // have replaced it in between: the completeness test below must use the TIGHTER of the two radii
+    if (K == 2) *r.my_slot = (uint16_t)(thr0 == TC_THR_NONE ? 0 : thr0 + 1024);
+  }
   asm volatile("bar.sync 1, 256;" ::: "memory");
   if (wg == 0) {
+    if (K == 2) {
+      const int peer0 = (int)*reinterpret_cast<const volatile uint16_t*>(peer_slot);
+      if (peer0 != 0) thr0 = max(thr0, peer0 - 1024);
+    }
     const uint2 o = slot[row_in_tile];
     const uint32_t lo = min(r.m1, o.x);
     uint32_t hi = min(max(r.m1, o.x), min(r.m2, o.y));
