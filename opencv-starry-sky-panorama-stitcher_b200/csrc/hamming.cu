@@ -538,14 +538,18 @@ static int hamming_match_impl(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, i
     }
   }
 
-  // kNN-2, tensor variant: predicted thresholds.  Every item leaves the 2nd-neighbour distances of its
-  // query rows behind; an item whose query image was already matched in THIS call against a train image
-  // of similar size starts its rows at those distances (+ margin).  Reset per call: nothing carries over
-  // from one call (one bench step) to the next.  SSP_B200_KNN_PRIOR=0 switches it off (A/B).
+  // kNN-2, tensor variant: predicted thresholds (EXPERIMENTAL, off unless SSP_B200_KNN_PRIOR=1).  Every item
+  // leaves the 2nd-neighbour distances of its query rows behind; an item whose query image was already
+  // matched in THIS call against a train image of similar size starts its rows at those distances
+  // (+ margin) instead of unfiltered, and rows that end incomplete are redone by a sparse pass -- exact.
+  // Measured: the 2nd-neighbour distance moves by +-3 bits from one train image to the
+  // next, so a margin small enough to save work sends 7-30 % of the rows through the redo pass: 69-84 ms
+  // against 65 ms at C3, and C5 is power-capped either way.  Reset per call: nothing carries over from
+  // one call (one bench step) to the next.
   std::vector<int> prior_items;   // indices into `work` of the items that READ a prediction
   if (!cross && tensor && !work.empty()) {
     const char* pe = getenv("SSP_B200_KNN_PRIOR");
-    if (!(pe && pe[0] == '0')) {
+    if (pe && pe[0] == '1') {
       const long long bank_rows = ctx->row_off.back();
       SSP_CUDA_TRY(ctx, ctx->h_prior.ensure((size_t)(bank_rows + 1) * sizeof(uint16_t)));
       SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_prior.p, 0xFF, (size_t)(bank_rows + 1) * sizeof(uint16_t), ctx->stream));

@@ -317,11 +317,12 @@ def test_engine_work_is_ordered_with_the_callers_torch_stream(default_stream):
 
 # ---- kNN-2 with predicted thresholds (a query row starts at its 2nd-neighbour distance of the previous image) ----
 
-def test_knn2_predictions_that_are_far_too_tight_are_redone_exactly(engine):
+def test_knn2_predictions_that_are_far_too_tight_are_redone_exactly(engine, monkeypatch):
     """Image 0 is matched against a near-duplicate of itself first (2nd-neighbour distances of a few
     bits), then against unrelated images: every prediction is far too tight, every row of those items
     comes back incomplete and goes through the unfiltered redo pass.  Results must equal the oracle's,
     and the same with the predictions switched off."""
+    monkeypatch.setenv("SSP_B200_KNN_PRIOR", "1")     # experimental, off by default
     rng = np.random.default_rng(91)
     n = 24_000                                        # 188 query tiles per item: more than one wave of 148 CTAs,
     base = rng.integers(0, 256, size=(n, 32), dtype=np.uint8)   # so that later items find the predictions
