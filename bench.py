@@ -511,7 +511,6 @@ def hamming_record(rt, wl, sets, pairs, mode, variant, steps, warmup, cpu_pairs)
                        "sharding": f"contiguous cost-balanced blocks of the pair list over {world} rank(s)", "l2": L2_NOTE},
             "gcmp_per_s": comparisons / (ms_per_step / 1e3) / 1e9,
             "matches_per_step": n_matches,
-            "redone_rows_per_step": st.get("redone_rows"),   # kNN-2: rows whose predicted threshold was too tight (rank 0)
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": bank_bytes + len(offs_known) * 8,
                     "d2h_bytes_per_step": d2h, "steps": steps, "ms_per_step": e2e_s * 1e3,
                     "gcmp_per_s": comparisons / e2e_s / 1e9, "timeline_ms": timeline},

@@ -151,11 +151,6 @@ int ssp_hamming_fetch_best2(ssp_ctx* ctx, int32_t* best2, int64_t capacity_rows,
  * dominant Hamming kernel during the last ssp_hamming_match_pairs call. */
 int ssp_hamming_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
                            int64_t* comparisons);
-/* Experimental (SSP_B200_KNN_PRIOR=1): kNN-2 with the tensor variant starts a query row at the
- * 2nd-neighbour distance it had against the previous train image of the same call (+ a margin) instead
- * of unfiltered; a row that ends an item with fewer than two neighbours inside that radius is redone
- * unfiltered, so results stay exact.  Number of query rows the last call had to redo (0 when off). */
-int ssp_hamming_last_redone_rows(ssp_ctx* ctx, int64_t* rows);
 
 /* ---- kernel 2: star -> sphere projection and polygon measure --------------------------
  * Star table of all images (the `keypoints[n_orb:]` star keypoints of

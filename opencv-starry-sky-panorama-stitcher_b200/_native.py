@@ -51,7 +51,6 @@ PROTOTYPES = {
     "ssp_hamming_fetch_best2": (_c.c_int, [_ctx_p, _i32p, _c.c_int64, _c.c_int]),
     "ssp_hamming_last_stats": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_float),
                                           _c.POINTER(_c.c_int64)]),
-    "ssp_hamming_last_redone_rows": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int64)]),
     "ssp_upload_star_bank": (_c.c_int, [_ctx_p, _f64p, _f64p, _i64p, _c.c_int, _c.c_int, _c.c_int,
                                         _c.c_double, _c.c_int]),
     "ssp_fetch_star_rays": (_c.c_int, [_ctx_p, _f64p, _c.c_int64, _c.c_int]),

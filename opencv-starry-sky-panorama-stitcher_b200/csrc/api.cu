@@ -76,7 +76,7 @@ int ssp_destroy(ssp_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   ssp::DevBuf* bufs[] = {&ctx->desc_owned, &ctx->h_work,      &ctx->h_pairs,     &ctx->h_best2,
                          &ctx->h_counts,   &ctx->h_offsets,   &ctx->h_mq,        &ctx->h_mt,
-                         &ctx->h_md,       &ctx->h_expanded,  &ctx->h_popc, &ctx->h_tc_work,  &ctx->h_tc_err,  &ctx->h_cc_aux, &ctx->h_cc_mark, &ctx->h_cc_slots, &ctx->h_cc_cls, &ctx->h_col_key, &ctx->h_col_thr, &ctx->h_prior,
+                         &ctx->h_md,       &ctx->h_expanded,  &ctx->h_popc, &ctx->h_tc_work,  &ctx->h_tc_err,  &ctx->h_cc_aux, &ctx->h_cc_mark, &ctx->h_cc_slots, &ctx->h_cc_cls, &ctx->h_col_key, &ctx->h_col_thr,
                          &ctx->s_xy,        &ctx->s_bright,
                          &ctx->s_rays,     &ctx->p_cand,      &ctx->p_status,    &ctx->p_scan,
                          &ctx->p_tmp_idx,  &ctx->p_tmp_angle, &ctx->p_tmp_side,  &ctx->p_tmp_bright,

@@ -78,9 +78,6 @@ struct HammingWork {
   // (hamming << 18 | row, atomicMin) and its 16-bit filter threshold; NULL = row direction only
   uint32_t* col_key = nullptr;
   int16_t* col_thr = nullptr;
-  // tensor variant, kNN-2: predicted 2nd-neighbour distances of the query image's rows (TcWork::prior)
-  uint16_t* prior = nullptr;
-  int prior_mode = 0;
 };
 
 // One image pair for the finalize kernels.
@@ -135,7 +132,6 @@ struct ssp_ctx {
   ssp::DevBuf h_tc_work, h_tc_err;
   ssp::DevBuf h_cc_aux, h_cc_mark, h_cc_slots, h_cc_cls;  // sparse reverse pass of the cross-check
   ssp::DevBuf h_col_key, h_col_thr;                        // fused cross-check: column keys / thresholds
-  ssp::DevBuf h_prior;                                     // kNN-2: predicted 2nd-neighbour distance per bank row
   bool h_expanded_valid = false;
   std::vector<long long> exp_byte_off;  // per image byte offset into h_expanded
   std::vector<int> exp_rows_pad;
@@ -145,7 +141,6 @@ struct ssp_ctx {
   int h_launches = 0;
   float h_main_ms = 0.f;
   long long h_comparisons = 0;
-  long long h_redone_rows = 0;  // kNN-2 with predicted thresholds: query rows the last call had to redo unfiltered
 
   // star bank
   ssp::DevBuf s_xy, s_bright, s_rays;

@@ -245,55 +245,6 @@ cc_slots_kernel(const CrossAux* __restrict__ aux, const int* __restrict__ mark, 
   if (threadIdx.x == 0) cls_count[blockIdx.x * 8 + c] = run;
 }
 
-// kNN-2 with predicted thresholds (hamming_tensor.cu, TcWork::prior): a query row that ended its item
-// with fewer neighbours than the train set can give was started too tight.  block (item, c) lists the
-// incomplete rows q = c (mod 8) of the item as sparse query slots (same layout as cc_slots_kernel) with
-// a distance bound no row can have (600 > 256): the sparse pass redoes them unfiltered.
-struct RedoAux {
-  long long fwd_row;    // best2 rows of the item
-  long long slot_off;   // first slot of the item
-  int nq, nt;
-};
-constexpr int REDO_DIST = 600;
-__global__ void __launch_bounds__(256)
-redo_slots_kernel(const RedoAux* __restrict__ aux, const int4* __restrict__ best2, int* __restrict__ slots,
-                  int* __restrict__ cls_count) {
-  const RedoAux a = aux[blockIdx.x];
-  const int c = blockIdx.y;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  __shared__ int warp_cnt[8];
-  __shared__ int run;
-  if (threadIdx.x == 0) run = 0;
-  __syncthreads();
-  const int n_c = (a.nq - c + 7) / 8;   // rows of this class
-  for (int base = 0; base < n_c; base += 256) {
-    const int i = base + threadIdx.x;
-    const int q = c + 8 * i;
-    bool keep = false;
-    if (i < n_c) {
-      const int4 rec = best2[a.fwd_row + q];
-      keep = (a.nt >= 1 && rec.x < 0) || (a.nt >= 2 && rec.z < 0);
-    }
-    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
-    if (lane == 0) warp_cnt[wid] = __popc(ballot);
-    __syncthreads();
-    int before = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) {
-      const int n = warp_cnt[w];
-      before += (w < wid) ? n : 0;
-      total += n;
-    }
-    if (keep)
-      slots[a.slot_off + (long long)(run + before + __popc(ballot & ((1u << lane) - 1u))) * 8 + c] =
-          q | (REDO_DIST << SSP_SLOT_DIST_SHIFT);
-    __syncthreads();
-    if (threadIdx.x == 0) run += total;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) cls_count[blockIdx.x * 8 + c] = run;
-}
-
 constexpr int FIN_THREADS = 512;
 
 __global__ void __launch_bounds__(FIN_THREADS)
@@ -418,7 +369,6 @@ static int hamming_match_impl(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, i
   ctx->h_launches = 0;
   ctx->h_main_ms = 0.f;
   ctx->h_comparisons = 0;
-  ctx->h_redone_rows = 0;
   ctx->h_match_offsets.assign((size_t)n_pairs + 1, 0);
   if (n_pairs == 0) {
     match_offsets[0] = 0;
@@ -538,36 +488,6 @@ static int hamming_match_impl(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, i
     }
   }
 
-  // kNN-2, tensor variant: predicted thresholds (EXPERIMENTAL, off unless SSP_B200_KNN_PRIOR=1).  Every item
-  // leaves the 2nd-neighbour distances of its query rows behind; an item whose query image was already
-  // matched in THIS call against a train image of similar size starts its rows at those distances
-  // (+ margin) instead of unfiltered, and rows that end incomplete are redone by a sparse pass -- exact.
-  // Measured: the 2nd-neighbour distance moves by +-3 bits from one train image to the
-  // next, so a margin small enough to save work sends 7-30 % of the rows through the redo pass: 69-84 ms
-  // against 65 ms at C3, and C5 is power-capped either way.  Reset per call: nothing carries over from
-  // one call (one bench step) to the next.
-  std::vector<int> prior_items;   // indices into `work` of the items that READ a prediction
-  if (!cross && tensor && !work.empty()) {
-    const char* pe = getenv("SSP_B200_KNN_PRIOR");
-    if (pe && pe[0] == '1') {
-      const long long bank_rows = ctx->row_off.back();
-      SSP_CUDA_TRY(ctx, ctx->h_prior.ensure((size_t)(bank_rows + 1) * sizeof(uint16_t)));
-      SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_prior.p, 0xFF, (size_t)(bank_rows + 1) * sizeof(uint16_t), ctx->stream));
-      std::vector<int> last_nt((size_t)n_images, -1);
-      for (size_t i = 0; i < work.size(); ++i) {
-        HammingWork& w = work[i];
-        w.prior = ctx->h_prior.as<uint16_t>() + ctx->row_off[(size_t)w.qi];
-        w.prior_mode = 2;
-        const int prev = last_nt[(size_t)w.qi];
-        if (prev >= 2 && w.nt >= 2 && 8LL * (w.nt > prev ? w.nt - prev : prev - w.nt) <= prev) {
-          w.prior_mode |= 1;
-          prior_items.push_back((int)i);
-        }
-        last_nt[(size_t)w.qi] = w.nt;
-      }
-    }
-  }
-
   const int k = cross ? 1 : 2;
   float rev_fwd_ms = 0.f;   // sparse cross-check: kernel time of the forward launch (ev0/ev1 then hold the reverse one)
   bool timed = false;
@@ -577,62 +497,9 @@ static int hamming_match_impl(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, i
     if (tensor) {
       NvtxRange range_k("kernel 1 (tcgen05)");
       std::string why;
-      cudaError_t e = launch_hamming_tensor(ctx, work, k, &why, /*wait=*/sparse_rev && !rev_work.empty());   // (the kNN-2 redo below synchronises itself)
+      cudaError_t e = launch_hamming_tensor(ctx, work, k, &why, /*wait=*/sparse_rev && !rev_work.empty());
       if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
       SSP_CUDA_TRY(ctx, e);
-      if (!prior_items.empty()) {
-        // rows that were started too tight come back incomplete: list them, redo them unfiltered
-        float main_ms = 0.f;
-        const int n_items = (int)prior_items.size();
-        std::vector<RedoAux> aux((size_t)n_items);
-        long long slots = 0;
-        for (int i = 0; i < n_items; ++i) {
-          const HammingWork& w = work[(size_t)prior_items[(size_t)i]];
-          aux[(size_t)i].fwd_row = w.out_row;
-          aux[(size_t)i].slot_off = slots;
-          aux[(size_t)i].nq = w.nq;
-          aux[(size_t)i].nt = w.nt;
-          slots += ((long long)w.nq + 127) / 128 * 128 + 256;
-        }
-        SSP_CUDA_TRY(ctx, ctx->h_cc_aux.ensure(aux.size() * sizeof(RedoAux)));
-        SSP_CUDA_TRY(ctx, ctx->h_cc_slots.ensure((size_t)slots * sizeof(int)));
-        SSP_CUDA_TRY(ctx, ctx->h_cc_cls.ensure((size_t)n_items * 8 * sizeof(int)));
-        SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_cc_aux.p, aux.data(), aux.size() * sizeof(RedoAux),
-                                          cudaMemcpyHostToDevice, ctx->stream));
-        SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->h_cc_slots.p, 0xFF, (size_t)slots * sizeof(int), ctx->stream));
-        redo_slots_kernel<<<dim3((unsigned)n_items, 8), 256, 0, ctx->stream>>>(
-            ctx->h_cc_aux.as<RedoAux>(), ctx->h_best2.as<int4>(), ctx->h_cc_slots.as<int>(), ctx->h_cc_cls.as<int>());
-        SSP_CUDA_TRY(ctx, cudaGetLastError());
-        ctx->h_launches += 1;
-        std::vector<int> cls((size_t)n_items * 8);
-        SSP_CUDA_TRY(ctx, cudaMemcpyAsync(cls.data(), ctx->h_cc_cls.p, cls.size() * sizeof(int),
-                                          cudaMemcpyDeviceToHost, ctx->stream));
-        SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-        SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&main_ms, ctx->ev0, ctx->ev1));
-        std::vector<HammingWork> redo;
-        long long redone = 0;
-        for (int i = 0; i < n_items; ++i) {
-          int most = 0;
-          for (int c = 0; c < 8; ++c) {
-            most = cls[(size_t)i * 8 + c] > most ? cls[(size_t)i * 8 + c] : most;
-            redone += cls[(size_t)i * 8 + c];
-          }
-          if (most == 0) continue;
-          HammingWork r = work[(size_t)prior_items[(size_t)i]];
-          r.slot_src = ctx->h_cc_slots.as<int>() + aux[(size_t)i].slot_off;
-          r.q_tiles = (most + 15) / 16;   // 16 slots of every class per 128-slot tile
-          r.prior = nullptr;
-          r.prior_mode = 0;
-          redo.push_back(r);
-        }
-        ctx->h_redone_rows = redone;
-        if (!redo.empty()) {
-          e = launch_hamming_tensor(ctx, redo, k, &why, /*wait=*/false);
-          if (!why.empty()) return fail(ctx, SSP_ERR_INVALID, "tensor variant unavailable: %s", why.c_str());
-          SSP_CUDA_TRY(ctx, e);
-          rev_fwd_ms = main_ms;   // ev0/ev1 now hold the redo launch: the main launch is added back below
-        }
-      }
       if (sparse_rev && !rev_work.empty()) {
         float fwd_ms = 0.f;
         SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&fwd_ms, ctx->ev0, ctx->ev1));  // the launch above has completed
@@ -794,12 +661,6 @@ int ssp_hamming_fetch_best2(ssp_ctx* ctx, int32_t* best2, int64_t capacity_rows,
   SSP_CUDA_TRY(ctx, cudaMemcpyAsync(best2, ctx->h_best2.p, (size_t)ctx->h_total_rows * 16,
                                     from_device_kind(mem_kind), ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  return SSP_OK;
-}
-
-int ssp_hamming_last_redone_rows(ssp_ctx* ctx, int64_t* rows) {
-  if (!ctx || !rows) return SSP_ERR_INVALID;
-  *rows = ctx->h_redone_rows;
   return SSP_OK;
 }
 

@@ -101,13 +101,6 @@ struct TcWork {              // one directed image pair
   // the row direction, and the 16-bit filter thresholds derived from it.  NULL = row direction only.
   uint32_t* col_key;
   int16_t* col_thr;
-  // kNN-2: distance of every query row's 2nd neighbour in the LAST train image it was matched against
-  // (uint16 per row of the query image, 0xFFFF = none yet) -- a prediction of where the k-th best of
-  // this item will settle.  prior_mode bit 0: start the rows at that distance + TC_PRIOR_MARGIN instead
-  // of unfiltered; bit 1: leave this item's 2nd-neighbour distances behind for the next item.
-  uint16_t* prior;
-  int prior_mode;
-  int pad2_;
 };
 
 // ---- bank expansion ---------------------------------------------------------------------------
@@ -245,9 +238,6 @@ struct TcRow {
   TC_PROF(long long p_wait; long long p_pass1; long long p_pass2; long long p_nflag;)
 };
 
-#ifndef TC_PRIOR_MARGIN
-#define TC_PRIOR_MARGIN 2   // a row starts at (predicted 2nd-neighbour distance + this many bits); a row that ends an
-#endif                      // item with fewer than two neighbours inside that radius is redone unfiltered (exact)
 #ifndef TC_PEER_AGED
 #define TC_PEER_AGED 1   // a peer value seen two tiles ago needs no tie margin
 #endif
@@ -615,22 +605,6 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   r.tag = (item & 63u) << 10;
   r.heavy = (w.slot_src == nullptr);
   r.slack = 0;
-  int thr0 = TC_THR_NONE;   // D the row was started at (predicted threshold), TC_THR_NONE = started unfiltered
-  if (K == 2 && w.prior != nullptr && (w.prior_mode & 1) && w.slot_src == nullptr) {
-    // Predicted thresholds: the 2nd-neighbour distance is set by the bulk of unrelated descriptors and
-    // barely moves from one train image to the next, so a row may start FILTERED at the distance it
-    // ended the previous image with, plus a margin -- no unfiltered start-up tiles, a third of the
-    // exact updates.  Exactness: only columns with D > thr0 are guaranteed to be examined, so the row
-    // is complete iff its final 2nd best itself lies inside that radius (D > thr0: then everything
-    // outside is farther than both; a warp-uniform update may also pick up columns outside the
-    // radius, which prove nothing).  Any other row is written out incomplete and redone from scratch
-    // by the sparse pass behind this launch (hamming.cu).
-    const unsigned p = (row >= 0) ? (unsigned)__ldcg(w.prior + row) : 0u;   // L2: written by other SMs a moment ago
-    const bool has = row < 0 || p != 0xFFFFu;
-    if (row < 0) r.thr = 511;                                   // no row: never flagged
-    else if (p != 0xFFFFu) r.thr = thr0 = r.pq - (int)p - TC_PRIOR_MARGIN - 1;
-    r.heavy = !__all_sync(0xffffffffu, has);                    // a row without a prediction keeps the warp unfiltered
-  }
   const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
   *r.my_slot = 0;
   uint32_t pv1 = 0xFFFFFFFFu, pv2 = 0xFFFFFFFFu;   // peer values read one and two tiles ago (none yet)
@@ -699,23 +673,12 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
                    warp, item, clock64() - p_t0, r.p_wait, r.p_pass1, r.p_pass2, r.p_nflag, n_t * (TC_HALF / 8));)
   // merge the two warpgroups' top-2 (disjoint train subsets) and write the row record
   uint2* slot = merge + (item & 1u) * TC_M;
-  if (wg == 1) {
-    slot[row_in_tile] = make_uint2(r.m1, r.m2);
-    // the two warpgroups read the row's prediction at slightly different moments and another item may
-    // have replaced it in between: the completeness test below must use the TIGHTER of the two radii
-    if (K == 2) *r.my_slot = (uint16_t)(thr0 == TC_THR_NONE ? 0 : thr0 + 1024);
-  }
+  if (wg == 1) slot[row_in_tile] = make_uint2(r.m1, r.m2);
   asm volatile("bar.sync 1, 256;" ::: "memory");
   if (wg == 0) {
-    if (K == 2) {
-      const int peer0 = (int)*reinterpret_cast<const volatile uint16_t*>(peer_slot);
-      if (peer0 != 0) thr0 = max(thr0, peer0 - 1024);
-    }
     const uint2 o = slot[row_in_tile];
     const uint32_t lo = min(r.m1, o.x);
-    uint32_t hi = min(max(r.m1, o.x), min(r.m2, o.y));
-    // started at a predicted threshold: complete only if the 2nd best lies strictly inside the radius
-    if (K == 2 && thr0 != TC_THR_NONE && hi != TC_KEY_NONE && r.pq - (int)(hi >> TC_KEY_SHIFT) <= thr0) hi = TC_KEY_NONE;
+    const uint32_t hi = min(max(r.m1, o.x), min(r.m2, o.y));
     if (row >= 0) {
       int4 out;
       out.x = (lo == TC_KEY_NONE) ? -1 : (int)(lo & TC_KEY_IDX_MASK);
@@ -723,8 +686,6 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
       out.z = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi & TC_KEY_IDX_MASK);
       out.w = (K == 1 || hi == TC_KEY_NONE) ? -1 : (int)(hi >> TC_KEY_SHIFT);
       best2[w.out_row + row] = out;
-      if (K == 2 && w.prior != nullptr && (w.prior_mode & 2) && hi != TC_KEY_NONE)
-        w.prior[row] = (uint16_t)(hi >> TC_KEY_SHIFT);
     }
   }
 }
@@ -1028,9 +989,6 @@ cudaError_t launch_hamming_tensor(ssp_ctx* ctx, const std::vector<HammingWork>& 
     t.pad_ = 0;
     t.col_key = w.col_key;
     t.col_thr = w.col_thr;
-    t.prior = w.prior;
-    t.prior_mode = w.prior_mode;
-    t.pad2_ = 0;
     cols = cols || (w.col_key != nullptr);
     const int tiles = w.slot_src ? w.q_tiles : (w.nq + TC_M - 1) / TC_M;
     if (tiles <= 0) continue;

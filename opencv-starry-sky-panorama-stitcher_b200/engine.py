@@ -268,10 +268,7 @@ class Engine:
         n, ms, cmp_ = ctypes.c_int(), ctypes.c_float(), ctypes.c_int64()
         self._check(self._lib.ssp_hamming_last_stats(self._ctx, ctypes.byref(n), ctypes.byref(ms),
                                                      ctypes.byref(cmp_)))
-        redone = ctypes.c_int64()
-        self._check(self._lib.ssp_hamming_last_redone_rows(self._ctx, ctypes.byref(redone)))
-        return {"launches": n.value, "main_kernel_ms": ms.value, "comparisons": cmp_.value,
-                "redone_rows": redone.value}
+        return {"launches": n.value, "main_kernel_ms": ms.value, "comparisons": cmp_.value}
 
     # -- kernel 2 -------------------------------------------------------------------------
     def upload_star_bank(self, xy: Sequence[np.ndarray], brightness: Sequence[np.ndarray],

@@ -313,48 +313,3 @@ def test_engine_work_is_ordered_with_the_callers_torch_stream(default_stream):
     np.testing.assert_array_equal(res.train_idx, mt)
     assert len(mq) > 500
     eng.close()
-
-
-# ---- kNN-2 with predicted thresholds (a query row starts at its 2nd-neighbour distance of the previous image) ----
-
-def test_knn2_predictions_that_are_far_too_tight_are_redone_exactly(engine, monkeypatch):
-    """Image 0 is matched against a near-duplicate of itself first (2nd-neighbour distances of a few
-    bits), then against unrelated images: every prediction is far too tight, every row of those items
-    comes back incomplete and goes through the unfiltered redo pass.  Results must equal the oracle's,
-    and the same with the predictions switched off."""
-    monkeypatch.setenv("SSP_B200_KNN_PRIOR", "1")     # experimental, off by default
-    rng = np.random.default_rng(91)
-    n = 24_000                                        # 188 query tiles per item: more than one wave of 148 CTAs,
-    base = rng.integers(0, 256, size=(n, 32), dtype=np.uint8)   # so that later items find the predictions
-    near = base.copy()
-    near[:, 0] ^= 1                                   # distance 1 to its partner ...
-    near2 = np.concatenate([near, near])              # ... and the partner is there twice: 2nd neighbour at 1, too
-    perm = rng.permutation(len(near2))[:n]
-    sets = [base, near2[perm], rng.integers(0, 256, size=(n, 32), dtype=np.uint8),
-            rng.integers(0, 256, size=(n - 100, 32), dtype=np.uint8), base[:3000]]
-    pairs = [(0, 1), (0, 2), (0, 3), (0, 4), (1, 2), (2, 3)]
-    engine.upload_descriptor_bank(sets)
-    res = engine.hamming_match_pairs(pairs, mode="knn2_ratio", return_best2=True)
-    assert engine.hamming_last_stats()["redone_rows"] >= 1000        # rows whose partner is there twice, in (0, 2)
-    for p, (a, b) in enumerate(pairs):
-        lo, hi = res.best2_offsets[p], res.best2_offsets[p + 1]
-        np.testing.assert_array_equal(res.best2[lo:hi], ho.knn2(sets[a], sets[b]), err_msg=f"pair {(a, b)}")
-    assert_result_equals(res, oracle_pairs(sets, pairs, "knn2_ratio"))
-
-
-@pytest.mark.parametrize("prior", ["1", "0"])
-def test_knn2_with_and_without_predictions_on_a_long_pair_list(engine, monkeypatch, prior):
-    """8 images, all 28 pairs, planted matches + ties, ragged sizes within and beyond the +-12.5 % window
-    in which a prediction is carried over: best-2 records of every pair against the oracle."""
-    monkeypatch.setenv("SSP_B200_KNN_PRIOR", prior)
-    sets = synth.descriptor_bank(6, 20_000, seed=93, world=36_000) + synth.tie_stress_bank(2, 20_000, seed=94)
-    sets[2] = sets[2][:18_800]
-    sets[4] = sets[4][:10_000]
-    pairs = synth.all_pairs(8)
-    engine.upload_descriptor_bank(sets)
-    res = engine.hamming_match_pairs(pairs, mode="knn2_ratio", return_best2=True)
-    for p, (a, b) in enumerate(pairs):
-        lo, hi = res.best2_offsets[p], res.best2_offsets[p + 1]
-        np.testing.assert_array_equal(res.best2[lo:hi], ho.knn2(sets[a], sets[b]), err_msg=f"pair {(a, b)}")
-    if prior == "0":
-        assert engine.hamming_last_stats()["redone_rows"] == 0

@@ -15,7 +15,7 @@ for flags in "$@"; do
       python -c "
 import json,sys
 d=json.loads(sys.stdin.read())
-print('flags [$flags] $wl kernel_ms', round(d['roofline']['kernel_ms_per_launch'],2), 'sm_mhz', d['clocks']['sm_mhz'], d['clocks']['reasons'], 'matches', d['matches_per_step'], 'redone', d.get('redone_rows_per_step'))") | tee -a "$OUT"
+print('flags [$flags] $wl kernel_ms', round(d['roofline']['kernel_ms_per_launch'],2), 'sm_mhz', d['clocks']['sm_mhz'], d['clocks']['reasons'], 'matches', d['matches_per_step'])") | tee -a "$OUT"
   done
 done
 rm -f build/hamming_tensor.o
