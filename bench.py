@@ -841,6 +841,13 @@ def run_stage(args, wl):
     dt = (time.perf_counter() - t0) / args.steps
     kept = sum(1 for mi in infos if mi.src_img_idx >= 0)
     bytes_in = int(g["descriptors"].nbytes)
+    # what comes back per step: (query, train, distance) int32 per cross-check match + the offsets table;
+    # with the device RANSAC also one 3x3 f64 model, an inlier count per pair and a mask byte per match
+    n_matches = sum(len(mi.matches) for mi in infos if 0 <= mi.src_img_idx < mi.dst_img_idx)
+    bytes_out = 0 if reference else n_matches * 12 + (n_pairs + 1) * 8
+    if not reference and args.ransac == "device":
+        bytes_in += int(g["points"].nbytes)
+        bytes_out += n_pairs * (72 + 4) + n_matches
     line = {
         "metric": "image_pairs_matched_per_sec", "value": n_pairs / dt, "unit": "pairs/s", "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
@@ -850,14 +857,16 @@ def run_stage(args, wl):
                    "note": "whole stage incl. cv.findHomography per pair and MatchesInfo construction on the host; "
                            "the matching itself is one engine call in front of the pair loop"},
         "e2e": {"value": n_pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": 0 if reference else bytes_in,
-                "d2h_bytes_per_step": 0},
+                "d2h_bytes_per_step": bytes_out,
+                "bytes_note": "d2h counts the matches of the pairs the stage KEEPS (a lower bound of what the engine returns)"},
     }
     if reference:
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": n_pairs / dt, "unit": "pairs/s", "cores": cv.getNumThreads(), "kind": "reference",
                                 "sample": f"cv2 {cv.__version__} BFMatcher crossCheck per pair + the same host logic, all {n_pairs} pairs per step"}
     else:
-        line["gpu_launches"] = args.steps * 4
+        # the engine's own count of the last match call (+ the one RANSAC launch), per step
+        line["gpu_launches"] = args.steps * (engine.hamming_last_stats()["launches"] + (args.ransac == "device"))
         engine.close()
     return line
 

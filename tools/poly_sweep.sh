@@ -9,7 +9,7 @@ for flags in "$@"; do
   rm -f build/polygon.o
   make EXTRA="$flags" -j8 > /dev/null 2>&1
   for wl in c4cap ${C4:+c4}; do
-    for k in queue legacy; do
+    for k in ${KINDS:-queue legacy}; do
       (cd ../.. && SSP_B200_POLY_COMPARE=$k python bench.py --steps 3 --warmup 3 --workload $wl --no-cpu-baseline 2>/dev/null |
         python -c "
 import json,sys
