@@ -726,24 +726,40 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
     sm_max_mhz = clk.get("sm_max_mhz") or info["sm_clock_khz"] / 1e3
     main_ms = float(np.mean(kernel_ms))
     rates = fp_pipe_peaks()
-    key, what = ("ffma", "FFMA") if fp32 else ("dsub_dmul_dadd_total", "unfused DSUB+DMUL+DADD (numpy's rounding)")
-    flop_per_clk_sm = rates.get(key)
-    if flop_per_clk_sm is not None and fp32:
-        flop_per_clk_sm *= 2.0          # an FFMA is 2 flop; the fp32 mode needs 15 FSUB + 15 FFMA = 45 flop in 30 issues
-        flop_per_clk_sm *= 45.0 / 60.0  # 30 issue slots carry 45 flop, not 60
-    peak = info["sm_count"] * flop_per_clk_sm * sm_max_mhz * 1e6 / 1e12 if flop_per_clk_sm else None
+    sm_hz = sm_max_mhz * 1e6
+    n_sm = info["sm_count"]
     # the kernel prunes exactly (a column whose partial sum already reaches the row's best is dropped):
     # the roofline counts the flops it EXECUTED (counted on the device), never the 45 per evaluation it skipped
     algorithmic = evals_local * FLOP_PER_EVALUATION / (main_ms / 1e3) / 1e12 if main_ms > 0 else None
     achieved = executed_local / (main_ms / 1e3) / 1e12 if (executed_local and main_ms > 0) else None
+    f64_rate = rates.get("dsub_dmul_dadd_total")                     # thread-ops per clock per SM, one flop each
+    f32_rate = max(rates.get("ffma", 0.0), 128.0)                    # nominal 4 x 32 lanes; the r01 microbench reached less
+    peak, peak_def, split = None, "not measured", None
+    if fp32:
+        # the fp32 mode needs 15 FSUB + 15 FFMA = 45 flop in 30 issue slots
+        peak = n_sm * f32_rate * 1.5 * sm_hz / 1e12
+        peak_def = f"{n_sm} SMs x {f32_rate:.0f} thread-ops/clk/SM x 1.5 flop per op (15 FSUB + 15 FFMA) x {sm_max_mhz:g} MHz"
+    elif f64_rate and executed_local:
+        # parity mode: the first-group FILTER of the compacted-pruning kernel runs in single precision
+        # (conservative, 10 ops for 14 flop per column), every result-bearing operation in unfused FP64.
+        # peak = the rate at which the two pipes, one after the other, would get through exactly this mix
+        f32_flops = st.get("executed_flops_fp32") or 0
+        f64_flops = executed_local - f32_flops
+        t64 = f64_flops / (n_sm * f64_rate * sm_hz)
+        t32 = f32_flops / (n_sm * f32_rate * 1.4 * sm_hz)
+        peak = executed_local / (t64 + t32) / 1e12
+        split = {"fp64_flops": f64_flops, "fp32_flops": f32_flops, "fp64_pipe_ms": t64 * 1e3, "fp32_pipe_ms": t32 * 1e3}
+        peak_def = (f"executed flops / (FP64 flops / ({n_sm} SMs x {f64_rate:.1f} unfused DSUB+DMUL+DADD per clk per SM, measured: "
+                    f"profiles/pipe_microbench_r01.json) + single-precision filter flops / ({n_sm} SMs x {f32_rate:.0f} ops/clk/SM x 1.4 flop "
+                    f"per op)) at {sm_max_mhz:g} MHz: the two arithmetic pipes one after the other")
     roofline = {
-        "bound": "fp32-pipe" if fp32 else "fp64-pipe", "kernel": "poly_compare_f32_kernel" if fp32 else "poly_compare_f64_kernel",
+        "bound": "fp32-pipe" if fp32 else "fp64-pipe", "kernel": "poly_compare_f32_kernel" if fp32 else "poly_compare_f64_queue_kernel",
         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak and achieved else None,
         "achieved_counts": "flops executed by the kernel (device counter); pruned terms are not counted",
         "executed_fraction_of_algorithmic_flops": (executed_local / (evals_local * FLOP_PER_EVALUATION)) if executed_local and evals_local else None,
-        "algorithmic_tflops_equivalent": algorithmic,
-        "peak_definition": (f"{info['sm_count']} SMs x {flop_per_clk_sm:.1f} flop/clk/SM ({what}, measured: "
-                            f"profiles/pipe_microbench_r01.json) x {sm_max_mhz:g} MHz") if peak else "not measured",
+        "algorithmic_tflops_equivalent": algorithmic, "executed_by_precision": split,
+        "peak_definition": peak_def,
+        "binding_unit": None if fp32 else "ncu: the shared-memory data pipe and instruction issue, not an arithmetic pipe (profiles/INDEX.md, kernel 3)",
         "flop_per_evaluation": FLOP_PER_EVALUATION, "kernel_ms_per_launch": main_ms,
         "evaluations_per_launch": evals_local, "evaluations_per_s": evals_local / (main_ms / 1e3) if main_ms > 0 else None,
         "traffic": None,

@@ -220,6 +220,10 @@ int ssp_polygon_last_stats(ssp_ctx* ctx, int* n_launches, float* main_kernel_ms,
  * dropped): flops it actually executed in the last call, counted on the device, or -1 when the
  * kernel that ran does not count (fp32 / min-over-shifts / legacy). */
 int ssp_polygon_last_executed_flops(ssp_ctx* ctx, int64_t* executed_flops);
+/* The same count split by precision: the compacted-pruning kernel's first-group FILTER runs in single
+ * precision (conservative: it only decides what the FP64 evaluation looks at), everything that
+ * produces a result in FP64.  Both -1 when the kernel that ran does not count. */
+int ssp_polygon_last_executed_flops_by_precision(ssp_ctx* ctx, int64_t* fp64_flops, int64_t* fp32_flops);
 
 /* ---- row N3: batched RANSAC homography (opt-in, NOT bit-compatible with OpenCV) -----------
  * Stands in for the per-pair cv.findHomography(src_pts, dst_pts, cv.RANSAC, 5) of

@@ -153,6 +153,7 @@ struct ssp_ctx {
   ssp::DevBuf p_cand, p_status, p_scan, p_tmp_idx, p_tmp_angle, p_tmp_side, p_tmp_bright, p_tmp_feat;
   ssp::DevBuf p_pairs, p_argmin, p_mindist, p_counts, p_offsets, p_m1, p_m2, p_md, p_flops;
   long long p_executed_flops = -1;  // flops the last pruning compare executed (device counter), -1 = not counted
+  long long p_executed_flops_f32 = -1;  // of those, the single-precision ones (the conservative first-group filter)
   std::vector<long long> p_match_offsets;
   long long p_total_rows = 0;
   long long p_n_matches = -1;

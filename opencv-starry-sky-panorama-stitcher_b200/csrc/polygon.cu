@@ -476,79 +476,125 @@ poly_compare_f64_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ ar
 // prunes against its own row's threshold, so after the first property group (which all 32 lanes
 // evaluate for every column) the warp drags 2-3 surviving lanes through the other two groups for
 // ~40 % of the columns: ncu showed 18.6 of 32 lanes active per FP64 instruction.  Here the first
-// group stays thread-per-row (row features in registers, column broadcast from shared memory),
-// but a survivor is only QUEUED: (row lane, column, first-group value) goes to a per-warp queue in
-// shared memory (ballot + prefix), and whenever 32 entries are waiting the warp evaluates them as one
-// dense batch -- lane i takes entry i, whatever row it belongs to (row features of the other two
-// groups sit in shared memory too).  An entry that beats its row's threshold is handed to the lane
-// that owns the row (shuffle broadcast, ascending lane = ascending column order per row, rare:
-// O(log P2) per row), which applies the sequential rule of the reference unchanged.  Thresholds
-// used for pruning are the row's own, possibly a few entries stale, i.e. never too small: exact.
+// group is only a thread-per-row FILTER, and a survivor is only QUEUED: (row lane, column) goes to a
+// per-warp queue in shared memory (ballot + prefix), and whenever 32 entries are waiting the warp
+// evaluates them as one dense batch -- lane i takes entry i, whatever row it belongs to (the rows'
+// features sit in shared memory too) -- from scratch, in exactly the operations and the order of
+// poly_dist2_f64<0>.  An entry that beats its row's threshold is handed to the lane that owns the row
+// (shuffle broadcast, ascending lane = ascending column order per row, rare: O(log P2) per row),
+// which applies the sequential rule of the reference unchanged.  Thresholds used for pruning are the
+// row's own, possibly a few entries stale, i.e. never too small: exact.
+//
+// The filter only has to be SAFE (never drop a column whose exact first-group sum is below the row's
+// threshold), not bit-equal, and ncu showed what it has to be cheap in: the shared-memory data pipe
+// (l1tex__data_pipe_lsu_wavefronts 92 % of peak -- a third of it the filter's broadcast loads, one
+// wavefront per 8 bytes per column) and instruction issue (45 per column and warp, 72 % of peak).
+//   PQ_FILTER 2 (default): packed single precision -- the first group's features as floats, k-major,
+//     four columns per LDS.128, two columns per FADD2 / FFMA2: half the wavefronts, half the arithmetic
+//     instructions of the filter, none of them on the FP64 pipe.  Safety: with u = 2^-24, F >= every
+//     abs(feature) involved, delta_k the real differences and e_k the float ones,
+//     abs(e_k - delta_k) <= 4.0000003 u F, so sum e_k^2 <= sum delta_k^2 + 80.0001 u F^2, and the float
+//     accumulation (five roundings of non-negative terms, FMA) gives S_f <= (sum e_k^2)(1 + u)^5.  A
+//     column is dropped iff S_f >= T_f with T_f >= (thr (1 + 2^-48) + 81 u F^2)(1 + 6 u), which implies
+//     sum delta_k^2 >= thr (1 + 2^-48) and so the FP64 sum (>= (1 - 2^-50) sum delta_k^2) >= thr.  F is
+//     taken per row and per column tile; where F^2 could overflow a float, T_f is NaN and nothing drops.
+//   PQ_FILTER 1: FP64 with fused multiply-adds (10 instead of 14 FP64 instructions per column): with the
+//     same rounded differences the fused sum Gf and numpy's G both lie within (1 +- u)^5 of the real
+//     sum, so a column dropped at Gf >= thr (1 + 2^-40) has G >= thr.
 #ifndef PQ_TILE_COLS
 #define PQ_TILE_COLS 64
 #endif
 #ifndef PQ_UNROLL
-#define PQ_UNROLL 4      // columns whose first-group sums are in flight together (independent FP64 chains)
+#define PQ_UNROLL 4      // columns whose first-group sums are in flight together (independent chains)
 #endif
-constexpr int PQ_TILE = PQ_TILE_COLS;        // columns per shared-memory tile (shared memory bounds the occupancy)
+#ifndef PQ_FILTER
+#define PQ_FILTER 2
+#endif
+#ifndef PQ_MIN_BLOCKS
+#define PQ_MIN_BLOCKS 7  // resident blocks per SM the register allocation is held to (72 registers, no spills)
+#endif
+static_assert(PQ_UNROLL % 4 == 0 && PQ_TILE_COLS % PQ_UNROLL == 0, "column steps are whole groups of four");
+constexpr int PQ_TILE = PQ_TILE_COLS;        // columns per shared-memory tile
 constexpr int PQ_QUEUE = 32 * (PQ_UNROLL + 1);   // queue entries per warp: 31 left over + one column step of PQ_UNROLL x 32
 constexpr int PQ_G2 = 3 - POLY_G0 - POLY_G1; // the third property group
-#ifndef PQ_FMA_BOUND
-#define PQ_FMA_BOUND 1   // first-group FILTER with fused multiply-adds (10 instead of 14 FP64 instructions per column)
-#endif
-// The filter only has to be SAFE, not bit-equal: with the same rounded differences d_k, the fused sum
-// Gf = fl(d4^2 + fl(d3^2 + ...)) and numpy's G = fl(fl(d4^2) + fl(fl(d3^2) + ...)) both lie within
-// (1 +- u)^5 of the real sum, so G >= Gf * (1 - 10 u).  A column is dropped only if Gf >= thr * (1 + 2^-40),
-// which implies G >= thr -- exactly the columns the reference's evaluation order would drop, minus a
-// sliver that is kept.  Every survivor is re-evaluated from scratch in numpy's order inside its batch.
+constexpr int PQ_RS = 15;                    // values per row in shared memory: groups POLY_G1, PQ_G2, POLY_G0 (odd: see rows_lo)
+constexpr int PQ_TFS = PQ_TILE + 4;          // floats per feature of the float tile (16-byte aligned rows)
 constexpr double PQ_LOOSE = 1.0 + 9.094947017729282e-13;   // 1 + 2^-40
 
-__global__ void __launch_bounds__(PC_THREADS)
+// Threshold of the float filter for the FP64 threshold thr and the margin 81 u F^2 (see above).
+__device__ __forceinline__ float pq_float_threshold(double thr, double margin, bool f_ok) {
+  const double t = (thr * (1.0 + 3.552713678800501e-15) + margin + 1e-36) * (1.0 + 6.0 * 5.9604644775390625e-8);
+  return f_ok ? __double2float_ru(t) : __int_as_float(0x7fc00000);
+}
+
+__global__ void __launch_bounds__(PC_THREADS, PQ_MIN_BLOCKS)
 poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ argmin,
                               double* __restrict__ mindist, unsigned long long* __restrict__ executed_flops) {
   __shared__ __align__(16) double tile[(PQ_TILE + PQ_UNROLL) * 15];
-#if PQ_FMA_BOUND
-  constexpr int RS = 15;   // the batch re-evaluates all three groups of a row
-#else
-  constexpr int RS = 10;   // groups POLY_G1 and PQ_G2; the first-group sum travels in the queue
-  __shared__ double q_g0[PC_THREADS / 32][PQ_QUEUE];
-#endif
-  __shared__ __align__(16) double rows_s[PC_THREADS * RS];
-  __shared__ double thr_s[PC_THREADS];
+  // rows and thresholds as separate low / high words: a batch reads them at 32 arbitrary rows, and a
+  // 32-bit access at an odd row stride has no bank conflict whatever the rows are (an LDS.64 there took
+  // 3.9 wavefronts instead of 2: rows r and r + 16 share a bank pair)
+  __shared__ unsigned rows_lo[PC_THREADS * PQ_RS], rows_hi[PC_THREADS * PQ_RS];
+  __shared__ unsigned thr_lo[PC_THREADS], thr_hi[PC_THREADS];
   __shared__ int q_rc[PC_THREADS / 32][PQ_QUEUE];             // row lane << 16 | column in tile
+#if PQ_FILTER == 2
+  __shared__ __align__(16) float tile_f[5 * PQ_TFS];           // first group of the tile's columns, feature-major
+  __shared__ unsigned tile_fmax[2];                            // max abs first-group feature of the tile (float bits)
+#endif
   const PolyPair pp = pairs[blockIdx.x];
   const int row0 = blockIdx.y * PC_THREADS;
   if (row0 >= pp.p1) return;
   const int r = row0 + threadIdx.x;
   const bool live = r < pp.p1;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  double a[15];
-#pragma unroll
-  for (int k = 0; k < 15; ++k) a[k] = live ? pp.f1[(long long)r * 15 + k] : 0.0;
+#if PQ_FILTER == 2
+  float2 na[5];          // (-a_k, -a_k) of the first group
+  float f_row = 0.0f;    // >= abs of the row's first-group features
+#else
+  double a0[5];
+#endif
 #pragma unroll
   for (int k = 0; k < 5; ++k) {
-    rows_s[threadIdx.x * RS + k] = a[POLY_G1 * 5 + k];
-    rows_s[threadIdx.x * RS + 5 + k] = a[PQ_G2 * 5 + k];
-#if PQ_FMA_BOUND
-    rows_s[threadIdx.x * RS + 10 + k] = a[POLY_G0 * 5 + k];
+    const double g0v = live ? pp.f1[(long long)r * 15 + POLY_G0 * 5 + k] : 0.0;
+    const double g1v = live ? pp.f1[(long long)r * 15 + POLY_G1 * 5 + k] : 0.0;
+    const double g2v = live ? pp.f1[(long long)r * 15 + PQ_G2 * 5 + k] : 0.0;
+    rows_lo[threadIdx.x * PQ_RS + k] = (unsigned)__double2loint(g1v);
+    rows_hi[threadIdx.x * PQ_RS + k] = (unsigned)__double2hiint(g1v);
+    rows_lo[threadIdx.x * PQ_RS + 5 + k] = (unsigned)__double2loint(g2v);
+    rows_hi[threadIdx.x * PQ_RS + 5 + k] = (unsigned)__double2hiint(g2v);
+    rows_lo[threadIdx.x * PQ_RS + 10 + k] = (unsigned)__double2loint(g0v);
+    rows_hi[threadIdx.x * PQ_RS + 10 + k] = (unsigned)__double2hiint(g0v);
+#if PQ_FILTER == 2
+    const float af = __double2float_rn(g0v);
+    na[k] = make_float2(-af, -af);
+    f_row = fmaxf(f_row, __double2float_ru(fabs(g0v)));
+#else
+    a0[k] = g0v;
 #endif
   }
-  // a dead lane (row beyond p1) never passes the first test
+  // a dead lane (row beyond p1) has threshold -1: nothing it queues ever qualifies
   double thr = live ? INFINITY : -1.0, best = INFINITY;
+#if PQ_FILTER == 2
+  float thr_filter = 0.0f;                       // set per tile
+  double margin = 0.0;
+  bool f_ok = true;
+  if (threadIdx.x < 2) tile_fmax[threadIdx.x] = 0u;
+#else
   double thr_filter = thr;                       // what the first-group filter compares with (thr, loosened)
-  int best_c = 0;
-  thr_s[threadIdx.x] = thr;
-  unsigned flops = 0;
-  int q_n = 0;                                   // entries waiting in this warp's queue (warp-uniform)
-#if !PQ_FMA_BOUND
-  double* my_g0 = q_g0[wid];
 #endif
+  int best_c = 0;
+  thr_lo[threadIdx.x] = (unsigned)__double2loint(thr);
+  thr_hi[threadIdx.x] = (unsigned)__double2hiint(thr);
+  unsigned flops = 0, flops_f32 = 0;   // executed by this thread: FP64 (batches, FP64 filter), single precision (filter)
+  int q_n = 0;                                   // entries waiting in this warp's queue (warp-uniform)
   int* my_rc = q_rc[wid];
-  const double* my_rows = rows_s + wid * 32 * RS;
-  double* my_thr = thr_s + wid * 32;
+  const unsigned* my_rows_lo = rows_lo + wid * 32 * PQ_RS;
+  const unsigned* my_rows_hi = rows_hi + wid * 32 * PQ_RS;
+  unsigned* my_thr_lo = thr_lo + wid * 32;
+  unsigned* my_thr_hi = thr_hi + wid * 32;
 
   // evaluates up to 32 queued entries [first, first + n) as one dense batch
-  auto run_batch = [&](int first, int n, int c0) {
+  auto run_batch = [&](int first, int n, int c0, int ncol) {
     double v = 0.0;
     int rl = 0, col = 0;
     bool cand = false;
@@ -556,34 +602,33 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
       const int rc = my_rc[first + lane];
       rl = rc >> 16;
       col = rc & 0xFFFF;
+    }
+    if (lane < n && col < ncol) {   // a padding column of a ragged tile may get here when nothing is dropped
       const double* b = tile + col * 15;
-      const double* ar = my_rows + rl * RS;
-      const double t = my_thr[rl];
-#if PQ_FMA_BOUND
-      double g0 = 0.0;     // the filter's fused sum was only a bound: the real first group, numpy's order
+      const unsigned* alo = my_rows_lo + rl * PQ_RS;
+      const unsigned* ahi = my_rows_hi + rl * PQ_RS;
+      auto ar = [&](int k) { return __hiloint2double((int)ahi[k], (int)alo[k]); };
+      const double t = __hiloint2double((int)my_thr_hi[rl], (int)my_thr_lo[rl]);
+      double g0 = 0.0;     // the filter's sum was only a bound: the real first group, numpy's order
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
-        const double d = __dsub_rn(ar[10 + k], b[POLY_G0 * 5 + k]);
+        const double d = __dsub_rn(ar(10 + k), b[POLY_G0 * 5 + k]);
         const double sq = __dmul_rn(d, d);
         g0 = (k == 0) ? sq : __dadd_rn(g0, sq);
       }
-      flops += 14;
-#else
-      const double g0 = my_g0[first + lane];
-#endif
       double g1 = 0.0;
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
-        const double d = __dsub_rn(ar[k], b[POLY_G1 * 5 + k]);
+        const double d = __dsub_rn(ar(k), b[POLY_G1 * 5 + k]);
         const double sq = __dmul_rn(d, d);
         g1 = (k == 0) ? sq : __dadd_rn(g1, sq);
       }
-      flops += 15;
+      flops += 14 + 15;
       if (g0 < t && __dadd_rn(g0, g1) < t) {
         double g2 = 0.0;
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
-          const double d = __dsub_rn(ar[5 + k], b[PQ_G2 * 5 + k]);
+          const double d = __dsub_rn(ar(5 + k), b[PQ_G2 * 5 + k]);
           const double sq = __dmul_rn(d, d);
           g2 = (k == 0) ? sq : __dadd_rn(g2, sq);
         }
@@ -611,81 +656,116 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
           best_c = c0 + o_col;
         }
         thr = o_v;
-        thr_filter = PQ_FMA_BOUND ? o_v * PQ_LOOSE : o_v;
-        my_thr[lane] = o_v;
+#if PQ_FILTER == 2
+        thr_filter = pq_float_threshold(o_v, margin, f_ok);
+#else
+        thr_filter = o_v * PQ_LOOSE;
+#endif
+        my_thr_lo[lane] = (unsigned)__double2loint(o_v);
+        my_thr_hi[lane] = (unsigned)__double2hiint(o_v);
       }
       __syncwarp();
     }
   };
 
-  for (int c0 = 0; c0 < pp.p2; c0 += PQ_TILE) {
+  for (int c0 = 0, it = 0; c0 < pp.p2; c0 += PQ_TILE, ++it) {
     const int ncol = min(PQ_TILE, pp.p2 - c0);
+    const int ncol_pad = ((ncol + PQ_UNROLL - 1) / PQ_UNROLL) * PQ_UNROLL;
     __syncthreads();
-    for (int i = threadIdx.x; i < ncol * 15; i += PC_THREADS)
-      tile[i] = pp.f2[(long long)c0 * 15 + i];
+#if PQ_FILTER == 2
+    float fm = 0.0f;
+#endif
+    for (int i = threadIdx.x; i < ncol * 15; i += PC_THREADS) {
+      const double x = pp.f2[(long long)c0 * 15 + i];
+      tile[i] = x;
+#if PQ_FILTER == 2
+      const int col = i / 15, k = i - col * 15 - POLY_G0 * 5;
+      if (k >= 0 && k < 5) {
+        tile_f[k * PQ_TFS + col] = __double2float_rn(x);
+        fm = fmaxf(fm, __double2float_ru(fabs(x)));
+      }
+#endif
+    }
+    // the columns of the last column step past the end of a ragged tile: +inf, they do not pass
+#if PQ_FILTER == 2
+    for (int i = ncol + threadIdx.x; i < ncol_pad; i += PC_THREADS)
+#pragma unroll
+      for (int k = 0; k < 5; ++k) tile_f[k * PQ_TFS + i] = INFINITY;
+    fm = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(fm)));   // non-negative floats order like their bits
+    if (lane == 0) atomicMax(&tile_fmax[it & 1], __float_as_uint(fm));
+#else
+    for (int i = ncol * 15 + threadIdx.x; i < ncol_pad * 15; i += PC_THREADS) tile[i] = INFINITY;
+#endif
     __syncthreads();
+#if PQ_FILTER == 2
+    {
+      const float f = fmaxf(f_row, __uint_as_float(tile_fmax[it & 1]));
+      if (threadIdx.x == 0) tile_fmax[(it + 1) & 1] = 0u;   // the next tile's slot; its atomics come after the next barrier
+      f_ok = f < 1e15f;                                        // f * f stays far from float overflow (and f is not NaN)
+      margin = 81.0 * 5.9604644775390625e-8 * PQ_LOOSE * (double)f * (double)f;
+      thr_filter = pq_float_threshold(thr, margin, f_ok);
+    }
+#endif
     for (int j0 = 0; j0 < ncol; j0 += PQ_UNROLL) {
+#if PQ_FILTER == 2
+      float g0[PQ_UNROLL];
+#pragma unroll
+      for (int u4 = 0; u4 < PQ_UNROLL; u4 += 4) {
+        float2 s01, s23;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const float4 bv = *reinterpret_cast<const float4*>(tile_f + k * PQ_TFS + j0 + u4);
+          const float2 d01 = __fadd2_rn(make_float2(bv.x, bv.y), na[k]);
+          const float2 d23 = __fadd2_rn(make_float2(bv.z, bv.w), na[k]);
+          s01 = (k == 0) ? __fmul2_rn(d01, d01) : __ffma2_rn(d01, d01, s01);
+          s23 = (k == 0) ? __fmul2_rn(d23, d23) : __ffma2_rn(d23, d23, s23);
+        }
+        g0[u4] = s01.x;
+        g0[u4 + 1] = s01.y;
+        g0[u4 + 2] = s23.x;
+        g0[u4 + 3] = s23.y;
+      }
+#else
       double g0[PQ_UNROLL];
 #pragma unroll
       for (int u = 0; u < PQ_UNROLL; ++u) {
-        // columns past the end of a ragged tile read stale shared memory; they never pass (j < ncol below)
         const double* b = tile + (j0 + u) * 15;
         double acc = 0.0;
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
-          const double d = __dsub_rn(a[POLY_G0 * 5 + k], b[POLY_G0 * 5 + k]);
-#if PQ_FMA_BOUND
+          const double d = __dsub_rn(a0[k], b[POLY_G0 * 5 + k]);
           acc = (k == 0) ? __dmul_rn(d, d) : __fma_rn(d, d, acc);
-#else
-          const double sq = __dmul_rn(d, d);
-          acc = (k == 0) ? sq : __dadd_rn(acc, sq);
-#endif
         }
         g0[u] = acc;
       }
+#endif
 #pragma unroll
       for (int u = 0; u < PQ_UNROLL; ++u) {
-        const int j = j0 + u;
-        const bool pass = j < ncol && g0[u] < thr_filter;
+        const bool pass = !(g0[u] >= thr_filter);
         const unsigned m = __ballot_sync(0xffffffffu, pass);
-        if (pass) {
-          const int pos = q_n + __popc(m & ((1u << lane) - 1u));
-#if !PQ_FMA_BOUND
-          my_g0[pos] = g0[u];
-#endif
-          my_rc[pos] = (lane << 16) | j;
-        }
+        if (pass) my_rc[q_n + __popc(m & ((1u << lane) - 1u))] = (lane << 16) | (j0 + u);
         q_n += __popc(m);
       }
       if (q_n >= 32) {   // one call site: dense batches from the front, the (< 32) rest moves up
         __syncwarp();
         int first = 0;
         while (q_n - first >= 32) {
-          run_batch(first, 32, c0);
+          run_batch(first, 32, c0, ncol);
           first += 32;
         }
         const int rest = q_n - first;
         int mr = 0;
-#if !PQ_FMA_BOUND
-        double mg = 0.0;
-        if (lane < rest) mg = my_g0[first + lane];
-#endif
         if (lane < rest) mr = my_rc[first + lane];
         __syncwarp();
-        if (lane < rest) {
-#if !PQ_FMA_BOUND
-          my_g0[lane] = mg;
-#endif
-          my_rc[lane] = mr;
-        }
+        if (lane < rest) my_rc[lane] = mr;
         q_n = rest;
         __syncwarp();
       }
     }
-    flops += live ? 14u * (unsigned)ncol : 0u;
+    (PQ_FILTER == 2 ? flops_f32 : flops) += live ? 14u * (unsigned)ncol : 0u;
     // the tile is about to be overwritten: drain what is left
     if (q_n > 0) {
-      run_batch(0, q_n, c0);
+      run_batch(0, q_n, c0, ncol);
       q_n = 0;
       __syncwarp();
     }
@@ -694,10 +774,16 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
     argmin[pp.out_row + r] = best_c;
     mindist[pp.out_row + r] = best;
   }
-  // flops executed by this warp (lane-level: pruned terms are not counted)
+  // flops executed by this warp (lane-level: pruned terms are not counted): [0] FP64, [1] single precision
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) flops += __shfl_xor_sync(0xffffffffu, flops, o);
-  if (lane == 0 && executed_flops) atomicAdd(executed_flops, (unsigned long long)flops);
+  for (int o = 16; o > 0; o >>= 1) {
+    flops += __shfl_xor_sync(0xffffffffu, flops, o);
+    flops_f32 += __shfl_xor_sync(0xffffffffu, flops_f32, o);
+  }
+  if (lane == 0 && executed_flops) {
+    atomicAdd(executed_flops, (unsigned long long)flops);
+    if (flops_f32) atomicAdd(executed_flops + 1, (unsigned long long)flops_f32);
+  }
 }
 
 // FP32 fast mode (non-parity): features converted on the fly, FMA accumulation.
@@ -1240,6 +1326,7 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
   SSP_CUDA_TRY(ctx, ctx->p_flops.ensure(16));
   SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->p_flops.p, 0, 16, ctx->stream));
   ctx->p_executed_flops = -1;
+  ctx->p_executed_flops_f32 = -1;
   bool counted = false;
   if (max_p1 > 0) {
     NvtxRange range("kernel 3 (polygon compare)");
@@ -1284,13 +1371,16 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
     SSP_CUDA_TRY(ctx, cudaGetLastError());
     ctx->p_launches += 3;
   }
-  unsigned long long flops = 0;
+  unsigned long long flops[2] = {0, 0};
   SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_match_offsets.data(), ctx->p_offsets.p,
                                     ((size_t)n_pairs + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&flops, ctx->p_flops.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(flops, ctx->p_flops.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   const long long total = ctx->p_match_offsets[(size_t)n_pairs];
-  if (counted) ctx->p_executed_flops = (long long)flops;
+  if (counted) {
+    ctx->p_executed_flops = (long long)(flops[0] + flops[1]);
+    ctx->p_executed_flops_f32 = (long long)flops[1];
+  }
   if (max_p1 > 0) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->p_main_ms, ctx->ev0, ctx->ev1));
   for (int p = 0; p <= n_pairs; ++p) match_offsets[p] = ctx->p_match_offsets[(size_t)p];
   ctx->p_n_matches = total;
@@ -1329,6 +1419,13 @@ int ssp_polygon_fetch_rowmin(ssp_ctx* ctx, int32_t* argmin, double* mindist, int
   if (argmin) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(argmin, ctx->p_argmin.p, (size_t)n * 4, kind, ctx->stream));
   if (mindist) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(mindist, ctx->p_mindist.p, (size_t)n * 8, kind, ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+int ssp_polygon_last_executed_flops_by_precision(ssp_ctx* ctx, int64_t* fp64_flops, int64_t* fp32_flops) {
+  if (!ctx || !fp64_flops || !fp32_flops) return SSP_ERR_INVALID;
+  *fp64_flops = ctx->p_executed_flops < 0 ? -1 : ctx->p_executed_flops - ctx->p_executed_flops_f32;
+  *fp32_flops = ctx->p_executed_flops < 0 ? -1 : ctx->p_executed_flops_f32;
   return SSP_OK;
 }
 

@@ -434,8 +434,12 @@ class Engine:
                                                      ctypes.byref(ev)))
         fl = ctypes.c_int64()
         self._check(self._lib.ssp_polygon_last_executed_flops(self._ctx, ctypes.byref(fl)))
+        f64, f32 = ctypes.c_int64(), ctypes.c_int64()
+        self._check(self._lib.ssp_polygon_last_executed_flops_by_precision(self._ctx, ctypes.byref(f64), ctypes.byref(f32)))
         return {"launches": n.value, "main_kernel_ms": ms.value, "evaluations": ev.value,
-                "executed_flops": fl.value if fl.value >= 0 else None}
+                "executed_flops": fl.value if fl.value >= 0 else None,
+                "executed_flops_fp64": f64.value if f64.value >= 0 else None,
+                "executed_flops_fp32": f32.value if f32.value >= 0 else None}
 
     # -- row N3 ---------------------------------------------------------------------------
     def ransac_homography_pairs(self, keypoint_xy: Sequence[np.ndarray], pairs, n_matches: int,

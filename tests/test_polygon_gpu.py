@@ -373,6 +373,51 @@ def test_queue_compare_kernel_equals_per_lane_pruning_and_numpy(engine, monkeypa
     assert engine.polygon_last_stats()["executed_flops"] > 0
 
 
+@pytest.mark.parametrize("case", ["offset_1000", "differences_below_float_resolution", "scale_1e20",
+                                  "scale_1e100", "first_group_sum_at_the_threshold"])
+def test_queue_compare_float_filter_never_drops_a_column_it_must_keep(engine, monkeypatch, case):
+    """The queue kernel's first-group filter runs in packed single precision with a margin that makes
+    it conservative (csrc/polygon.cu, PQ_FILTER 2).  Inputs chosen against that margin: features far
+    from [0, 1], differences a float cannot resolve, magnitudes beyond the float range, and columns
+    whose first-group sum sits within a few double ulps of the row's threshold."""
+    rng = np.random.default_rng(77)
+    rows, cols = 300, 700
+    f1 = rng.uniform(0.0, 1.0, size=(rows, 15))
+    f2 = rng.uniform(0.0, 1.0, size=(cols, 15))
+    if case == "offset_1000":
+        f1 += 1000.0
+        f2 += 1000.0
+    elif case == "differences_below_float_resolution":
+        base = rng.uniform(0.2, 0.8, size=15)
+        f1 = base + rng.uniform(-1e-9, 1e-9, size=(rows, 15))
+        f2 = base + rng.uniform(-1e-9, 1e-9, size=(cols, 15))
+    elif case == "scale_1e20":
+        f1 *= 1e20
+        f2 *= 1e20
+    elif case == "scale_1e100":
+        f1 *= 1e100
+        f2 *= 1e100
+    else:
+        # every column differs from row r only in ONE feature of ONE group by the same amount up to
+        # an ulp: all three group orders see sums that straddle the running threshold
+        f2 = np.repeat(f1[:1], cols, axis=0)
+        step = 0.125 * (1.0 + np.arange(cols) % 7 * 2.0 ** -52)
+        for c in range(cols):
+            f2[c, (c * 5) % 15] += step[c]
+        f1 = np.repeat(f1[:1], rows, axis=0)
+    engine.polygon_upload_features(0, f1)
+    engine.polygon_upload_features(1, f2)
+    out = {}
+    for kind in ("legacy", "queue"):
+        monkeypatch.setenv("SSP_B200_POLY_COMPARE", kind)
+        out[kind] = engine.polygon_match_pairs([(0, 1)], threshold=1e300, return_rowmin=True)
+    np.testing.assert_array_equal(out["queue"].argmin, out["legacy"].argmin)
+    np.testing.assert_array_equal(out["queue"].mindist, out["legacy"].mindist)
+    m = PolygonOracle.compare(f1, f2)
+    np.testing.assert_array_equal(out["queue"].argmin, np.argmin(m, axis=1))
+    np.testing.assert_array_equal(out["queue"].mindist, m.min(axis=1))
+
+
 def test_batch_measure_of_all_images_equals_the_per_image_form(engine):
     """ssp_polygon_measure_batch: several images, ONE measure + ONE compaction launch; banks, counts and
     the matches that follow equal those of the per-image calls -- also with an image without
