@@ -735,6 +735,7 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
     f64_rate = rates.get("dsub_dmul_dadd_total")                     # thread-ops per clock per SM, one flop each
     f32_rate = max(rates.get("ffma", 0.0), 128.0)                    # nominal 4 x 32 lanes; the r01 microbench reached less
     peak, peak_def, split = None, "not measured", None
+    kernel_name = "poly_compare_f32_kernel" if fp32 else "poly_compare_f64_kernel"
     if fp32:
         # the fp32 mode needs 15 FSUB + 15 FFMA = 45 flop in 30 issue slots
         peak = n_sm * f32_rate * 1.5 * sm_hz / 1e12
@@ -745,21 +746,24 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
         # peak = the rate at which the two pipes, one after the other, would get through exactly this mix
         f32_flops = st.get("executed_flops_fp32") or 0
         f64_flops = executed_local - f32_flops
+        screen = f32_flops == 44 * evals_local      # every cell screened on all 15 properties: 15 FADD + FMUL + 14 FFMA
+        flop_per_op = 44.0 / 30.0 if screen else 14.0 / 10.0
+        kernel_name = "poly_compare_f64_screen_kernel" if screen else "poly_compare_f64_queue_kernel"
         t64 = f64_flops / (n_sm * f64_rate * sm_hz)
-        t32 = f32_flops / (n_sm * f32_rate * 1.4 * sm_hz)
+        t32 = f32_flops / (n_sm * f32_rate * flop_per_op * sm_hz)
         peak = executed_local / (t64 + t32) / 1e12
         split = {"fp64_flops": f64_flops, "fp32_flops": f32_flops, "fp64_pipe_ms": t64 * 1e3, "fp32_pipe_ms": t32 * 1e3}
         peak_def = (f"executed flops / (FP64 flops / ({n_sm} SMs x {f64_rate:.1f} unfused DSUB+DMUL+DADD per clk per SM, measured: "
-                    f"profiles/pipe_microbench_r01.json) + single-precision filter flops / ({n_sm} SMs x {f32_rate:.0f} ops/clk/SM x 1.4 flop "
+                    f"profiles/pipe_microbench_r01.json) + single-precision screen flops / ({n_sm} SMs x {f32_rate:.0f} ops/clk/SM x {flop_per_op:.3f} flop "
                     f"per op)) at {sm_max_mhz:g} MHz: the two arithmetic pipes one after the other")
     roofline = {
-        "bound": "fp32-pipe" if fp32 else "fp64-pipe", "kernel": "poly_compare_f32_kernel" if fp32 else "poly_compare_f64_queue_kernel",
+        "bound": "fp32-pipe" if fp32 else "fp64-pipe", "kernel": kernel_name,
         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak and achieved else None,
         "achieved_counts": "flops executed by the kernel (device counter); pruned terms are not counted",
         "executed_fraction_of_algorithmic_flops": (executed_local / (evals_local * FLOP_PER_EVALUATION)) if executed_local and evals_local else None,
         "algorithmic_tflops_equivalent": algorithmic, "executed_by_precision": split,
         "peak_definition": peak_def,
-        "binding_unit": None if fp32 else "ncu: the shared-memory data pipe and instruction issue, not an arithmetic pipe (profiles/INDEX.md, kernel 3)",
+        "binding_unit": None if fp32 else "ncu (profiles/INDEX.md, kernel 3): the screen kernel is bound by the FP32 pipe, the queue kernel by the shared-memory data pipe and instruction issue",
         "flop_per_evaluation": FLOP_PER_EVALUATION, "kernel_ms_per_launch": main_ms,
         "evaluations_per_launch": evals_local, "evaluations_per_s": evals_local / (main_ms / 1e3) if main_ms > 0 else None,
         "traffic": None,

@@ -505,7 +505,7 @@ poly_compare_f64_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ ar
 #define PQ_TILE_COLS 64
 #endif
 #ifndef PQ_UNROLL
-#define PQ_UNROLL 4      // columns whose first-group sums are in flight together (independent chains)
+#define PQ_UNROLL 8      // columns whose first-group sums are in flight together (independent chains)
 #endif
 #ifndef PQ_FILTER
 #define PQ_FILTER 2
@@ -783,6 +783,256 @@ poly_compare_f64_queue_kernel(const PolyPair* __restrict__ pairs, int* __restric
   if (lane == 0 && executed_flops) {
     atomicAdd(executed_flops, (unsigned long long)flops);
     if (flops_f32) atomicAdd(executed_flops + 1, (unsigned long long)flops_f32);
+  }
+}
+
+// FP64 parity kernel, shift 0, with a SINGLE-PRECISION SCREEN in front (round 2, default).  What the
+// reference keeps of a row is its first minimum; a column matters only if its distance is below the
+// row's best so far, which happens O(log P2) times per row.  So every (row, column) cell is first
+// evaluated in packed single precision -- all 15 properties, columns feature-major in shared memory,
+// four columns per LDS.128, two columns per FADD2 / FFMA2, PS_ROWS rows per thread sharing the loads --
+// against a threshold that makes the float sum a SAFE screen (below), and only the cells that pass are
+// queued per warp (row slot, absolute column) and evaluated 32 at a time, from global memory, in FP64
+// and in exactly the operations and the order of poly_dist2_f64<0>; improvements go to the lane that
+// owns the row in ascending column order per row, which applies the reference's sequential rule.
+// The result is the FP64 one bit for bit; the float arithmetic only decides what FP64 looks at.
+//
+// Safety of the screen.  u = 2^-24, F >= abs of every feature of the row and of the column tile,
+// delta_k the real differences, e_k = fl32(fl32(b_k) - fl32(a_k)): abs(e_k - delta_k) <= 4.0000003 u F and
+// abs(delta_k) <= 2 F give sum e_k^2 <= sum delta_k^2 + 240.0002 u F^2; the float accumulation (one FMUL,
+// fourteen FFMA, terms >= 0) gives S_f <= (sum e_k^2)(1 + 15.0001 u).  A cell is dropped iff S_f >= T_f
+// with T_f >= (thr (1 + 2^-48) + 241 u F^2 + 1e-36)(1 + 17 u), hence sum delta_k^2 >= thr (1 + 2^-48), and
+// the FP64 value (nine roundings: >= (1 - 2^-49.8) sum delta_k^2) is >= thr: exactly a cell the
+// reference's evaluation would not have taken.  Rounding towards a smaller S_f (underflow) only keeps
+// more cells; the 1e-36 covers denormal rounding.  Where F^2 could leave the float range (or is NaN) T_f
+// is NaN and every cell passes.  NaN sums pass too and are settled in FP64.
+#ifndef PS_ROWS
+#define PS_ROWS 2        // rows per thread (they share the column loads)
+#endif
+#ifndef PS_TILE_COLS
+#define PS_TILE_COLS 128
+#endif
+#ifndef PS_UNROLL
+#define PS_UNROLL 4      // columns per step
+#endif
+#ifndef PS_MIN_BLOCKS
+#define PS_MIN_BLOCKS 7   // 72 registers (the FP64 batch is the rare path)
+#endif
+static_assert(PS_UNROLL % 4 == 0 && PS_TILE_COLS % PS_UNROLL == 0, "column steps are whole groups of four");
+static_assert(PS_ROWS >= 1 && PS_ROWS <= 4, "row slot is packed into 8 bits");
+constexpr int PS_TFS = PS_TILE_COLS + 4;             // floats per feature of the tile (16-byte aligned rows)
+constexpr int PS_SLOTS = 32 * PS_ROWS;               // rows per warp
+constexpr int PS_CTA_ROWS = PC_THREADS * PS_ROWS;    // rows per block
+constexpr int PS_QUEUE = PS_SLOTS * PS_UNROLL + 32;  // 31 left over + everything one step can add
+constexpr int PS_MAX_COLS = 1 << 24;                 // column index bits of a queue entry
+constexpr int PS_AUTO_MIN_COLS = 8192;               // below this many columns the first-group queue kernel is the default
+
+__device__ __forceinline__ float ps_float_threshold(double thr, double margin, bool f_ok) {
+  const double t = (thr * (1.0 + 3.552713678800501e-15) + margin + 1e-36) * (1.0 + 17.0 * 5.9604644775390625e-8);
+  return f_ok ? __double2float_ru(t) : __int_as_float(0x7fc00000);
+}
+
+__global__ void __launch_bounds__(PC_THREADS, PS_MIN_BLOCKS)
+poly_compare_f64_screen_kernel(const PolyPair* __restrict__ pairs, int* __restrict__ argmin,
+                               double* __restrict__ mindist, unsigned long long* __restrict__ executed_flops) {
+  __shared__ __align__(16) float tile_f[15 * PS_TFS];            // the tile's columns in single precision, feature-major
+  __shared__ unsigned tile_fmax[2];                               // max abs feature of the tile (float bits), by tile parity
+  __shared__ unsigned thr_lo[PC_THREADS * PS_ROWS], thr_hi[PC_THREADS * PS_ROWS];   // FP64 thresholds by row slot
+  __shared__ int q_rc[PC_THREADS / 32][PS_QUEUE];                 // row slot << 24 | column
+  __shared__ int q_cnt[PC_THREADS / 32];
+  const PolyPair pp = pairs[blockIdx.x];
+  const int row0 = blockIdx.y * PS_CTA_ROWS;
+  if (row0 >= pp.p1) return;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int warp_row0 = row0 + wid * PS_SLOTS;    // row slot s = w * 32 + lane of this warp is row warp_row0 + s
+  float na[PS_ROWS][15];                          // -fl32(feature)
+  float f_row[PS_ROWS], thr_f[PS_ROWS];
+  double thr[PS_ROWS], best[PS_ROWS], margin[PS_ROWS];
+  int best_c[PS_ROWS];
+  bool f_ok[PS_ROWS];
+  unsigned* my_thr_lo = thr_lo + wid * PS_SLOTS;
+  unsigned* my_thr_hi = thr_hi + wid * PS_SLOTS;
+  int* my_rc = q_rc[wid];
+#pragma unroll
+  for (int w = 0; w < PS_ROWS; ++w) {
+    const int r = warp_row0 + w * 32 + lane;
+    const bool live = r < pp.p1;
+    f_row[w] = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 15; ++k) {
+      const double x = live ? pp.f1[(long long)r * 15 + k] : 0.0;
+      na[w][k] = -__double2float_rn(x);
+      f_row[w] = fmaxf(f_row[w], __double2float_ru(fabs(x)));
+    }
+    thr[w] = live ? INFINITY : -1.0;             // a dead row: nothing it queues ever qualifies
+    best[w] = INFINITY;
+    best_c[w] = 0;
+    thr_f[w] = 0.0f;                             // set per tile
+    margin[w] = 0.0;
+    f_ok[w] = true;
+    my_thr_lo[w * 32 + lane] = (unsigned)__double2loint(thr[w]);
+    my_thr_hi[w * 32 + lane] = (unsigned)__double2hiint(thr[w]);
+  }
+  if (threadIdx.x < 2) tile_fmax[threadIdx.x] = 0u;
+  if (lane == 0) q_cnt[wid] = 0;
+  unsigned flops = 0, flops_f32 = 0;
+
+  // evaluates the queued entries [first, first + n), n <= 32, in FP64
+  auto run_batch = [&](int first, int n) {
+    double v = 0.0;
+    int slot = 0, col = 0;
+    bool cand = false;
+    if (lane < n) {
+      const int rc = my_rc[first + lane];
+      slot = (int)((unsigned)rc >> 24);
+      col = rc & (PS_MAX_COLS - 1);
+    }
+    const int row = warp_row0 + slot;
+    if (lane < n && row < pp.p1 && col < pp.p2) {   // (dead rows and padding columns get here only through NaNs)
+      double a[15];
+#pragma unroll
+      for (int k = 0; k < 15; ++k) a[k] = pp.f1[(long long)row * 15 + k];
+      const double* b = pp.f2 + (long long)col * 15;
+      const double t = __hiloint2double((int)my_thr_hi[slot], (int)my_thr_lo[slot]);
+      v = poly_dist2_f64<0>(a, b);
+      flops += 45;
+      cand = v < t;
+    }
+    // improvements go to the lane that owns the row, in ascending entry (= column) order
+    unsigned todo = __ballot_sync(FULL, cand);
+    while (todo) {
+      const int src = __ffs((int)todo) - 1;
+      todo &= todo - 1;
+      const int o_slot = __shfl_sync(FULL, slot, src);
+      const int o_col = __shfl_sync(FULL, col, src);
+      const double o_v = __shfl_sync(FULL, v, src);
+      if (lane == (o_slot & 31)) {
+#pragma unroll
+        for (int w = 0; w < PS_ROWS; ++w)
+          if ((o_slot >> 5) == w && o_v < thr[w]) {
+            const double sv = sqrt(o_v);
+            if (sv < best[w]) {
+              best[w] = sv;
+              best_c[w] = o_col;
+            }
+            thr[w] = o_v;
+            thr_f[w] = ps_float_threshold(o_v, margin[w], f_ok[w]);
+            my_thr_lo[o_slot] = (unsigned)__double2loint(o_v);
+            my_thr_hi[o_slot] = (unsigned)__double2hiint(o_v);
+          }
+      }
+      __syncwarp();
+    }
+  };
+
+  for (int c0 = 0, it = 0; c0 < pp.p2; c0 += PS_TILE_COLS, ++it) {
+    const int ncol = min(PS_TILE_COLS, pp.p2 - c0);
+    const int ncol_pad = ((ncol + PS_UNROLL - 1) / PS_UNROLL) * PS_UNROLL;
+    __syncthreads();
+    float fm = 0.0f;
+    for (int i = threadIdx.x; i < ncol * 15; i += PC_THREADS) {
+      const double x = pp.f2[(long long)c0 * 15 + i];
+      const int col = i / 15, k = i - col * 15;
+      tile_f[k * PS_TFS + col] = __double2float_rn(x);
+      fm = fmaxf(fm, __double2float_ru(fabs(x)));
+    }
+    // the columns of the last step past the end of a ragged tile: +inf, dropped by every finite threshold
+    for (int i = ncol + threadIdx.x; i < ncol_pad; i += PC_THREADS)
+#pragma unroll
+      for (int k = 0; k < 15; ++k) tile_f[k * PS_TFS + i] = INFINITY;
+    fm = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(fm)));   // non-negative floats order like their bits
+    if (lane == 0) atomicMax(&tile_fmax[it & 1], __float_as_uint(fm));
+    __syncthreads();
+    {
+      const float f_tile = __uint_as_float(tile_fmax[it & 1]);
+      if (threadIdx.x == 0) tile_fmax[(it + 1) & 1] = 0u;   // the next tile's slot; its atomics come after the next barrier
+#pragma unroll
+      for (int w = 0; w < PS_ROWS; ++w) {
+        const float f = fmaxf(f_row[w], f_tile);
+        f_ok[w] = f < 1e15f;                                 // f * f stays far inside the float range (and f is not NaN)
+        margin[w] = 241.0 * 5.9604644775390625e-8 * (1.0 + 9.094947017729282e-13) * (double)f * (double)f;
+        thr_f[w] = ps_float_threshold(thr[w], margin[w], f_ok[w]);
+      }
+    }
+    for (int j0 = 0; j0 < ncol; j0 += PS_UNROLL) {
+      float2 s[PS_ROWS][PS_UNROLL / 2];
+#pragma unroll
+      for (int k = 0; k < 15; ++k) {
+#pragma unroll
+        for (int u4 = 0; u4 < PS_UNROLL / 4; ++u4) {
+          const float4 bv = *reinterpret_cast<const float4*>(tile_f + k * PS_TFS + j0 + 4 * u4);
+#pragma unroll
+          for (int w = 0; w < PS_ROWS; ++w) {
+            const float2 nk = make_float2(na[w][k], na[w][k]);
+            const float2 d01 = __fadd2_rn(make_float2(bv.x, bv.y), nk);
+            const float2 d23 = __fadd2_rn(make_float2(bv.z, bv.w), nk);
+            s[w][2 * u4] = (k == 0) ? __fmul2_rn(d01, d01) : __ffma2_rn(d01, d01, s[w][2 * u4]);
+            s[w][2 * u4 + 1] = (k == 0) ? __fmul2_rn(d23, d23) : __ffma2_rn(d23, d23, s[w][2 * u4 + 1]);
+          }
+        }
+      }
+      bool any = false;
+#pragma unroll
+      for (int w = 0; w < PS_ROWS; ++w)
+#pragma unroll
+        for (int h = 0; h < PS_UNROLL / 2; ++h)
+          any = any || !(s[w][h].x >= thr_f[w]) || !(s[w][h].y >= thr_f[w]);
+      if (__any_sync(FULL, any)) {
+        // rare: queue the cells that passed, each row's in ascending column order
+#pragma unroll
+        for (int h = 0; h < PS_UNROLL / 2; ++h)
+#pragma unroll
+          for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int w = 0; w < PS_ROWS; ++w) {
+              const float sv = e ? s[w][h].y : s[w][h].x;
+              if (!(sv >= thr_f[w]))
+                my_rc[atomicAdd(&q_cnt[wid], 1)] = ((w * 32 + lane) << 24) | (c0 + j0 + 2 * h + e);
+            }
+        __syncwarp();
+        const int n = *reinterpret_cast<volatile int*>(&q_cnt[wid]);
+        if (n >= 32) {   // dense batches from the front, the (< 32) rest moves up
+          int first = 0;
+          while (n - first >= 32) {
+            run_batch(first, 32);
+            first += 32;
+          }
+          const int rest = n - first;
+          int mr = 0;
+          if (lane < rest) mr = my_rc[first + lane];
+          __syncwarp();
+          if (lane < rest) my_rc[lane] = mr;
+          if (lane == 0) q_cnt[wid] = rest;
+          __syncwarp();
+        }
+      }
+    }
+#pragma unroll
+    for (int w = 0; w < PS_ROWS; ++w) flops_f32 += (warp_row0 + w * 32 + lane < pp.p1) ? 44u * (unsigned)ncol : 0u;
+  }
+  __syncwarp();
+  {
+    const int n = *reinterpret_cast<volatile int*>(&q_cnt[wid]);
+    if (n > 0) run_batch(0, n);
+  }
+#pragma unroll
+  for (int w = 0; w < PS_ROWS; ++w) {
+    const int r = warp_row0 + w * 32 + lane;
+    if (r < pp.p1) {
+      argmin[pp.out_row + r] = best_c[w];
+      mindist[pp.out_row + r] = best[w];
+    }
+  }
+  // flops executed by this warp: [0] FP64, [1] single precision (44 per screened cell)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    flops += __shfl_xor_sync(FULL, flops, o);
+    flops_f32 += __shfl_xor_sync(FULL, flops_f32, o);
+  }
+  if (lane == 0 && executed_flops) {
+    atomicAdd(executed_flops, (unsigned long long)flops);
+    atomicAdd(executed_flops + 1, (unsigned long long)flops_f32);
   }
 }
 
@@ -1294,7 +1544,7 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
   }
   std::vector<PolyPair> pp((size_t)n_pairs);
   long long rows = 0;
-  int max_p1 = 0;
+  int max_p1 = 0, max_p2 = 0;
   for (int p = 0; p < n_pairs; ++p) {
     const int i1 = pairs[2 * p], i2 = pairs[2 * p + 1];
     SSP_REQUIRE(ctx, i1 >= 0 && (size_t)i1 < ctx->poly.size() && ctx->poly[(size_t)i1].count >= 0 &&
@@ -1308,6 +1558,7 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
     pp[p].out_row = rows;
     rows += pp[p].p1;
     max_p1 = pp[p].p1 > max_p1 ? pp[p].p1 : max_p1;
+    max_p2 = pp[p].p2 > max_p2 ? pp[p].p2 : max_p2;
     ctx->p_evaluations += (long long)pp[p].p1 * pp[p].p2;
   }
   ctx->p_total_rows = rows;
@@ -1338,13 +1589,24 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
     const bool ms = (shift_mode == SSP_SHIFT_MIN_OVER_SHIFTS);
     // default: the compacted-pruning kernel (round 2: 85 ms against 108 ms at the 15 000 cap, bit-equal);
     // SSP_B200_POLY_COMPARE=legacy selects round 1's per-lane pruning for A/B runs
+    // which exact kernel: the single-precision screen costs the same ~1.1 ps per cell whatever the data
+    // (52 ms at the 15 000 cap against 69 ms), the first-group queue less where real matches tighten
+    // the rows' thresholds early (2.6 against 3.5 ms at C4, 3.4 k polygons per image)
     const char* env = getenv("SSP_B200_POLY_COMPARE");
     const bool legacy = env && env[0] == 'l';
+    const bool screen_fits = max_p2 < PS_MAX_COLS;
+    const bool queue = (env && env[0] == 'q') || !screen_fits ||
+                       (!(env && env[0] == 's') && max_p2 < PS_AUTO_MIN_COLS);
     if (precision == SSP_PRECISION_FP64) {
       if (ms) poly_compare_f64_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
       else if (legacy) poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
-      else {
+      else if (queue) {
         poly_compare_f64_queue_kernel<<<grid, PC_THREADS, 0, ctx->stream>>>(
+            dp, am, md, ctx->p_flops.as<unsigned long long>());
+        counted = true;
+      } else {
+        dim3 grid_s((unsigned)n_pairs, (unsigned)((max_p1 + PS_CTA_ROWS - 1) / PS_CTA_ROWS));
+        poly_compare_f64_screen_kernel<<<grid_s, PC_THREADS, 0, ctx->stream>>>(
             dp, am, md, ctx->p_flops.as<unsigned long long>());
         counted = true;
       }

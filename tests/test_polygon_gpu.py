@@ -349,7 +349,8 @@ def test_device_candidate_generation_yields_the_reference_candidate_set(engine, 
 
 @pytest.mark.parametrize("rows,cols", [(1, 1), (33, 257), (700, 4100), (3000, 3000)])
 def test_queue_compare_kernel_equals_per_lane_pruning_and_numpy(engine, monkeypatch, rows, cols):
-    """SSP_B200_POLY_COMPARE=queue (survivors of the first property group are queued per warp and
+    """The default kernel (single-precision screen, FP64 evaluation of what passes) and
+    SSP_B200_POLY_COMPARE=queue (survivors of the first property group are queued per warp and
     evaluated as dense batches) must return the per-lane kernel's argmin / mindist bit for bit, also
     with duplicate columns (ties keep the first) and ragged tile ends."""
     feat = synth.polygon_feature_bank(2, max(rows, cols), seed=41)
@@ -362,24 +363,30 @@ def test_queue_compare_kernel_equals_per_lane_pruning_and_numpy(engine, monkeypa
     engine.polygon_upload_features(0, f1)
     engine.polygon_upload_features(1, f2)
     out = {}
-    for kind in ("legacy", "queue"):
+    for kind in ("legacy", "queue", "screen"):
         monkeypatch.setenv("SSP_B200_POLY_COMPARE", kind)
         out[kind] = engine.polygon_match_pairs([(0, 1)], threshold=10.0, return_rowmin=True)
-    np.testing.assert_array_equal(out["queue"].argmin, out["legacy"].argmin)
-    np.testing.assert_array_equal(out["queue"].mindist, out["legacy"].mindist)
+        st = engine.polygon_last_stats()
+        assert (st["executed_flops"] is None) == (kind == "legacy")
     m = PolygonOracle.compare(f1, f2)
-    np.testing.assert_array_equal(out["queue"].argmin, np.argmin(m, axis=1))
-    np.testing.assert_array_equal(out["queue"].mindist, m.min(axis=1))
-    assert engine.polygon_last_stats()["executed_flops"] > 0
+    for kind in ("queue", "screen"):
+        np.testing.assert_array_equal(out[kind].argmin, out["legacy"].argmin)
+        np.testing.assert_array_equal(out[kind].mindist, out["legacy"].mindist)
+        np.testing.assert_array_equal(out[kind].argmin, np.argmin(m, axis=1))
+        np.testing.assert_array_equal(out[kind].mindist, m.min(axis=1))
+    # the screen evaluates every cell once in single precision and only what passes in FP64
+    assert st["executed_flops_fp32"] == 44 * rows * cols and 45 * rows <= st["executed_flops_fp64"] <= 45 * rows * cols
 
 
 @pytest.mark.parametrize("case", ["offset_1000", "differences_below_float_resolution", "scale_1e20",
-                                  "scale_1e100", "first_group_sum_at_the_threshold"])
-def test_queue_compare_float_filter_never_drops_a_column_it_must_keep(engine, monkeypatch, case):
-    """The queue kernel's first-group filter runs in packed single precision with a margin that makes
-    it conservative (csrc/polygon.cu, PQ_FILTER 2).  Inputs chosen against that margin: features far
-    from [0, 1], differences a float cannot resolve, magnitudes beyond the float range, and columns
-    whose first-group sum sits within a few double ulps of the row's threshold."""
+                                  "scale_1e100", "first_group_sum_at_the_threshold",
+                                  "every_column_improves_every_row", "nan_and_inf_features"])
+def test_compare_float_screens_never_drop_a_column_they_must_keep(engine, monkeypatch, case):
+    """The default kernel screens every cell in packed single precision (all 15 properties), the queue
+    kernel its first property group, each with a margin that makes the float sum conservative
+    (csrc/polygon.cu).  Inputs chosen against that margin: features far from [0, 1], differences a
+    float cannot resolve, magnitudes beyond the float range, sums within a few double ulps of the row's
+    threshold, a bank in which every cell passes (queue pressure), and NaN / inf features."""
     rng = np.random.default_rng(77)
     rows, cols = 300, 700
     f1 = rng.uniform(0.0, 1.0, size=(rows, 15))
@@ -397,6 +404,16 @@ def test_queue_compare_float_filter_never_drops_a_column_it_must_keep(engine, mo
     elif case == "scale_1e100":
         f1 *= 1e100
         f2 *= 1e100
+    elif case == "every_column_improves_every_row":
+        base = rng.uniform(0.2, 0.8, size=15)
+        f1 = base + rng.uniform(-1e-4, 1e-4, size=(rows, 15))
+        f2 = np.repeat(base[None, :], cols, axis=0)
+        f2[:, 3] += (cols - np.arange(cols)) * 1e-3       # distances fall monotonically with the column
+    elif case == "nan_and_inf_features":
+        f2[5, 2] = np.nan
+        f2[17, 11] = np.inf
+        f1[3, 7] = np.nan
+        f1[9, 0] = -np.inf
     else:
         # every column differs from row r only in ONE feature of ONE group by the same amount up to
         # an ulp: all three group orders see sums that straddle the running threshold
@@ -408,14 +425,16 @@ def test_queue_compare_float_filter_never_drops_a_column_it_must_keep(engine, mo
     engine.polygon_upload_features(0, f1)
     engine.polygon_upload_features(1, f2)
     out = {}
-    for kind in ("legacy", "queue"):
+    for kind in ("legacy", "queue", "screen"):
         monkeypatch.setenv("SSP_B200_POLY_COMPARE", kind)
         out[kind] = engine.polygon_match_pairs([(0, 1)], threshold=1e300, return_rowmin=True)
-    np.testing.assert_array_equal(out["queue"].argmin, out["legacy"].argmin)
-    np.testing.assert_array_equal(out["queue"].mindist, out["legacy"].mindist)
-    m = PolygonOracle.compare(f1, f2)
-    np.testing.assert_array_equal(out["queue"].argmin, np.argmin(m, axis=1))
-    np.testing.assert_array_equal(out["queue"].mindist, m.min(axis=1))
+    for kind in ("queue", "screen"):
+        np.testing.assert_array_equal(out[kind].argmin, out["legacy"].argmin)
+        np.testing.assert_array_equal(out[kind].mindist, out["legacy"].mindist)
+    if case != "nan_and_inf_features":     # numpy's argmin stops at a NaN; the kernels skip it like the per-lane one
+        m = PolygonOracle.compare(f1, f2)
+        np.testing.assert_array_equal(out["screen"].argmin, np.argmin(m, axis=1))
+        np.testing.assert_array_equal(out["screen"].mindist, m.min(axis=1))
 
 
 def test_batch_measure_of_all_images_equals_the_per_image_form(engine):
