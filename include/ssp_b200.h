@@ -224,6 +224,14 @@ int ssp_polygon_last_executed_flops(ssp_ctx* ctx, int64_t* executed_flops);
  * precision (conservative: it only decides what the FP64 evaluation looks at), everything that
  * produces a result in FP64.  Both -1 when the kernel that ran does not count. */
 int ssp_polygon_last_executed_flops_by_precision(ssp_ctx* ctx, int64_t* fp64_flops, int64_t* fp32_flops);
+/* The default parity compare screens every (row, column) cell with a TF32 tensor-core contraction and
+ * evaluates in FP64 only the cells that can hold a row's minimum.  Of the last call: whether that form ran
+ * to the end (used_tensor), why it was abandoned for the CUDA-core kernels if it was (fallback_flags: 1
+ * shared-memory alignment, 2 features beyond the float range, 4 candidate pool overflow, 8 a screen value
+ * further from its FP64 value than the bound), the candidates it evaluated in FP64, the largest
+ * abs(screen - FP64) / F^2 seen among them and the bound it must stay under (F = largest abs feature). */
+int ssp_polygon_last_screen_stats(ssp_ctx* ctx, int* used_tensor, int* fallback_flags, int64_t* candidates,
+                                  double* worst_error_coef, double* bound_coef);
 
 /* ---- row N3: batched RANSAC homography (opt-in, NOT bit-compatible with OpenCV) -----------
  * Stands in for the per-pair cv.findHomography(src_pts, dst_pts, cv.RANSAC, 5) of

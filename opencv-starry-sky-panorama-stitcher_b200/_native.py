@@ -70,6 +70,8 @@ PROTOTYPES = {
                                           _c.POINTER(_c.c_int64)]),
     "ssp_polygon_last_executed_flops": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int64)]),
     "ssp_polygon_last_executed_flops_by_precision": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64)]),
+    "ssp_polygon_last_screen_stats": (_c.c_int, [_ctx_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_int), _c.POINTER(_c.c_int64),
+                                                 _c.POINTER(_c.c_double), _c.POINTER(_c.c_double)]),
     "ssp_ransac_homography_pairs": (_c.c_int, [_ctx_p, _vp, _i64p, _c.c_int, _i32p, _c.c_int, _c.c_double, _c.c_int,
                                                _c.c_uint32, _c.c_int, _f64p, _u8p, _c.c_int64, _i32p]),
     "ssp_star_regions": (_c.c_int, [_ctx_p, _c.c_int, _vp, _c.c_int64]),

@@ -152,6 +152,15 @@ struct ssp_ctx {
   std::vector<ssp::PolyImage> poly;
   ssp::DevBuf p_cand, p_status, p_scan, p_tmp_idx, p_tmp_angle, p_tmp_side, p_tmp_bright, p_tmp_feat;
   ssp::DevBuf p_pairs, p_argmin, p_mindist, p_counts, p_offsets, p_m1, p_m2, p_md, p_flops;
+  // tensor-core screen of kernel 3 (polygon_tensor.cuh): operand banks, |a|^2 table, F per image, tables,
+  // candidate pool (+ sqrt values), per-CTA counts, row keys, flags + stats
+  ssp::DevBuf t_bank, t_na2, t_f, t_imgs, t_work, t_na2ptr, t_pool, t_sv, t_counts, t_rowkey, t_flags;
+  long long t_stats_off = 0;    // statistics word behind the F table
+  int t_grid = 0;
+  int t_used = 0;               // the last ssp_polygon_match_pairs call ran the tensor-core screen
+  int t_fallback_flags = 0;     // non-zero: it was abandoned for the CUDA-core kernels (PT_FLAG_*)
+  long long t_candidates = -1;
+  double t_worst_coef = -1.0;   // max abs(screen - FP64) / F^2 over the candidates of the last call
   long long p_executed_flops = -1;  // flops the last pruning compare executed (device counter), -1 = not counted
   long long p_executed_flops_f32 = -1;  // of those, the single-precision ones (the conservative first-group filter)
   std::vector<long long> p_match_offsets;
@@ -253,6 +262,61 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
           "r"(smem_u32(dst)),
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
+}
+// ---- tcgen05 helpers shared by the tensor-core kernels (hamming_tensor.cu, polygon_tensor.cu) ----
+// mbarrier wait.  try_wait carries a suspend-time hint so the polling warp sleeps in hardware
+// instead of burning issue slots of the SM sub-partition it shares with two epilogue warps (ncu:
+// the clock64-per-iteration loop this replaces was 22 % of all issued instructions).  Watchdog by
+// spin count: a protocol bug must surface as a CUDA error, not as a hung GPU.
+constexpr uint32_t TC_WAIT_HINT_NS = 20000;
+__device__ __forceinline__ bool tc_try_wait_hint(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
+      " selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(TC_WAIT_HINT_NS)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void tc_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!tc_try_wait_hint(bar, parity)) {
+    if (++spins > 100000000u) __trap();
+  }
+}
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
+// start address >> 4 [0,14), LBO >> 4 [16,30) (unused for swizzled K-major), SBO >> 4 [32,46)
+// = 1024 B between 8-row groups, version 1 [46,48), layout type 2 = SWIZZLE_128B [61,64).
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__device__ __forceinline__ void tc_release(uint64_t* acc_empty, int lane) {
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(acc_empty);
 }
 // Exclusive scan of n ints into n+1 int64 offsets, single CTA (n is the number of pairs).
 static __global__ void __launch_bounds__(1024) scan_counts_kernel(const int* __restrict__ counts, int n,

@@ -158,43 +158,8 @@ expand_bank_kernel(const uint8_t* __restrict__ bank, const ExpandImg* __restrict
   *reinterpret_cast<uint4*>(out + enc_stride + off) = vt;
 }
 
-// mbarrier wait.  try_wait carries a suspend-time hint so the polling warp sleeps in hardware
-// instead of burning issue slots of the SM sub-partition it shares with two epilogue warps (ncu:
-// the clock64-per-iteration loop this replaces was 22 % of all issued instructions).  Watchdog by
-// spin count: a protocol bug must surface as a CUDA error, not as a hung GPU.
-constexpr uint32_t TC_WAIT_HINT_NS = 20000;
-__device__ __forceinline__ bool tc_try_wait_hint(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n"
-      " .reg .pred p;\n"
-      " mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
-      " selp.u32 %0, 1, 0, p;\n"
-      "}\n"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity), "r"(TC_WAIT_HINT_NS)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void tc_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!tc_try_wait_hint(bar, parity)) {
-    if (++spins > 100000000u) __trap();
-  }
-}
-
-// ---- PTX wrappers ---------------------------------------------------------------------------------
-__device__ __forceinline__ void tc_fence_before() {
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tc_fence_after() {
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                   smem_u32(bar))
-               : "memory");
-}
+// (mbarrier wait with a hardware sleep hint, tcgen05 fences / commit, the UMMA shared-memory descriptor and
+// the accumulator hand-back live in common.cuh: the polygon screen kernel uses the same ones)
 // D[tmem] (+)= A[smem] * B[smem]^T, int8 x int8 -> int32, M128 N256 K32
 __device__ __forceinline__ void tc_mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
                                           uint32_t idesc, uint32_t accumulate) {
@@ -206,18 +171,6 @@ __device__ __forceinline__ void tc_mma_i8(uint32_t tmem_d, uint64_t adesc, uint6
       "}\n" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
-}
-// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
-// start address >> 4 [0,14), LBO >> 4 [16,30) (unused for swizzled K-major), SBO >> 4 [32,46)
-// = 1024 B between 8-row groups, version 1 [46,48), layout type 2 = SWIZZLE_128B [61,64).
-__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)1 << 16;
-  d |= (uint64_t)(1024 >> 4) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
-  return d;
 }
 // instruction descriptor (cute::UMMA::InstrDescriptor): c_format S32 = 2 [4,6), a/b format
 // signed int8 = 1 [7,10) / [10,13), both K-major, N >> 3 [17,23), M >> 4 [24,29)
@@ -288,11 +241,6 @@ __device__ __forceinline__ uint32_t tc_pop(uint32_t& flags) {
   const uint32_t c = (uint32_t)__ffs((int)flags) - 1u;
   flags &= flags - 1u;
   return c;
-}
-__device__ __forceinline__ void tc_release(uint64_t* acc_empty, int lane) {
-  tc_fence_before();
-  __syncwarp();
-  if (lane == 0) mbar_arrive(acc_empty);
 }
 // Pass 2 for a tile in which MANY chunks are flagged (the first tiles of every work item, while
 // the thresholds are still settling): one branch-free tournament over all 128 columns instead of

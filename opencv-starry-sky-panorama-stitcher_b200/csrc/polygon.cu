@@ -1146,6 +1146,131 @@ poly_compact_kernel(const PolyPair* __restrict__ pairs, const int* __restrict__ 
 }  // namespace ssp
 
 // =============================================================================================
+
+#include "polygon_tensor.cuh"
+
+// Launches the tensor-core screen and the exact part for the pairs of this call (polygon_tensor.cuh).
+// Everything is queued on ctx->stream; flags and statistics are read by the caller behind its one
+// synchronisation.  `counted`: the device counter holds the FP64 flops of the exact part.
+static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ssp::PolyPair>& pp,
+                                              const int32_t* pairs, int n_pairs, long long rows) {
+  using namespace ssp;
+  cudaError_t e;
+  // operand banks of the images this call touches
+  std::vector<int> slot_of(ctx->poly.size(), -1);
+  std::vector<PtBankImg> imgs;
+  std::vector<long long> off, row0;
+  long long bytes = 0, n_rows = 0;
+  int max_pad = 0;
+  for (int p = 0; p < n_pairs; ++p)
+    for (int s = 0; s < 2; ++s) {
+      const int i = pairs[2 * p + s];
+      if (slot_of[(size_t)i] >= 0) continue;
+      const long long count = ctx->poly[(size_t)i].count;
+      PtBankImg im;
+      im.feat = ctx->poly[(size_t)i].feat.as<double>();
+      im.count = (int)count;
+      im.rows_pad = (int)((count + PT_PAD - 1) / PT_PAD * PT_PAD);
+      im.out_off = bytes;
+      im.row0 = n_rows;
+      im.slot = (int)imgs.size();
+      im.pad_ = 0;
+      slot_of[(size_t)i] = im.slot;
+      bytes += 2ll * im.rows_pad * PT_ROW_BYTES;
+      n_rows += count;
+      max_pad = im.rows_pad > max_pad ? im.rows_pad : max_pad;
+      imgs.push_back(im);
+    }
+  if ((e = ctx->t_bank.ensure((size_t)bytes + 1024)) != cudaSuccess) return e;
+  if ((e = ctx->t_na2.ensure((size_t)(n_rows + 1) * 8)) != cudaSuccess) return e;
+  if ((e = ctx->t_f.ensure(imgs.size() * 4 + 16)) != cudaSuccess) return e;   // + statistics word behind the table
+  if ((e = ctx->t_imgs.ensure(imgs.size() * sizeof(PtBankImg))) != cudaSuccess) return e;
+  if ((e = ctx->t_flags.ensure(sizeof(int))) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(ctx->t_f.p, 0, imgs.size() * 4 + 16, ctx->stream)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(ctx->t_flags.p, 0, sizeof(int), ctx->stream)) != cudaSuccess) return e;
+  // pageable sources: the runtime stages them before returning
+  if ((e = cudaMemcpyAsync(ctx->t_imgs.p, imgs.data(), imgs.size() * sizeof(PtBankImg), cudaMemcpyHostToDevice,
+                           ctx->stream)) != cudaSuccess)
+    return e;
+  // work list, one entry per pair (pairs without rows or columns own no tile)
+  std::vector<PtWork> tw((size_t)n_pairs);
+  std::vector<const double*> na2ptr((size_t)n_pairs);
+  int total = 0;
+  for (int p = 0; p < n_pairs; ++p) {
+    const PtBankImg& a = imgs[(size_t)slot_of[(size_t)pairs[2 * p]]];
+    const PtBankImg& b = imgs[(size_t)slot_of[(size_t)pairs[2 * p + 1]]];
+    PtWork& w = tw[(size_t)p];
+    w.a_exp = ctx->t_bank.as<uint8_t>() + a.out_off;
+    w.b_exp = ctx->t_bank.as<uint8_t>() + b.out_off + (size_t)b.rows_pad * PT_ROW_BYTES;
+    w.f_a = ctx->t_f.as<float>() + a.slot;
+    w.f_b = ctx->t_f.as<float>() + b.slot;
+    w.p1 = pp[(size_t)p].p1;
+    w.p2 = pp[(size_t)p].p2;
+    w.a_rows_pad = a.rows_pad;
+    w.b_rows_pad = b.rows_pad;
+    w.tile_begin = total;
+    w.pair = p;
+    na2ptr[(size_t)p] = ctx->t_na2.as<double>() + a.row0;
+    if (w.p1 > 0 && w.p2 > 0) total += (w.p1 + PT_M - 1) / PT_M;
+  }
+  if ((e = ctx->t_work.ensure(tw.size() * sizeof(PtWork))) != cudaSuccess) return e;
+  if ((e = ctx->t_na2ptr.ensure(na2ptr.size() * sizeof(double*))) != cudaSuccess) return e;
+  if ((e = cudaMemcpyAsync(ctx->t_work.p, tw.data(), tw.size() * sizeof(PtWork), cudaMemcpyHostToDevice,
+                           ctx->stream)) != cudaSuccess)
+    return e;
+  if ((e = cudaMemcpyAsync(ctx->t_na2ptr.p, na2ptr.data(), na2ptr.size() * sizeof(double*), cudaMemcpyHostToDevice,
+                           ctx->stream)) != cudaSuccess)
+    return e;
+  const int grid = total < ctx->sm_count ? (total > 0 ? total : 1) : ctx->sm_count;
+  // candidate pool: ~ln(P2) + a few per row are expected; 24 per row and a floor per CTA, split evenly
+  const unsigned long long pool_total = 24ull * (unsigned long long)rows + 8192ull * (unsigned)grid;
+  const unsigned seg_cap = (unsigned)(pool_total / (unsigned)grid);
+  if ((e = ctx->t_pool.ensure((size_t)seg_cap * grid * sizeof(PtCand))) != cudaSuccess) return e;
+  if ((e = ctx->t_sv.ensure((size_t)seg_cap * grid * 8)) != cudaSuccess) return e;
+  if ((e = ctx->t_counts.ensure((size_t)grid * 4)) != cudaSuccess) return e;
+  if ((e = ctx->t_rowkey.ensure((size_t)(rows + 1) * 8)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(ctx->t_counts.p, 0, (size_t)grid * 4, ctx->stream)) != cudaSuccess) return e;
+
+  if ((e = cudaEventRecord(ctx->ev0, ctx->stream)) != cudaSuccess) return e;
+  {
+    const long long threads = (long long)max_pad * 16;
+    poly_tf32_bank_kernel<<<dim3((unsigned)((threads + 255) / 256), (unsigned)imgs.size()), 256, 0, ctx->stream>>>(
+        ctx->t_imgs.as<PtBankImg>(), ctx->t_bank.as<uint8_t>(), ctx->t_na2.as<double>(), ctx->t_f.as<unsigned>());
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  }
+  poly_cand_init_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, ctx->stream>>>(
+      ctx->t_rowkey.as<unsigned long long>(), ctx->p_argmin.as<int>(), rows);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  if (total > 0) {
+    if ((e = cudaFuncSetAttribute(poly_screen_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)PT_SMEM_BYTES)) != cudaSuccess)
+      return e;
+    poly_screen_tcgen05_kernel<<<grid, PT_THREADS, PT_SMEM_BYTES, ctx->stream>>>(
+        ctx->t_work.as<PtWork>(), n_pairs, total, ctx->t_pool.as<PtCand>(), seg_cap, ctx->t_counts.as<unsigned>(),
+        ctx->t_flags.as<int>());
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    unsigned* stats = ctx->t_f.as<unsigned>() + imgs.size();
+    poly_cand_eval_kernel<<<dim3(64, (unsigned)grid), 256, 0, ctx->stream>>>(
+        ctx->p_pairs.as<PolyPair>(), ctx->t_work.as<PtWork>(), ctx->t_pool.as<PtCand>(), seg_cap,
+        ctx->t_counts.as<unsigned>(), ctx->t_na2ptr.as<const double*>(), ctx->t_sv.as<double>(),
+        ctx->t_rowkey.as<unsigned long long>(), stats, ctx->t_flags.as<int>(), ctx->p_flops.as<unsigned long long>());
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    poly_cand_argmin_kernel<<<dim3(64, (unsigned)grid), 256, 0, ctx->stream>>>(
+        ctx->p_pairs.as<PolyPair>(), ctx->t_pool.as<PtCand>(), seg_cap, ctx->t_counts.as<unsigned>(),
+        ctx->t_sv.as<double>(), ctx->t_rowkey.as<unsigned long long>(), ctx->p_argmin.as<int>());
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  }
+  poly_cand_finish_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, ctx->stream>>>(
+      ctx->t_rowkey.as<unsigned long long>(), ctx->p_argmin.as<int>(), ctx->p_mindist.as<double>(), rows);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  if ((e = cudaEventRecord(ctx->ev1, ctx->stream)) != cudaSuccess) return e;
+  ctx->p_launches += total > 0 ? 6 : 3;
+  ctx->t_stats_off = (long long)imgs.size();
+  ctx->t_grid = grid;
+  return cudaSuccess;
+}
+
+
 extern "C" {
 
 int ssp_upload_star_bank(ssp_ctx* ctx, const double* xy, const double* brightness,
@@ -1517,6 +1642,7 @@ int ssp_polygon_upload_features(ssp_ctx* ctx, int image, const double* feat,
   return SSP_OK;
 }
 
+
 int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, double threshold,
                             int shift_mode, int precision, int64_t* match_offsets) {
   using namespace ssp;
@@ -1575,75 +1701,115 @@ int ssp_polygon_match_pairs(ssp_ctx* ctx, const int32_t* pairs, int n_pairs, dou
   SSP_CUDA_TRY(ctx, ctx->p_m2.ensure((size_t)(rows + 1) * 4));
   SSP_CUDA_TRY(ctx, ctx->p_md.ensure((size_t)(rows + 1) * 8));
   SSP_CUDA_TRY(ctx, ctx->p_flops.ensure(16));
-  SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->p_flops.p, 0, 16, ctx->stream));
   ctx->p_executed_flops = -1;
   ctx->p_executed_flops_f32 = -1;
-  bool counted = false;
-  if (max_p1 > 0) {
-    NvtxRange range("kernel 3 (polygon compare)");
-    dim3 grid((unsigned)n_pairs, (unsigned)((max_p1 + PC_THREADS - 1) / PC_THREADS));
-    SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    const PolyPair* dp = ctx->p_pairs.as<PolyPair>();
-    int* am = ctx->p_argmin.as<int>();
-    double* md = ctx->p_mindist.as<double>();
-    const bool ms = (shift_mode == SSP_SHIFT_MIN_OVER_SHIFTS);
-    // default: the compacted-pruning kernel (round 2: 85 ms against 108 ms at the 15 000 cap, bit-equal);
-    // SSP_B200_POLY_COMPARE=legacy selects round 1's per-lane pruning for A/B runs
-    // which exact kernel: the single-precision screen costs the same ~1.1 ps per cell whatever the data
-    // (52 ms at the 15 000 cap against 69 ms), the first-group queue less where real matches tighten
-    // the rows' thresholds early (2.6 against 3.5 ms at C4, 3.4 k polygons per image)
-    const char* env = getenv("SSP_B200_POLY_COMPARE");
-    const bool legacy = env && env[0] == 'l';
-    const bool screen_fits = max_p2 < PS_MAX_COLS;
-    const bool queue = (env && env[0] == 'q') || !screen_fits ||
-                       (!(env && env[0] == 's') && max_p2 < PS_AUTO_MIN_COLS);
-    if (precision == SSP_PRECISION_FP64) {
-      if (ms) poly_compare_f64_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
-      else if (legacy) poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
-      else if (queue) {
-        poly_compare_f64_queue_kernel<<<grid, PC_THREADS, 0, ctx->stream>>>(
-            dp, am, md, ctx->p_flops.as<unsigned long long>());
-        counted = true;
+  // Which exact form.  SSP_B200_POLY_COMPARE = tensor | screen | queue | legacy picks one (A/B runs and tests);
+  // by default the TF32 tensor-core screen with FP64 evaluation of its candidates (polygon_tensor.cuh), which
+  // hands the call over to the CUDA-core kernels when it must (features beyond the float range, candidate
+  // pool overflow, a screen value further from FP64 than its bound).  Of the CUDA-core kernels the
+  // single-precision screen costs the same ~1.1 ps per cell whatever the data (52 ms at the 15 000 cap
+  // against 69 ms), the first-group queue less where real matches tighten the rows' thresholds early (2.6
+  // against 3.5 ms at C4, 3.4 k polygons per image).
+  const char* env = getenv("SSP_B200_POLY_COMPARE");
+  const char kind = env ? env[0] : 0;
+  const bool ms = (shift_mode == SSP_SHIFT_MIN_OVER_SHIFTS);
+  bool tensor = precision == SSP_PRECISION_FP64 && !ms && max_p1 > 0 && max_p2 > 0 && (kind == 0 || kind == 't');
+  ctx->t_used = 0;
+  ctx->t_fallback_flags = 0;
+  ctx->t_candidates = -1;
+  ctx->t_worst_coef = -1.0;
+  long long total = 0;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    bool counted = false;
+    ctx->p_launches = 0;
+    SSP_CUDA_TRY(ctx, cudaMemsetAsync(ctx->p_flops.p, 0, 16, ctx->stream));
+    if (max_p1 > 0 && tensor) {
+      NvtxRange range("kernel 3 (polygon compare, tensor-core screen)");
+      SSP_CUDA_TRY(ctx, launch_poly_compare_tensor(ctx, pp, pairs, n_pairs, rows));
+      counted = true;
+    } else if (max_p1 > 0) {
+      NvtxRange range("kernel 3 (polygon compare)");
+      dim3 grid((unsigned)n_pairs, (unsigned)((max_p1 + PC_THREADS - 1) / PC_THREADS));
+      SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+      const PolyPair* dp = ctx->p_pairs.as<PolyPair>();
+      int* am = ctx->p_argmin.as<int>();
+      double* md = ctx->p_mindist.as<double>();
+      const bool legacy = kind == 'l';
+      const bool screen_fits = max_p2 < PS_MAX_COLS;
+      const bool queue = kind == 'q' || !screen_fits || (kind != 's' && max_p2 < PS_AUTO_MIN_COLS);
+      if (precision == SSP_PRECISION_FP64) {
+        if (ms) poly_compare_f64_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+        else if (legacy) poly_compare_f64_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+        else if (queue) {
+          poly_compare_f64_queue_kernel<<<grid, PC_THREADS, 0, ctx->stream>>>(
+              dp, am, md, ctx->p_flops.as<unsigned long long>());
+          counted = true;
+        } else {
+          dim3 grid_s((unsigned)n_pairs, (unsigned)((max_p1 + PS_CTA_ROWS - 1) / PS_CTA_ROWS));
+          poly_compare_f64_screen_kernel<<<grid_s, PC_THREADS, 0, ctx->stream>>>(
+              dp, am, md, ctx->p_flops.as<unsigned long long>());
+          counted = true;
+        }
       } else {
-        dim3 grid_s((unsigned)n_pairs, (unsigned)((max_p1 + PS_CTA_ROWS - 1) / PS_CTA_ROWS));
-        poly_compare_f64_screen_kernel<<<grid_s, PC_THREADS, 0, ctx->stream>>>(
-            dp, am, md, ctx->p_flops.as<unsigned long long>());
-        counted = true;
+        if (ms) poly_compare_f32_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+        else poly_compare_f32_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
       }
-    } else {
-      if (ms) poly_compare_f32_kernel<true><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
-      else poly_compare_f32_kernel<false><<<grid, PC_THREADS, 0, ctx->stream>>>(dp, am, md);
+      SSP_CUDA_TRY(ctx, cudaGetLastError());
+      SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+      ctx->p_launches += 1;
     }
-    SSP_CUDA_TRY(ctx, cudaGetLastError());
-    SSP_CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    ctx->p_launches += 1;
+    {
+      NvtxRange range("finalize (count, scan, compact)");
+      poly_count_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
+          ctx->p_pairs.as<PolyPair>(), ctx->p_mindist.as<double>(), threshold, ctx->p_counts.as<int>());
+      SSP_CUDA_TRY(ctx, cudaGetLastError());
+      scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->p_counts.as<int>(), n_pairs,
+                                                      ctx->p_offsets.as<long long>());
+      SSP_CUDA_TRY(ctx, cudaGetLastError());
+      poly_compact_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
+          ctx->p_pairs.as<PolyPair>(), ctx->p_argmin.as<int>(), ctx->p_mindist.as<double>(), threshold,
+          ctx->p_offsets.as<long long>(), ctx->p_m1.as<int>(), ctx->p_m2.as<int>(),
+          ctx->p_md.as<double>());
+      SSP_CUDA_TRY(ctx, cudaGetLastError());
+      ctx->p_launches += 3;
+    }
+    unsigned long long flops[2] = {0, 0};
+    int t_flags = 0;
+    unsigned t_worst = 0;
+    std::vector<unsigned> t_counts;
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_match_offsets.data(), ctx->p_offsets.p,
+                                      ((size_t)n_pairs + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    SSP_CUDA_TRY(ctx, cudaMemcpyAsync(flops, ctx->p_flops.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    if (tensor && max_p1 > 0) {
+      t_counts.assign((size_t)ctx->t_grid, 0u);
+      SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&t_flags, ctx->t_flags.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+      SSP_CUDA_TRY(ctx, cudaMemcpyAsync(&t_worst, ctx->t_f.as<unsigned>() + ctx->t_stats_off, 4,
+                                        cudaMemcpyDeviceToHost, ctx->stream));
+      SSP_CUDA_TRY(ctx, cudaMemcpyAsync(t_counts.data(), ctx->t_counts.p, t_counts.size() * 4,
+                                        cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (tensor && max_p1 > 0) {
+      float worst;
+      memcpy(&worst, &t_worst, 4);
+      ctx->t_worst_coef = (double)worst;
+      ctx->t_candidates = 0;
+      for (unsigned c : t_counts) ctx->t_candidates += c;
+      if (t_flags != 0) {          // hand the call over to the CUDA-core kernels
+        ctx->t_fallback_flags = t_flags;
+        tensor = false;
+        continue;
+      }
+      ctx->t_used = 1;
+    }
+    total = ctx->p_match_offsets[(size_t)n_pairs];
+    if (counted) {
+      ctx->p_executed_flops = (long long)(flops[0] + flops[1]);
+      ctx->p_executed_flops_f32 = (long long)flops[1];
+    }
+    if (max_p1 > 0) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->p_main_ms, ctx->ev0, ctx->ev1));
+    break;
   }
-  {
-    NvtxRange range("finalize (count, scan, compact)");
-    poly_count_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
-        ctx->p_pairs.as<PolyPair>(), ctx->p_mindist.as<double>(), threshold, ctx->p_counts.as<int>());
-    SSP_CUDA_TRY(ctx, cudaGetLastError());
-    scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->p_counts.as<int>(), n_pairs,
-                                                    ctx->p_offsets.as<long long>());
-    SSP_CUDA_TRY(ctx, cudaGetLastError());
-    poly_compact_kernel<<<n_pairs, PF_THREADS, 0, ctx->stream>>>(
-        ctx->p_pairs.as<PolyPair>(), ctx->p_argmin.as<int>(), ctx->p_mindist.as<double>(), threshold,
-        ctx->p_offsets.as<long long>(), ctx->p_m1.as<int>(), ctx->p_m2.as<int>(),
-        ctx->p_md.as<double>());
-    SSP_CUDA_TRY(ctx, cudaGetLastError());
-    ctx->p_launches += 3;
-  }
-  unsigned long long flops[2] = {0, 0};
-  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p_match_offsets.data(), ctx->p_offsets.p,
-                                    ((size_t)n_pairs + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(flops, ctx->p_flops.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
-  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  const long long total = ctx->p_match_offsets[(size_t)n_pairs];
-  if (counted) {
-    ctx->p_executed_flops = (long long)(flops[0] + flops[1]);
-    ctx->p_executed_flops_f32 = (long long)flops[1];
-  }
-  if (max_p1 > 0) SSP_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->p_main_ms, ctx->ev0, ctx->ev1));
   for (int p = 0; p <= n_pairs; ++p) match_offsets[p] = ctx->p_match_offsets[(size_t)p];
   ctx->p_n_matches = total;
   return SSP_OK;
@@ -1681,6 +1847,17 @@ int ssp_polygon_fetch_rowmin(ssp_ctx* ctx, int32_t* argmin, double* mindist, int
   if (argmin) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(argmin, ctx->p_argmin.p, (size_t)n * 4, kind, ctx->stream));
   if (mindist) SSP_CUDA_TRY(ctx, cudaMemcpyAsync(mindist, ctx->p_mindist.p, (size_t)n * 8, kind, ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+int ssp_polygon_last_screen_stats(ssp_ctx* ctx, int* used_tensor, int* fallback_flags, int64_t* candidates,
+                                  double* worst_error_coef, double* bound_coef) {
+  if (!ctx || !used_tensor || !fallback_flags || !candidates || !worst_error_coef || !bound_coef) return SSP_ERR_INVALID;
+  *used_tensor = ctx->t_used;
+  *fallback_flags = ctx->t_fallback_flags;
+  *candidates = ctx->t_candidates;
+  *worst_error_coef = ctx->t_worst_coef;
+  *bound_coef = (double)ssp::PT_ERR_COEF;
   return SSP_OK;
 }
 

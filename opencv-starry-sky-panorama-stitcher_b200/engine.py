@@ -436,7 +436,15 @@ class Engine:
         self._check(self._lib.ssp_polygon_last_executed_flops(self._ctx, ctypes.byref(fl)))
         f64, f32 = ctypes.c_int64(), ctypes.c_int64()
         self._check(self._lib.ssp_polygon_last_executed_flops_by_precision(self._ctx, ctypes.byref(f64), ctypes.byref(f32)))
+        used, fb, cand = ctypes.c_int(), ctypes.c_int(), ctypes.c_int64()
+        worst, bound = ctypes.c_double(), ctypes.c_double()
+        self._check(self._lib.ssp_polygon_last_screen_stats(self._ctx, ctypes.byref(used), ctypes.byref(fb), ctypes.byref(cand),
+                                                            ctypes.byref(worst), ctypes.byref(bound)))
         return {"launches": n.value, "main_kernel_ms": ms.value, "evaluations": ev.value,
+                "tensor_screen": {"used": bool(used.value), "fallback_flags": fb.value,
+                                  "candidates": cand.value if cand.value >= 0 else None,
+                                  "worst_error_coef": worst.value if worst.value >= 0 else None,
+                                  "bound_coef": bound.value},
                 "executed_flops": fl.value if fl.value >= 0 else None,
                 "executed_flops_fp64": f64.value if f64.value >= 0 else None,
                 "executed_flops_fp32": f32.value if f32.value >= 0 else None}

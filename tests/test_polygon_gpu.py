@@ -363,13 +363,18 @@ def test_queue_compare_kernel_equals_per_lane_pruning_and_numpy(engine, monkeypa
     engine.polygon_upload_features(0, f1)
     engine.polygon_upload_features(1, f2)
     out = {}
-    for kind in ("legacy", "queue", "screen"):
+    for kind in ("legacy", "queue", "tensor", "screen"):
         monkeypatch.setenv("SSP_B200_POLY_COMPARE", kind)
         out[kind] = engine.polygon_match_pairs([(0, 1)], threshold=10.0, return_rowmin=True)
         st = engine.polygon_last_stats()
         assert (st["executed_flops"] is None) == (kind == "legacy")
+        ts = st["tensor_screen"]
+        assert ts["used"] == (kind == "tensor") and ts["fallback_flags"] == 0
+        if kind == "tensor":
+            # every row has at least one candidate; the screen stays far inside its error bound
+            assert rows <= ts["candidates"] <= 24 * rows + 8192 and ts["worst_error_coef"] < ts["bound_coef"] / 4
     m = PolygonOracle.compare(f1, f2)
-    for kind in ("queue", "screen"):
+    for kind in ("queue", "screen", "tensor"):
         np.testing.assert_array_equal(out[kind].argmin, out["legacy"].argmin)
         np.testing.assert_array_equal(out[kind].mindist, out["legacy"].mindist)
         np.testing.assert_array_equal(out[kind].argmin, np.argmin(m, axis=1))
@@ -425,10 +430,18 @@ def test_compare_float_screens_never_drop_a_column_they_must_keep(engine, monkey
     engine.polygon_upload_features(0, f1)
     engine.polygon_upload_features(1, f2)
     out = {}
-    for kind in ("legacy", "queue", "screen"):
+    for kind in ("legacy", "queue", "screen", "tensor"):
         monkeypatch.setenv("SSP_B200_POLY_COMPARE", kind)
         out[kind] = engine.polygon_match_pairs([(0, 1)], threshold=1e300, return_rowmin=True)
-    for kind in ("queue", "screen"):
+    ts = engine.polygon_last_stats()["tensor_screen"]
+    # features beyond the float range (also +-inf) make the tensor-core screen hand the call over
+    want_flags = 2 if case in ("scale_1e20", "scale_1e100", "nan_and_inf_features") else None
+    if want_flags is not None:
+        assert not ts["used"] and ts["fallback_flags"] & want_flags
+    else:
+        assert ts["used"] or ts["fallback_flags"] == 4, ts      # 4: candidate pool overflow (every cell a candidate)
+        assert ts["worst_error_coef"] is None or ts["worst_error_coef"] < ts["bound_coef"] / 4 or not ts["used"]
+    for kind in ("queue", "screen", "tensor"):
         np.testing.assert_array_equal(out[kind].argmin, out["legacy"].argmin)
         np.testing.assert_array_equal(out[kind].mindist, out["legacy"].mindist)
     if case != "nan_and_inf_features":     # numpy's argmin stops at a NaN; the kernels skip it like the per-lane one
