@@ -351,6 +351,14 @@ def ncu_traffic(kernel):
         return None, None
 
 
+def measured_bf16_burst():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["bf16_tflops"])
+    except Exception:
+        return 1650.0
+
+
 def measured_hbm_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -756,20 +764,37 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
         peak_def = (f"executed flops / (FP64 flops / ({n_sm} SMs x {f64_rate:.1f} unfused DSUB+DMUL+DADD per clk per SM, measured: "
                     f"profiles/pipe_microbench_r01.json) + single-precision screen flops / ({n_sm} SMs x {f32_rate:.0f} ops/clk/SM x {flop_per_op:.3f} flop "
                     f"per op)) at {sm_max_mhz:g} MHz: the two arithmetic pipes one after the other")
+    ts = st.get("tensor_screen") or {}
+    if ts.get("used"):
+        # default parity compare: every cell goes through a K = 64 TF32 contraction on the tensor cores
+        # (operands split in two TF32 halves, |b|^2 folded in), FP64 only for the candidates
+        flop_per_cell = 128.0
+        tc_flops = evals_local * flop_per_cell
+        achieved = tc_flops / (main_ms / 1e3) / 1e12 if main_ms > 0 else None
+        peak = n_sm * 4096.0 * sm_hz / 1e12
+        kernel_name = "poly_screen_tcgen05_kernel"
+        split = {"tf32_tensor_flops": tc_flops, "fp64_flops": executed_local, "candidates": ts.get("candidates"),
+                 "screen_worst_error_coef": ts.get("worst_error_coef"), "screen_bound_coef": ts.get("bound_coef")}
+        peak_def = (f"{n_sm} SMs x 4096 flop/clk/SM (tcgen05 kind::tf32 M128 N256 K8 = 128 clk) x {sm_max_mhz:g} MHz; achieved counts the "
+                    f"K = 64 contraction the screen executes per cell (128 flop), over the whole compare (operand banks + screen + FP64 "
+                    f"evaluation of the candidates); cuBLAS bf16 burst / 2 on this pool = {measured_bf16_burst() / 2:.0f} TFLOP/s (power-capped proxy)")
     roofline = {
-        "bound": "fp32-pipe" if fp32 else "fp64-pipe", "kernel": kernel_name,
+        "bound": "fp32-pipe" if fp32 else ("tensor" if ts.get("used") else "fp64-pipe"), "kernel": kernel_name,
         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak and achieved else None,
         "achieved_counts": "flops executed by the kernel (device counter); pruned terms are not counted",
         "executed_fraction_of_algorithmic_flops": (executed_local / (evals_local * FLOP_PER_EVALUATION)) if executed_local and evals_local else None,
         "algorithmic_tflops_equivalent": algorithmic, "executed_by_precision": split,
         "peak_definition": peak_def,
-        "binding_unit": None if fp32 else "ncu (profiles/INDEX.md, kernel 3): the screen kernel is bound by the FP32 pipe, the queue kernel by the shared-memory data pipe and instruction issue",
+        "binding_unit": None if fp32 else ("tensor pipe + epilogue issue (profiles/INDEX.md, kernel 3)" if ts.get("used") else
+                                           "ncu (profiles/INDEX.md, kernel 3): the screen kernel is bound by the FP32 pipe, the queue kernel by the shared-memory data pipe and instruction issue"),
+        "tensor_screen": ts or None,
         "flop_per_evaluation": FLOP_PER_EVALUATION, "kernel_ms_per_launch": main_ms,
         "evaluations_per_launch": evals_local, "evaluations_per_s": evals_local / (main_ms / 1e3) if main_ms > 0 else None,
         "traffic": None,
     }
     if not measured and not fp32 and world == 1:   # the committed ncu capture is of exactly this launch
-        roofline["traffic"], roofline["traffic_source"] = ncu_traffic("poly_compare_f64_kernel")
+        roofline["traffic"], roofline["traffic_source"] = ncu_traffic(
+            "poly_screen_tcgen05_kernel" if ts.get("used") else "poly_compare_f64_kernel")
     rec = None
     if rank == 0:
         rec = {

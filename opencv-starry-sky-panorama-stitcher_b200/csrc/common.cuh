@@ -268,7 +268,10 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
 // instead of burning issue slots of the SM sub-partition it shares with two epilogue warps (ncu:
 // the clock64-per-iteration loop this replaces was 22 % of all issued instructions).  Watchdog by
 // spin count: a protocol bug must surface as a CUDA error, not as a hung GPU.
-constexpr uint32_t TC_WAIT_HINT_NS = 20000;
+#ifndef TC_WAIT_HINT_NS
+#define TC_WAIT_HINT_NS 20000
+#endif
+template <uint32_t HINT_NS>
 __device__ __forceinline__ bool tc_try_wait_hint(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
@@ -278,16 +281,18 @@ __device__ __forceinline__ bool tc_try_wait_hint(uint64_t* bar, uint32_t parity)
       " selp.u32 %0, 1, 0, p;\n"
       "}\n"
       : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity), "r"(TC_WAIT_HINT_NS)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(HINT_NS)
       : "memory");
   return ok != 0;
 }
-__device__ __forceinline__ void tc_wait(uint64_t* bar, uint32_t parity) {
+template <uint32_t HINT_NS>
+__device__ __forceinline__ void tc_wait_hint(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
-  while (!tc_try_wait_hint(bar, parity)) {
+  while (!tc_try_wait_hint<HINT_NS>(bar, parity)) {
     if (++spins > 100000000u) __trap();
   }
 }
+__device__ __forceinline__ void tc_wait(uint64_t* bar, uint32_t parity) { tc_wait_hint<TC_WAIT_HINT_NS>(bar, parity); }
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() {

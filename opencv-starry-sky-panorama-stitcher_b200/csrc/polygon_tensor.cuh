@@ -52,6 +52,10 @@ constexpr int PT_THREADS = 256 + 64;          // 8 epilogue warps, producer, MMA
 constexpr int PT_PAD = 256;                   // rows of every operand bank are padded to this
 constexpr int PT_TAIL_BYTES = 256 + 2 * 2 * PT_M * (int)sizeof(float) + 16;   // barriers, theta exchange [parity][half][row], counter
 constexpr size_t PT_SMEM_BYTES = (size_t)PT_A_BYTES + (size_t)PT_STAGES * PT_B_BYTES + PT_TAIL_BYTES;
+#ifndef PT_WAIT_HINT_NS
+#define PT_WAIT_HINT_NS 20000   // suspend-time hint of the mbarrier waits
+#endif
+__device__ __forceinline__ void pt_wait(uint64_t* bar, uint32_t parity) { tc_wait_hint<PT_WAIT_HINT_NS>(bar, parity); }
 constexpr float PT_ERR_COEF = 5e-4f;          // E = PT_ERR_COEF * F^2
 constexpr float PT_F_MAX = 1e15f;             // beyond this F^2 leaves the float range: no screen
 constexpr int PT_FLAG_SMEM = 1, PT_FLAG_RANGE = 2, PT_FLAG_OVERFLOW = 4, PT_FLAG_ERROR = 8;
@@ -289,7 +293,7 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
         const PtWork w = work[pt_find_work(work, n_work, tile)];
         const int r_tile = tile - w.tile_begin;
-        if (item > 0) tc_wait(a_empty, (item - 1) & 1u);
+        if (item > 0) pt_wait(a_empty, (item - 1) & 1u);
         mbar_arrive_expect_tx(a_full, PT_A_BYTES);
         tma_bulk_g2s(sA, w.a_exp + (size_t)r_tile * (PT_M * 128), PT_M * 128, a_full);
         tma_bulk_g2s(sA + PT_M * 128, w.a_exp + (size_t)w.a_rows_pad * 128 + (size_t)r_tile * (PT_M * 128),
@@ -298,7 +302,7 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
         for (int t = 0; t < n_t; ++t, ++g) {
           const uint32_t s = g % PT_STAGES;
           const uint32_t ph = (g / PT_STAGES) & 1u;
-          tc_wait(&b_empty[s], ph ^ 1u);
+          pt_wait(&b_empty[s], ph ^ 1u);
           mbar_arrive_expect_tx(&b_full[s], PT_B_BYTES);
           uint8_t* dst = sB + (size_t)s * PT_B_BYTES;
           tma_bulk_g2s(dst, w.b_exp + (size_t)t * (PT_N * 128), PT_N * 128, &b_full[s]);
@@ -315,13 +319,13 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++item) {
         const PtWork w = work[pt_find_work(work, n_work, tile)];
         const int n_t = (w.p2 + PT_N - 1) / PT_N;
-        tc_wait(a_full, item & 1u);
+        pt_wait(a_full, item & 1u);
         for (int t = 0; t < n_t; ++t, ++g) {
           const uint32_t s = g % PT_STAGES;
           const uint32_t ph = (g / PT_STAGES) & 1u;
           const uint32_t buf = g % PT_ACC;
-          tc_wait(&b_full[s], ph);
-          tc_wait(&acc_empty[buf], ((g / PT_ACC) & 1u) ^ 1u);
+          pt_wait(&b_full[s], ph);
+          pt_wait(&acc_empty[buf], ((g / PT_ACC) & 1u) ^ 1u);
           tc_fence_after();
           const uint32_t b_addr = smem_u32(sB + (size_t)s * PT_B_BYTES);
 #pragma unroll
@@ -356,7 +360,7 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
         const uint32_t buf = g % PT_ACC;
         __syncwarp();                        // the rare path of the previous tile diverges
         theta = fminf(theta, *peer_slot);
-        tc_wait(&acc_full[buf], (g / PT_ACC) & 1u);
+        pt_wait(&acc_full[buf], (g / PT_ACC) & 1u);
         tc_fence_after();
         const uint32_t taddr = taddr0 + buf * PT_N;
         uint32_t v[PT_HALF];
