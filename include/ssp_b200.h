@@ -299,6 +299,24 @@ int ssp_star_brightness(ssp_ctx* ctx, const uint8_t* gray, int h, int w, const i
                         int64_t n, const int32_t* disc_dxdy, int n_disc, int top_k,
                         int32_t* brightness, int mem_kind);
 
+/* ssp_star_brightness without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, same results; the device-side staging (image,
+ * centres, disc offsets, result) lives in one file-scope device array of
+ * SSP_BRIGHTNESS_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until the process
+ * exits.  The call itself performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ * Limits: h * w <= SSP_BRIGHTNESS_STATIC_MAX_PIXELS (2 Mi pixels; the reference's 894 x 1342 work image is
+ * 1.2 M), n <= SSP_BRIGHTNESS_STATIC_MAX_STARS; beyond them SSP_ERR_CAPACITY with a message, nothing
+ * launched.  ALL calls on one GPU (from any context or thread) share the array: it keeps the last call's
+ * contents, nothing in it needs clearing between calls, and two calls that overlap on the GPU race -- run
+ * them one after the other (each call returns after its stream has drained). */
+#define SSP_BRIGHTNESS_STATIC_MAX_PIXELS (2 * 1024 * 1024)
+#define SSP_BRIGHTNESS_STATIC_MAX_STARS 16384
+#define SSP_BRIGHTNESS_STATIC_SCRATCH_BYTES (SSP_BRIGHTNESS_STATIC_MAX_PIXELS + SSP_BRIGHTNESS_STATIC_MAX_STARS * 12 + 4096)
+int ssp_star_brightness_static(ssp_ctx* ctx, const uint8_t* gray, int h, int w, const int32_t* center_xy,
+                               int64_t n, const int32_t* disc_dxdy, int n_disc, int top_k,
+                               int32_t* brightness, int mem_kind);
+
 #ifdef __cplusplus
 }
 #endif

@@ -80,6 +80,8 @@ PROTOTYPES = {
                                           _c.POINTER(_c.c_int64), _c.POINTER(_c.c_void_p)]),
     "ssp_star_brightness": (_c.c_int, [_ctx_p, _u8p, _c.c_int, _c.c_int, _i32p, _c.c_int64, _i32p,
                                        _c.c_int, _c.c_int, _i32p, _c.c_int]),
+    "ssp_star_brightness_static": (_c.c_int, [_ctx_p, _u8p, _c.c_int, _c.c_int, _i32p, _c.c_int64, _i32p,
+                                              _c.c_int, _c.c_int, _i32p, _c.c_int]),
 }
 
 

@@ -7,6 +7,8 @@
 // disc in registers, then top_k rounds of (lane max -> warp max -> retire one instance).
 #include "common.cuh"
 
+#include <mutex>
+
 namespace ssp {
 
 constexpr int SB_MAX_PER_LANE = 16;  // supports discs up to 512 pixels (radius 10 -> 317)
@@ -90,6 +92,93 @@ extern "C" int ssp_star_brightness(ssp_ctx* ctx, const uint8_t* gray, int h, int
   SSP_CUDA_TRY(ctx, cudaGetLastError());
   SSP_CUDA_TRY(ctx, cudaMemcpyAsync(brightness, ctx->b_out.p, (size_t)n * 4,
                                     from_device_kind(mem_kind), ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return SSP_OK;
+}
+
+// ---- the same kernel without any allocation ---------------------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it): the device-side staging of ssp_star_brightness -- image, centres, disc offsets, result --
+// lives in ONE file-scope device array of a fixed size instead of the context's growable buffers.  Every GPU
+// that loads the library holds these SSP_BRIGHTNESS_STATIC_SCRATCH_BYTES (2.2 MiB) until the process exits.
+// In host code the array's NAME is a host-side stand-in, not a device address: the address is asked for
+// once per device (cudaGetSymbolAddress with that device current) and only that pointer goes to the kernel.
+namespace ssp {
+
+constexpr size_t SBS_IMG_BYTES = (size_t)SSP_BRIGHTNESS_STATIC_MAX_PIXELS;            // uint8 grey image
+constexpr size_t SBS_XY_BYTES = (size_t)SSP_BRIGHTNESS_STATIC_MAX_STARS * 8;          // int32 (n, 2)
+constexpr size_t SBS_DISC_BYTES = (size_t)32 * SB_MAX_PER_LANE * 8;                   // int32 (n_disc, 2)
+constexpr size_t SBS_OUT_BYTES = (size_t)SSP_BRIGHTNESS_STATIC_MAX_STARS * 4;         // int32 (n)
+constexpr size_t SBS_XY_OFF = SBS_IMG_BYTES;
+constexpr size_t SBS_DISC_OFF = SBS_XY_OFF + SBS_XY_BYTES;
+constexpr size_t SBS_OUT_OFF = SBS_DISC_OFF + SBS_DISC_BYTES;
+constexpr size_t SBS_TOTAL = SBS_OUT_OFF + SBS_OUT_BYTES;
+static_assert(SBS_TOTAL == SSP_BRIGHTNESS_STATIC_SCRATCH_BYTES, "header and scratch layout disagree");
+static_assert(SBS_XY_OFF % 256 == 0 && SBS_DISC_OFF % 256 == 0 && SBS_OUT_OFF % 256 == 0, "256-byte aligned parts");
+
+static __device__ __align__(256) unsigned char sbs_scratch[SBS_TOTAL];
+
+constexpr int SBS_MAX_DEVICES = 64;
+static std::mutex sbs_mutex;
+static unsigned char* sbs_device_ptr[SBS_MAX_DEVICES];   // device address of sbs_scratch, per device; nullptr = not asked yet
+
+// the calling thread's current device must be `device`
+static cudaError_t sbs_scratch_address(int device, unsigned char** out) {
+  std::lock_guard<std::mutex> lock(sbs_mutex);
+  if (sbs_device_ptr[device] == nullptr) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, sbs_scratch);
+    if (e != cudaSuccess) return e;
+    sbs_device_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = sbs_device_ptr[device];
+  return cudaSuccess;
+}
+
+}  // namespace ssp
+
+extern "C" int ssp_star_brightness_static(ssp_ctx* ctx, const uint8_t* gray, int h, int w,
+                                          const int32_t* center_xy, int64_t n, const int32_t* disc_dxdy,
+                                          int n_disc, int top_k, int32_t* brightness, int mem_kind) {
+  using namespace ssp;
+  if (!ctx) return SSP_ERR_INVALID;
+  if (int rc = use_device(ctx)) return rc;
+  SSP_REQUIRE(ctx, h > 0 && w > 0 && gray != nullptr, SSP_ERR_INVALID,
+              "ssp_star_brightness_static: bad image");
+  SSP_REQUIRE(ctx, n >= 0 && (n == 0 || (center_xy != nullptr && brightness != nullptr)),
+              SSP_ERR_INVALID, "ssp_star_brightness_static: bad star arrays");
+  SSP_REQUIRE(ctx, n_disc > 0 && n_disc <= 32 * SB_MAX_PER_LANE && disc_dxdy != nullptr,
+              SSP_ERR_INVALID, "ssp_star_brightness_static: disc must have 1..%d pixels",
+              32 * SB_MAX_PER_LANE);
+  SSP_REQUIRE(ctx, top_k > 0 && top_k <= n_disc, SSP_ERR_INVALID, "ssp_star_brightness_static: bad top_k");
+  SSP_REQUIRE(ctx, (long long)h * w <= (long long)SSP_BRIGHTNESS_STATIC_MAX_PIXELS, SSP_ERR_CAPACITY,
+              "ssp_star_brightness_static: image of %d x %d pixels exceeds the fixed scratch (%d pixels); "
+              "use ssp_star_brightness",
+              h, w, SSP_BRIGHTNESS_STATIC_MAX_PIXELS);
+  SSP_REQUIRE(ctx, n <= (int64_t)SSP_BRIGHTNESS_STATIC_MAX_STARS, SSP_ERR_CAPACITY,
+              "ssp_star_brightness_static: %lld stars exceed the fixed scratch (%d stars); use "
+              "ssp_star_brightness or split the call",
+              (long long)n, SSP_BRIGHTNESS_STATIC_MAX_STARS);
+  SSP_REQUIRE(ctx, ctx->device >= 0 && ctx->device < SBS_MAX_DEVICES, SSP_ERR_INVALID,
+              "ssp_star_brightness_static: device index %d beyond %d", ctx->device, SBS_MAX_DEVICES);
+  if (n == 0) return SSP_OK;
+  unsigned char* base = nullptr;
+  SSP_CUDA_TRY(ctx, sbs_scratch_address(ctx->device, &base));
+  unsigned char* d_img = base;
+  int* d_xy = reinterpret_cast<int*>(base + SBS_XY_OFF);
+  int* d_disc = reinterpret_cast<int*>(base + SBS_DISC_OFF);
+  int* d_out = reinterpret_cast<int*>(base + SBS_OUT_OFF);
+  // Nothing in the scratch has to start at zero: the kernel reads only what the three copies below have
+  // just written and writes out[0, n) completely; what earlier calls left beyond that is never read.
+  const cudaMemcpyKind in_kind = to_device_kind(mem_kind);
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(d_img, gray, (size_t)h * w, in_kind, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(d_xy, center_xy, (size_t)n * 8, in_kind, ctx->stream));
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(d_disc, disc_dxdy, (size_t)n_disc * 8, cudaMemcpyHostToDevice, ctx->stream));
+  const long long threads = n * 32;
+  star_brightness_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, ctx->stream>>>(
+      d_img, h, w, d_xy, n, d_disc, n_disc, top_k, d_out);
+  SSP_CUDA_TRY(ctx, cudaGetLastError());
+  SSP_CUDA_TRY(ctx, cudaMemcpyAsync(brightness, d_out, (size_t)n * 4, from_device_kind(mem_kind), ctx->stream));
   SSP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return SSP_OK;
 }

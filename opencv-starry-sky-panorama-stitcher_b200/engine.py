@@ -523,3 +523,18 @@ class Engine:
                                                   c.shape[0], _ptr(d), d.shape[0], int(top_k),
                                                   _ptr(out), N.MEM_HOST))
         return out
+
+    def star_brightness_static(self, gray: np.ndarray, centers_xy, disc_dxdy, top_k: int = 10):
+        """`star_brightness` through `ssp_star_brightness_static`: no allocation on the device, the staging
+        lives in a fixed device array (at most 2 Mi pixels and 16 384 stars per call; calls on one GPU must
+        not overlap).  No counterpart in the reference."""
+        g = np.ascontiguousarray(gray, dtype=np.uint8)
+        if g.ndim != 2:
+            raise ValueError("gray must be (h, w) uint8")
+        c = np.ascontiguousarray(np.asarray(centers_xy, dtype=np.int32).reshape(-1, 2))
+        d = np.ascontiguousarray(np.asarray(disc_dxdy, dtype=np.int32).reshape(-1, 2))
+        out = np.empty(c.shape[0], dtype=np.int32)
+        self._check(self._lib.ssp_star_brightness_static(self._ctx, _ptr(g), g.shape[0], g.shape[1], _ptr(c),
+                                                         c.shape[0], _ptr(d), d.shape[0], int(top_k),
+                                                         _ptr(out), N.MEM_HOST))
+        return out
