@@ -352,7 +352,8 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
       const int row = (tile - w.tile_begin) * PT_M + row_in_tile;
       const float f = fmaxf(*w.f_a, *w.f_b);
       if (!(f < PT_F_MAX) && tid == 0) atomicOr(flags, PT_FLAG_RANGE);
-      const float e3 = 3.0f * PT_ERR_COEF * f * f;
+      // (the floor keeps the columns of an all-zero bank candidates of each other -- exact ties -- instead of none)
+      const float e3 = fmaxf(3.0f * PT_ERR_COEF * f * f, 1e-30f);
       float theta = row < w.p1 ? INFINITY : -INFINITY;     // a padding row takes nothing
       volatile float* my_slot = share + (item & 1u) * (2 * PT_M) + wg * PT_M + row_in_tile;
       const volatile float* peer_slot = share + (item & 1u) * (2 * PT_M) + (wg ^ 1u) * PT_M + row_in_tile;

@@ -385,7 +385,8 @@ def test_queue_compare_kernel_equals_per_lane_pruning_and_numpy(engine, monkeypa
 
 @pytest.mark.parametrize("case", ["offset_1000", "differences_below_float_resolution", "scale_1e20",
                                   "scale_1e100", "first_group_sum_at_the_threshold",
-                                  "every_column_improves_every_row", "nan_and_inf_features"])
+                                  "every_column_improves_every_row", "nan_and_inf_features",
+                                  "all_zero_features"])
 def test_compare_float_screens_never_drop_a_column_they_must_keep(engine, monkeypatch, case):
     """The default kernel screens every cell in packed single precision (all 15 properties), the queue
     kernel its first property group, each with a margin that makes the float sum conservative
@@ -414,6 +415,9 @@ def test_compare_float_screens_never_drop_a_column_they_must_keep(engine, monkey
         f1 = base + rng.uniform(-1e-4, 1e-4, size=(rows, 15))
         f2 = np.repeat(base[None, :], cols, axis=0)
         f2[:, 3] += (cols - np.arange(cols)) * 1e-3       # distances fall monotonically with the column
+    elif case == "all_zero_features":
+        f1[:] = 0.0                                        # every column ties at distance 0: column 0 wins
+        f2[:] = 0.0
     elif case == "nan_and_inf_features":
         f2[5, 2] = np.nan
         f2[17, 11] = np.inf

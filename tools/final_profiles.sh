@@ -33,6 +33,8 @@ timeout 500 ncu --set full --clock-control none --import-source on -k regex:hamm
 timeout 400 ncu --metrics gpu__time_duration.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed,smsp__inst_executed.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_sector_hit_rate.pct,sm__cycles_elapsed.avg \
   --clock-control none -k regex:hamming_tcgen05 -s 1 -c 1 --csv --log-file $OUT/reverse_launch.csv \
   python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-sub --mode crosscheck > $OUT/ncu_rev.log 2>&1
-timeout 500 ncu --set full --clock-control none --import-source on -k regex:poly_compare -c 1 -f -o $OUT/poly_compare \
+timeout 500 ncu --set full --clock-control none --import-source on -k regex:poly_screen_tcgen05 -c 1 -f -o $OUT/poly_tensor_screen \
   python bench.py --steps 1 --warmup 0 --no-cpu-baseline --workload c4cap > $OUT/ncu_f4.log 2>&1
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $OUT/launches_c4cap.csv \
+  python bench.py --steps 1 --warmup 1 --no-cpu-baseline --workload c4cap > $OUT/ncu_l5.log 2>&1
 ls -la $OUT
