@@ -643,7 +643,38 @@ def fp_pipe_peaks():
         return {}
 
 
-def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
+def polygon_parity_in_run(eng, inp, pairs, measured, max_rows=1500):
+    """Kernel 3's answer for one sampled pair against numpy's on the SAME polygon banks (the banks the GPU
+    holds, fetched back): argmin and FP64 distance of every row (the first `max_rows` at the cap, where
+    numpy's (P1, P2, 5) temporaries would not fit) and the thresholded matches, bit for bit.  Where the
+    step measures its polygons (kernel 2), the first 300 candidates of the first image are also measured by
+    the CPU port and must agree (same polygons, same vertex order, features within 1e-9)."""
+    from oracle.polygon_oracle import PolygonOracle
+    a, b = pairs[len(pairs) // 2]
+    fa = eng.polygon_fetch(a, raw=False)
+    fb = eng.polygon_fetch(b, raw=False)
+    n = len(fa["feat"]) if len(fb["feat"]) <= 8000 else min(len(fa["feat"]), max_rows)
+    chk = eng.polygon_match_pairs([(a, b)], return_rowmin=True)
+    m = PolygonOracle.compare(fa["feat"][:n], fb["feat"])
+    same = bool(np.array_equal(chk.argmin[:n], np.argmin(m, axis=1)) and np.array_equal(chk.mindist[:n], m.min(axis=1)))
+    rows, cols, d = PolygonOracle.select(m, 0.1566)
+    r, c, dd = chk.pair(0)
+    keep = r < n
+    same = same and bool(np.array_equal(r[keep], rows) and np.array_equal(c[keep], cols) and np.array_equal(dd[keep], d))
+    detail = (f"pair ({a}, {b}): argmin, FP64 distance and thresholded matches of {n} rows x {len(fb['feat'])} columns, "
+              f"GPU (kernel {eng.polygon_last_stats()['tensor_screen']['used'] and 'poly_screen_tcgen05 + FP64 candidates' or 'CUDA-core'}) "
+              f"vs numpy on the same banks: exact")
+    if measured:
+        oracle = PolygonOracle((IMG_H, IMG_W, 3), FOCAL)
+        want = oracle.characteristics(inp["xy"][a], inp["br"][a], inp["cands"][a][:300])
+        nv = int(want["valid"].sum())
+        same = same and bool(np.array_equal(fa["star_idx"][:nv], want["star_idx"]) and
+                             np.allclose(fa["feat"][:nv], want["feat"], rtol=0, atol=1e-9))
+        detail += f"; kernel 2: the first {nv} polygons of image {a} vs the CPU port (vertex order equal, features within 1e-9)"
+    return same, detail
+
+
+def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32, parity=False):
     from ssp_b200.distributed import (shard_pairs_contiguous, broadcast_star_bank, measure_polygons_sharded,
                                       gather_polygon_matches_resident, _broadcaster)
     torch, world, rank, dev, dist = rt.torch, rt.world, rt.rank, rt.dev, rt.dist
@@ -811,6 +842,8 @@ def polygon_record(rt, wl, inp, pairs, steps, warmup, fp32):
                     "d2h_bytes_per_step": d2h, "steps": steps, "ms_per_step": e2e_s * 1e3},
             "gpu_launches": launches, "clocks": clk, "roofline": roofline,
         }
+    if rec is not None and parity and world == 1 and not fp32:
+        rec["parity_in_run"], rec["parity_in_run_detail"] = polygon_parity_in_run(eng, inp, pairs, measured)
     eng.close()
     return rec
 
@@ -964,7 +997,7 @@ def main():
             emit(run_polygon_reference(args, wl, inp, pairs))
             return 0
         rt = Runtime()
-        rec = polygon_record(rt, wl, inp, pairs, args.steps, args.warmup, args.fp32)
+        rec = polygon_record(rt, wl, inp, pairs, args.steps, args.warmup, args.fp32, parity=bool(cpu_pairs))
         if rank == 0:
             if cpu_pairs:
                 ref_args = argparse.Namespace(**{**vars(args), "steps": 2, "warmup": 0})
@@ -1020,7 +1053,7 @@ def main():
                 pp = synth.all_pairs(wp["n_images"])
 
                 def poly(wp=wp, inp=inp, pp=pp):
-                    r = polygon_record(rt, wp, inp, pp, k, w, False)
+                    r = polygon_record(rt, wp, inp, pp, k, w, False, parity=bool(cpu_pairs))
                     if rank == 0 and cpu_pairs:
                         ref_args = argparse.Namespace(**{**vars(args), "steps": 2, "warmup": 0})
                         r["cpu_baseline"] = run_polygon_reference(ref_args, wp, inp, pp)["cpu_baseline"]
