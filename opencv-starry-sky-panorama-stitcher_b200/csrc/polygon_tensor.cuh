@@ -13,13 +13,13 @@
 // K halves: the layout of kernel 1's expanded descriptor bank), so kernel 1's machinery carries over: one
 // persistent CTA per SM, a TMA producer warp (row tile once per item, column tiles through a three-stage
 // ring), one thread issuing 8 x tcgen05.mma kind::tf32 (M128 N256 K8) per stage into one of two TMEM
-// accumulators, and eight epilogue warps, each thread owning one row and one 128-column half.
+// accumulators, and sixteen epilogue warps, each thread owning one row and one 64-column quarter.
 //
 // Epilogue.  A thread keeps theta = min over the columns it took of (D + 3E), E an upper bound of
 // abs(D - D_real) (below).  A column with D >= theta has dist^2 larger than that of a column already
 // taken by at least E, far more than FP64 rounding and sqrt ties can bridge: it is neither the row's minimum
 // nor a tie of it.  A column with D < theta is a CANDIDATE: (pair, row, column, D) goes to this CTA's
-// segment of a global pool.  The two threads of a row exchange theta through shared memory.  Expected
+// segment of a global pool.  The four threads of a row exchange theta through shared memory.  Expected
 // candidates per row: the records of a random sequence, ~ln(P2) + a few.
 //
 // Exact part.  poly_cand_eval_kernel evaluates every candidate with poly_dist2_f64<0> and takes the row
@@ -43,14 +43,20 @@ namespace ssp {
 constexpr int PT_M = 128;                     // rows per tile = TMEM lanes
 constexpr int PT_N = 256;                     // columns per stage = TMEM columns per accumulator
 constexpr int PT_ACC = 2;
-constexpr int PT_HALF = PT_N / 2;
+#ifndef PT_WGS
+#define PT_WGS 4                              // epilogue warpgroups: each drains PT_N / PT_WGS columns of every accumulator
+                                              // (4: 9.4 ms at the cap against 10.05 with 2 -- a warp held up on its candidate path
+                                              // delays the hand-back of half as many columns; 23 % more candidates)
+#endif
+constexpr int PT_HALF = PT_N / PT_WGS;        // columns of an accumulator per epilogue thread
+constexpr int PT_EPI_WARPS = 4 * PT_WGS;
 constexpr int PT_STAGES = 3;
 constexpr int PT_ROW_BYTES = 256;             // 64 floats
 constexpr int PT_A_BYTES = PT_M * PT_ROW_BYTES;
 constexpr int PT_B_BYTES = PT_N * PT_ROW_BYTES;
-constexpr int PT_THREADS = 256 + 64;          // 8 epilogue warps, producer, MMA issuer
+constexpr int PT_THREADS = 32 * PT_EPI_WARPS + 64;   // epilogue warps, producer, MMA issuer
 constexpr int PT_PAD = 256;                   // rows of every operand bank are padded to this
-constexpr int PT_TAIL_BYTES = 256 + 2 * 2 * PT_M * (int)sizeof(float) + 16;   // barriers, theta exchange [parity][half][row], counter
+constexpr int PT_TAIL_BYTES = 256 + PT_WGS * PT_M * (int)sizeof(float) + 16;   // barriers, theta exchange [warpgroup][row], counter
 constexpr size_t PT_SMEM_BYTES = (size_t)PT_A_BYTES + (size_t)PT_STAGES * PT_B_BYTES + PT_TAIL_BYTES;
 #ifndef PT_WAIT_HINT_NS
 #define PT_WAIT_HINT_NS 20000   // suspend-time hint of the mbarrier waits
@@ -246,8 +252,8 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
   uint64_t* acc_empty = acc_full + PT_ACC;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + PT_ACC);
   static_assert((2 + 2 * PT_STAGES + 2 * PT_ACC) * 8 + 4 <= 256, "barrier block overflows its 256 bytes");
-  float* share = reinterpret_cast<float*>(tail + 256);                                    // [2][2][128]
-  unsigned* cand_n = reinterpret_cast<unsigned*>(tail + 256 + 2 * 2 * PT_M * sizeof(float));
+  float* share = reinterpret_cast<float*>(tail + 256);                                    // [PT_WGS][128]
+  unsigned* cand_n = reinterpret_cast<unsigned*>(tail + 256 + PT_WGS * PT_M * sizeof(float));
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -269,13 +275,13 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
     }
     for (int b = 0; b < PT_ACC; ++b) {
       mbar_init(&acc_full[b], 1);
-      mbar_init(&acc_empty[b], 8);  // one arrive per epilogue warp
+      mbar_init(&acc_empty[b], PT_EPI_WARPS);  // one arrive per epilogue warp
     }
     fence_mbar_init();
     *cand_n = 0u;
   }
-  for (int i = tid; i < 2 * 2 * PT_M; i += PT_THREADS) share[i] = INFINITY;
-  if (warp == 9) {  // TMEM: all 512 columns (two accumulators of 256 FP32 columns)
+  for (int i = tid; i < PT_WGS * PT_M; i += PT_THREADS) share[i] = INFINITY;
+  if (warp == PT_EPI_WARPS + 1) {  // TMEM: all 512 columns (two accumulators of 256 FP32 columns)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot))
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -286,7 +292,7 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
   const uint32_t tmem_base = *tmem_slot;
   PtCand* seg = pool + (size_t)blockIdx.x * seg_cap;
 
-  if (warp == 8) {
+  if (warp == PT_EPI_WARPS) {
     // ===== TMA producer =====
     if (lane == 0) {
       uint32_t g = 0, item = 0;
@@ -311,7 +317,7 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
         }
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == PT_EPI_WARPS + 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
       uint32_t g = 0, item = 0;
@@ -355,37 +361,44 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
       // (the floor keeps the columns of an all-zero bank candidates of each other -- exact ties -- instead of none)
       const float e3 = fmaxf(3.0f * PT_ERR_COEF * f * f, 1e-30f);
       float theta = row < w.p1 ? INFINITY : -INFINITY;     // a padding row takes nothing
-      volatile float* my_slot = share + (item & 1u) * (2 * PT_M) + wg * PT_M + row_in_tile;
-      const volatile float* peer_slot = share + (item & 1u) * (2 * PT_M) + (wg ^ 1u) * PT_M + row_in_tile;
+      volatile float* row_slots = share + row_in_tile;   // [wg * PT_M]
+      volatile float* my_slot = row_slots + wg * PT_M;
       for (int t = 0; t < n_t; ++t, ++g) {
         const uint32_t buf = g % PT_ACC;
         __syncwarp();                        // the rare path of the previous tile diverges
-        theta = fminf(theta, *peer_slot);
+#pragma unroll
+        for (int o = 1; o < PT_WGS; ++o) theta = fminf(theta, row_slots[((wg + o) % PT_WGS) * PT_M]);
         pt_wait(&acc_full[buf], (g / PT_ACC) & 1u);
         tc_fence_after();
         const uint32_t taddr = taddr0 + buf * PT_N;
         uint32_t v[PT_HALF];
         pt_ld32<0>(taddr, v);
         pt_ld32<32>(taddr, v);
-        pt_ld32<64>(taddr, v);
-        pt_ld32<96>(taddr, v);
+        if constexpr (PT_HALF == 128) {
+          pt_ld32<64>(taddr, v);
+          pt_ld32<96>(taddr, v);
+        }
         pt_wait_ld32<0>(v);
         pt_wait_ld32<32>(v);
-        pt_wait_ld32<64>(v);
-        pt_wait_ld32<96>(v);
+        if constexpr (PT_HALF == 128) {
+          pt_wait_ld32<64>(v);
+          pt_wait_ld32<96>(v);
+        }
         tc_release(&acc_empty[buf], lane);   // the accumulator goes back as soon as it sits in registers
         const int col0 = t * PT_N + (int)wg * PT_HALF;
         pt_chunk<0>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
         pt_chunk<32>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
-        pt_chunk<64>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
-        pt_chunk<96>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
+        if constexpr (PT_HALF == 128) {
+          pt_chunk<64>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
+          pt_chunk<96>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
+        }
       }
-      // the slot of the NEXT item is reset before the two warpgroups meet, so that none of them reads a
-      // theta of another row there
-      share[((item + 1u) & 1u) * (2 * PT_M) + wg * PT_M + row_in_tile] = INFINITY;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      // every thread resets its slot between two meetings of the warpgroups, so that none of them reads a
+      // theta of the previous row there
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * PT_EPI_WARPS) : "memory");
+      *my_slot = INFINITY;
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * PT_EPI_WARPS) : "memory");
     }
-    asm volatile("bar.sync 1, 256;" ::: "memory");
     if (tid == 0) cand_counts[blockIdx.x] = min(*cand_n, seg_cap);
   }
 
