@@ -62,6 +62,9 @@ constexpr size_t PT_SMEM_BYTES = (size_t)PT_A_BYTES + (size_t)PT_STAGES * PT_B_B
 #define PT_WAIT_HINT_NS 20000   // suspend-time hint of the mbarrier waits
 #endif
 __device__ __forceinline__ void pt_wait(uint64_t* bar, uint32_t parity) { tc_wait_hint<PT_WAIT_HINT_NS>(bar, parity); }
+#ifndef PT_EXPERIMENT
+#define PT_EXPERIMENT 0   // probes (results are wrong): 1 = accumulators handed back unread (MMA + operand feed only), 2 = read but not examined
+#endif
 constexpr float PT_ERR_COEF = 5e-4f;          // E = PT_ERR_COEF * F^2
 constexpr float PT_F_MAX = 1e15f;             // beyond this F^2 leaves the float range: no screen
 constexpr int PT_FLAG_SMEM = 1, PT_FLAG_RANGE = 2, PT_FLAG_OVERFLOW = 4, PT_FLAG_ERROR = 8;
@@ -372,6 +375,7 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
         tc_fence_after();
         const uint32_t taddr = taddr0 + buf * PT_N;
         uint32_t v[PT_HALF];
+#if PT_EXPERIMENT != 1
         pt_ld32<0>(taddr, v);
         pt_ld32<32>(taddr, v);
         if constexpr (PT_HALF == 128) {
@@ -384,14 +388,19 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
           pt_wait_ld32<64>(v);
           pt_wait_ld32<96>(v);
         }
+#endif
         tc_release(&acc_empty[buf], lane);   // the accumulator goes back as soon as it sits in registers
         const int col0 = t * PT_N + (int)wg * PT_HALF;
+#if PT_EXPERIMENT == 0
         pt_chunk<0>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
         pt_chunk<32>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
         if constexpr (PT_HALF == 128) {
           pt_chunk<64>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
           pt_chunk<96>(v, theta, e3, w, row, col0, cand_n, seg, seg_cap, flags, my_slot);
         }
+#elif PT_EXPERIMENT == 2
+        if (__uint_as_float(v[0]) == 12345.678f && __uint_as_float(v[PT_HALF - 1]) == 1.0f) *my_slot = (float)col0;   // keeps the loads alive
+#endif
       }
       // every thread resets its slot between two meetings of the warpgroups, so that none of them reads a
       // theta of the previous row there
