@@ -71,12 +71,18 @@ constexpr int TC_M = 128;                    // query rows per tile = TMEM lanes
 // from shared memory and the A tile is re-read for half as much work.
 constexpr int TC_N = 256;                    // train rows per stage = TMEM columns per accumulator
 constexpr int TC_ACC = 2;                    // accumulators in flight (2 x 256 = all 512 TMEM columns)
-constexpr int TC_HALF = TC_N / 2;            // columns of an accumulator drained by one warpgroup
+#ifndef TC_WGS
+#define TC_WGS 2          // epilogue warpgroups: each drains TC_N / TC_WGS columns of every accumulator (2 or 4)
+#endif
+static_assert(TC_WGS == 2 || TC_WGS == 4, "two or four epilogue warpgroups");
+constexpr int TC_HALF = TC_N / TC_WGS;       // columns of an accumulator drained by one warpgroup
+constexpr int TC_NREG = TC_HALF / 2;         // packed registers (two s16 columns each) per thread and tile
+constexpr int TC_EPI_WARPS = 4 * TC_WGS;
 constexpr int TC_STAGES = 3;
 constexpr int TC_ROW_BYTES = 256;            // expanded row
 constexpr int TC_A_BYTES = TC_M * TC_ROW_BYTES;      // 32 KB
 constexpr int TC_B_BYTES = TC_N * TC_ROW_BYTES;      // 64 KB
-constexpr int TC_EPI_THREADS = 256;
+constexpr int TC_EPI_THREADS = 32 * TC_EPI_WARPS;
 constexpr int TC_THREADS = TC_EPI_THREADS + 64 + (TC_PROFILE ? 32 : 0);  // profile builds add an observer warp
 constexpr int TC_PAD = 256;                  // rows of every expanded image are padded to this
 constexpr uint32_t TC_KEY_SHIFT = 22;
@@ -84,7 +90,8 @@ constexpr uint32_t TC_KEY_IDX_MASK = (1u << TC_KEY_SHIFT) - 1u;
 constexpr uint32_t TC_KEY_NONE = 0xFFFFFFFFu;
 constexpr int TC_THR_NONE = -100000;         // "no k-th neighbour yet"
 // bytes after the operand stages: mbarriers + TMEM slot (256), best-2 merge slots, thresholds
-constexpr int TC_TAIL_BYTES = 256 + 2 * TC_M * (int)sizeof(uint2) + 2 * TC_M * (int)sizeof(uint16_t);
+constexpr int TC_MERGE_BYTES = (TC_WGS == 2 ? 2 : 1) * TC_M * (int)sizeof(uint2);   // [parity][row] / [row], see the end of tc_epilogue_item
+constexpr int TC_TAIL_BYTES = 256 + TC_MERGE_BYTES + TC_WGS * TC_M * (int)sizeof(uint16_t);
 
 struct TcWork {              // one directed image pair
   const uint8_t* q_exp;      // query image, -+64 encoding
@@ -222,6 +229,19 @@ __device__ __forceinline__ void tc_ld128_packed(uint32_t taddr, uint32_t (&v)[64
                : "r"(taddr)
                : "memory");
 }
+// the same for 64 consecutive columns = 32 registers (four epilogue warpgroups)
+__device__ __forceinline__ void tc_ld128_packed(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
 __device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[64]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;"
                : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31]), "+r"(v[32]), "+r"(v[33]), "+r"(v[34]), "+r"(v[35]), "+r"(v[36]), "+r"(v[37]), "+r"(v[38]), "+r"(v[39]), "+r"(v[40]), "+r"(v[41]), "+r"(v[42]), "+r"(v[43]), "+r"(v[44]), "+r"(v[45]), "+r"(v[46]), "+r"(v[47]), "+r"(v[48]), "+r"(v[49]), "+r"(v[50]), "+r"(v[51]), "+r"(v[52]), "+r"(v[53]), "+r"(v[54]), "+r"(v[55]), "+r"(v[56]), "+r"(v[57]), "+r"(v[58]), "+r"(v[59]), "+r"(v[60]), "+r"(v[61]), "+r"(v[62]), "+r"(v[63])
@@ -270,16 +290,16 @@ __device__ __forceinline__ uint32_t tc_key64(uint32_t p, uint32_t pos) {
 #endif
 template <int K>
 __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_t col_base, TcRow& r) {
-  uint32_t h[32], l[32];
+  uint32_t h[TC_NREG / 2], l[TC_NREG / 2];
 #pragma unroll
-  for (int i = 0; i < 32; ++i) {
-    const uint32_t k0 = tc_key64(p[2 * i], (uint32_t)(63 - 2 * i) * 0x10001u);
-    const uint32_t k1 = tc_key64(p[2 * i + 1], (uint32_t)(62 - 2 * i) * 0x10001u);
+  for (int i = 0; i < TC_NREG / 2; ++i) {
+    const uint32_t k0 = tc_key64(p[2 * i], (uint32_t)(TC_NREG - 1 - 2 * i) * 0x10001u);
+    const uint32_t k1 = tc_key64(p[2 * i + 1], (uint32_t)(TC_NREG - 2 - 2 * i) * 0x10001u);
     h[i] = __vmaxs2(k0, k1);
     if (K == 2) l[i] = __vmins2(k0, k1);
   }
 #pragma unroll
-  for (int n = 16; n >= 1; n >>= 1) {
+  for (int n = TC_NREG / 4; n >= 1; n >>= 1) {
 #pragma unroll
     for (int i = 0; i < n; ++i) {
       if (K == 2) l[i] = __vimax3_s16x2(__vmins2(h[2 * i], h[2 * i + 1]), l[2 * i], l[2 * i + 1]);
@@ -288,11 +308,11 @@ __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_
   }
   const int a = 2 * (int)(short)(h[0] & 0xFFFFu) + 1, b = 2 * ((int)h[0] >> 16);
   const int hi = max(a, b);
-  const uint32_t g1 = ((uint32_t)(r.pq - (hi >> 7)) << TC_KEY_SHIFT) + col_base + (127u - ((uint32_t)hi & 127u));
+  const uint32_t g1 = ((uint32_t)(r.pq - (hi >> 7)) << TC_KEY_SHIFT) + col_base + ((uint32_t)(TC_HALF - 1) - ((uint32_t)hi & 127u));
   if (K == 2) {
     const int c = 2 * (int)(short)(l[0] & 0xFFFFu) + 1, d = 2 * ((int)l[0] >> 16);
     const int lo = __vimax3_s32(min(a, b), c, d);
-    const uint32_t g2 = ((uint32_t)(r.pq - (lo >> 7)) << TC_KEY_SHIFT) + col_base + (127u - ((uint32_t)lo & 127u));
+    const uint32_t g2 = ((uint32_t)(r.pq - (lo >> 7)) << TC_KEY_SHIFT) + col_base + ((uint32_t)(TC_HALF - 1) - ((uint32_t)lo & 127u));
     r.m2 = min(min(r.m2, g2), max(r.m1, g1));   // g1 <= g2 and m1 <= m2
   }
   r.m1 = min(r.m1, g1);
@@ -300,7 +320,7 @@ __device__ __forceinline__ void tc_tile_full(uint32_t (&p)[TC_HALF / 2], uint32_
 }
 
 #ifndef TC_FULL_MIN_G
-#define TC_FULL_MIN_G 3   // flagged groups (of 8) from which the full-tile tournament is used
+#define TC_FULL_MIN_G (TC_WGS == 2 ? 3 : 2)   // flagged groups (of 8, or of 4) from which the full-tile tournament is used
 #endif
 constexpr int TC_GROUP = 16;   // columns per pass-1 group = 8 packed registers
 
@@ -363,6 +383,15 @@ __device__ __forceinline__ void tc_group_exact_packed(uint32_t (&q)[8], uint32_t
   if (kth != TC_KEY_NONE) tc_publish(r, kth);
 }
 
+// max over the group maxima of a tile and a packed threshold
+__device__ __forceinline__ uint32_t tc_all_max(const uint32_t (&gm)[TC_HALF / TC_GROUP], uint32_t thr) {
+#if TC_WGS == 2
+  return __vimax3_s16x2(__vimax3_s16x2(gm[0], gm[1], gm[2]), __vimax3_s16x2(gm[3], gm[4], gm[5]),
+                        __vimax3_s16x2(gm[6], gm[7], thr));
+#else
+  return __vimax3_s16x2(__vimax3_s16x2(gm[0], gm[1], gm[2]), gm[3], thr);
+#endif
+}
 // Row direction of one visit: `p` = this lane's 128 columns as packed s16 pairs (already loaded, the
 // accumulator already handed back).
 template <int K, bool MASKED>
@@ -391,8 +420,7 @@ __device__ __forceinline__ void tc_tile(uint32_t (&p)[TC_HALF / 2], uint32_t col
     const uint32_t* q = p + 8 * g;
     gm[g] = __vimax3_s16x2(__vimax3_s16x2(q[0], q[1], q[2]), __vimax3_s16x2(q[3], q[4], q[5]), __vmaxs2(q[6], q[7]));
   }
-  const uint32_t all = __vimax3_s16x2(__vimax3_s16x2(gm[0], gm[1], gm[2]), __vimax3_s16x2(gm[3], gm[4], gm[5]),
-                                      __vimax3_s16x2(gm[6], gm[7], thrp));
+  const uint32_t all = tc_all_max(gm, thrp);
 #if TC_EXPERIMENT == 2 || TC_EXPERIMENT == 3
   if (all == 0x12345678u) r.m1 = 0;  // keeps pass 1 alive, never true
   return;
@@ -414,8 +442,11 @@ __device__ __forceinline__ void tc_tile(uint32_t (&p)[TC_HALF / 2], uint32_t col
     uint32_t q[8];
     switch (g) {    // warp-uniform jump: register arrays cannot be indexed dynamically
 #define TC_CASE(i) case i: _Pragma("unroll") for (int j = 0; j < 8; ++j) q[j] = p[8 * i + j]; break;
-      TC_CASE(0) TC_CASE(1) TC_CASE(2) TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6)
-      default: _Pragma("unroll") for (int j = 0; j < 8; ++j) q[j] = p[56 + j]; break;
+      TC_CASE(0) TC_CASE(1) TC_CASE(2)
+#if TC_WGS == 2
+      TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6)
+#endif
+      default: _Pragma("unroll") for (int j = 0; j < 8; ++j) q[j] = p[TC_NREG - 8 + j]; break;
 #undef TC_CASE
     }
     tc_group_exact_packed<K, MASKED>(q, col_base + g * TC_GROUP, nt, r);
@@ -483,8 +514,7 @@ __device__ __forceinline__ void tc_cols(const uint32_t (&p)[TC_HALF / 2], const 
     for (int j = 0; j < 8; ++j) s[j] = p[8 * g + j] + c[8 * g + j];
     gm[g] = __vimax3_s16x2(__vimax3_s16x2(s[0], s[1], s[2]), __vimax3_s16x2(s[3], s[4], s[5]), __vmaxs2(s[6], s[7]));
   }
-  const uint32_t all = __vimax3_s16x2(__vimax3_s16x2(gm[0], gm[1], gm[2]), __vimax3_s16x2(gm[3], gm[4], gm[5]),
-                                      __vimax3_s16x2(gm[6], gm[7], thrq));
+  const uint32_t all = tc_all_max(gm, thrq);
   if (!__any_sync(0xffffffffu, all != thrq)) return;
   uint32_t flags = 0;
 #pragma unroll
@@ -495,8 +525,11 @@ __device__ __forceinline__ void tc_cols(const uint32_t (&p)[TC_HALF / 2], const 
     uint32_t q[8], cc[8];
     switch (g) {
 #define TC_CASE(i) case i: _Pragma("unroll") for (int j = 0; j < 8; ++j) { q[j] = p[8 * i + j]; cc[j] = c[8 * i + j]; } break;
-      TC_CASE(0) TC_CASE(1) TC_CASE(2) TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6)
-      default: _Pragma("unroll") for (int j = 0; j < 8; ++j) { q[j] = p[56 + j]; cc[j] = c[56 + j]; } break;
+      TC_CASE(0) TC_CASE(1) TC_CASE(2)
+#if TC_WGS == 2
+      TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6)
+#endif
+      default: _Pragma("unroll") for (int j = 0; j < 8; ++j) { q[j] = p[TC_NREG - 8 + j]; cc[j] = c[TC_NREG - 8 + j]; } break;
 #undef TC_CASE
     }
     tc_col_group(q, cc, thrq, col_base + g * TC_GROUP, pq, row, col_key, col_thr);
@@ -553,9 +586,16 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
   r.tag = (item & 63u) << 10;
   r.heavy = (w.slot_src == nullptr);
   r.slack = 0;
-  const uint16_t* peer_slot = share + (wg ^ 1u) * TC_M + row_in_tile;
+  // the other warpgroups' slots of this row, and what was read there one and two tiles ago (none yet)
+  const uint16_t* peer_slot[TC_WGS - 1];
+  uint32_t pv1[TC_WGS - 1], pv2[TC_WGS - 1];
+#pragma unroll
+  for (int o = 0; o < TC_WGS - 1; ++o) {
+    peer_slot[o] = share + ((wg + 1u + o) % TC_WGS) * TC_M + row_in_tile;
+    pv1[o] = 0xFFFFFFFFu;
+    pv2[o] = 0xFFFFFFFFu;
+  }
   *r.my_slot = 0;
-  uint32_t pv1 = 0xFFFFFFFFu, pv2 = 0xFFFFFFFFu;   // peer values read one and two tiles ago (none yet)
   const bool cols = COL && w.col_key != nullptr;   // uniform per item
   const int rot = COL ? tc_rot_start(w, n_t) : 0;
   // packed (64 * pq - 32) of this lane's row for the column test; rows that do not exist never flag
@@ -573,12 +613,16 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
       r.slack = 1;
     }
     TC_PROF(const long long c_w = clock64();)
-    const uint32_t pv = *reinterpret_cast<const volatile uint16_t*>(peer_slot);
-    tc_peer_bound(r, pv, 1);
-    if (TC_PEER_AGED && !(COL && rot != 0)) {   // the aged form relies on tiles arriving in index order
-      tc_peer_bound(r, wg ? pv1 : pv2, 0);   // wg 1's columns follow wg 0's of the same tile: one tile suffices
-      pv2 = pv1;
-      pv1 = pv;
+#pragma unroll
+    for (int o = 0; o < TC_WGS - 1; ++o) {
+      const uint32_t pv = *reinterpret_cast<const volatile uint16_t*>(peer_slot[o]);
+      tc_peer_bound(r, pv, 1);
+      if (TC_PEER_AGED && !(COL && rot != 0)) {   // the aged form relies on tiles arriving in index order
+        // my columns follow those of a LOWER warpgroup of the same tile: for such a peer one tile suffices
+        tc_peer_bound(r, ((wg + 1u + o) % TC_WGS) < wg ? pv1[o] : pv2[o], 0);
+        pv2[o] = pv1[o];
+        pv1[o] = pv;
+      }
     }
     const uint32_t col_base = (uint32_t)te * TC_N + wg * TC_HALF;
     // column thresholds of this half tile: issued before the wait so that the L2 round trip hides
@@ -620,9 +664,25 @@ __device__ __forceinline__ void tc_epilogue_item(const TcWork& w, int q_tile, ui
             printf("epi warp %d item %u: total %lld  wait acc_full %lld  tile work %lld (pass 2 %lld)  flagged %lld of %d chunks\n",
                    warp, item, clock64() - p_t0, r.p_wait, r.p_pass1, r.p_pass2, r.p_nflag, n_t * (TC_HALF / 8));)
   // merge the two warpgroups' top-2 (disjoint train subsets) and write the row record
+#if TC_WGS == 2
   uint2* slot = merge + (item & 1u) * TC_M;
   if (wg == 1) slot[row_in_tile] = make_uint2(r.m1, r.m2);
   asm volatile("bar.sync 1, 256;" ::: "memory");
+#else
+  // a chain through ONE slot per row (shared memory is full): warpgroup s hands its best-2 to s - 1
+  for (uint32_t s = TC_WGS - 1; s >= 1; --s) {
+    if (wg == s) merge[row_in_tile] = make_uint2(r.m1, r.m2);
+    asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_THREADS) : "memory");
+    if (wg == s - 1 && s > 1) {
+      const uint2 o = merge[row_in_tile];
+      const uint32_t lo = min(r.m1, o.x);
+      r.m2 = min(max(r.m1, o.x), min(r.m2, o.y));
+      r.m1 = lo;
+    }
+    if (s > 1) asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_THREADS) : "memory");   // read before the slot is rewritten
+  }
+  const uint2* slot = merge;   // wg 0 reads what wg 1 left; the next item's first write is a whole item away
+#endif
   if (wg == 0) {
     const uint2 o = slot[row_in_tile];
     const uint32_t lo = min(r.m1, o.x);
@@ -657,7 +717,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + TC_ACC);
   static_assert((2 + 2 * TC_STAGES + 2 * TC_ACC) * 8 + 4 <= 256, "barrier block overflows its 256 bytes");
   uint2* merge = reinterpret_cast<uint2*>(tail + 256);                                        // [2][128]
-  uint16_t* share = reinterpret_cast<uint16_t*>(tail + 256 + 2 * TC_M * sizeof(uint2));       // [2][128]
+  uint16_t* share = reinterpret_cast<uint16_t*>(tail + 256 + TC_MERGE_BYTES);                 // [TC_WGS][128]
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -676,12 +736,12 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
     }
     for (int b = 0; b < TC_ACC; ++b) {
       mbar_init(&acc_full[b], 1);
-      mbar_init(&acc_empty[b], 8);  // one arrive per epilogue warp
+      mbar_init(&acc_empty[b], TC_EPI_WARPS);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
-  if (tid < 2 * TC_M) share[tid] = 0;
-  if (warp == 9) {  // TMEM: all 512 columns (TC_ACC accumulators of TC_N int32 columns)
+  if (tid < TC_WGS * TC_M) share[tid] = 0;
+  if (warp == TC_EPI_WARPS + 1) {  // TMEM: all 512 columns (TC_ACC accumulators of TC_N int32 columns)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
                      smem_u32(tmem_slot))
                  : "memory");
@@ -692,7 +752,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 8) {
+  if (warp == TC_EPI_WARPS) {
     // ===== TMA producer =====
     // Lane 0 runs the pipeline; the other lanes only help to GATHER the query tile of a sparse
     // item.
@@ -760,7 +820,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
       }
       __syncwarp();
     }
-  } else if (warp == 9) {
+  } else if (warp == TC_EPI_WARPS + 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
       uint32_t g = 0, item = 0;
@@ -798,7 +858,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
                                           clock64() - p_t0, p_a, p_b, p_acc, g);)
     }
 #if TC_PROFILE
-  } else if (warp == 10) {
+  } else if (warp == TC_EPI_WARPS + 2) {
     // ===== observer (profile builds): when does each accumulator complete, by position of the
     // train tile inside its work item?  hist[t] = sum over items of (F_t - F_{t-1}).
     if (lane == 0 && blockIdx.x == 0) {
@@ -837,7 +897,7 @@ hamming_tcgen05_kernel(const TcWork* __restrict__ work, int n_work, int total_ti
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) {
+  if (warp == TC_EPI_WARPS + 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
   }
