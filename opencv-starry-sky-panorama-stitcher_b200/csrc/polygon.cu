@@ -1210,6 +1210,7 @@ static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ss
     w.b_rows_pad = b.rows_pad;
     w.tile_begin = total;
     w.pair = p;
+    w.out_row = pp[(size_t)p].out_row;
     na2ptr[(size_t)p] = ctx->t_na2.as<double>() + a.row0;
     if (w.p1 > 0 && w.p2 > 0) total += (w.p1 + PT_M - 1) / PT_M;
   }
@@ -1228,7 +1229,8 @@ static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ss
   if ((e = ctx->t_pool.ensure((size_t)seg_cap * grid * sizeof(PtCand))) != cudaSuccess) return e;
   if ((e = ctx->t_sv.ensure((size_t)seg_cap * grid * 8)) != cudaSuccess) return e;
   if ((e = ctx->t_counts.ensure((size_t)grid * 4)) != cudaSuccess) return e;
-  if ((e = ctx->t_rowkey.ensure((size_t)(rows + 1) * 8)) != cudaSuccess) return e;
+  if ((e = ctx->t_rowkey.ensure((size_t)(rows + 1) * 12)) != cudaSuccess) return e;   // row keys, then the rows' final thetas
+  unsigned* row_theta = reinterpret_cast<unsigned*>(ctx->t_rowkey.as<unsigned long long>() + (rows + 1));
   if ((e = cudaMemsetAsync(ctx->t_counts.p, 0, (size_t)grid * 4, ctx->stream)) != cudaSuccess) return e;
 
   if ((e = cudaEventRecord(ctx->ev0, ctx->stream)) != cudaSuccess) return e;
@@ -1239,7 +1241,7 @@ static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ss
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
   }
   poly_cand_init_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, ctx->stream>>>(
-      ctx->t_rowkey.as<unsigned long long>(), ctx->p_argmin.as<int>(), rows);
+      ctx->t_rowkey.as<unsigned long long>(), ctx->p_argmin.as<int>(), row_theta, rows);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   if (total > 0) {
     if ((e = cudaFuncSetAttribute(poly_screen_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1247,13 +1249,13 @@ static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ss
       return e;
     poly_screen_tcgen05_kernel<<<grid, PT_THREADS, PT_SMEM_BYTES, ctx->stream>>>(
         ctx->t_work.as<PtWork>(), n_pairs, total, ctx->t_pool.as<PtCand>(), seg_cap, ctx->t_counts.as<unsigned>(),
-        ctx->t_flags.as<int>());
+        row_theta, ctx->t_flags.as<int>());
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     unsigned* stats = ctx->t_f.as<unsigned>() + imgs.size();
     poly_cand_eval_kernel<<<dim3(64, (unsigned)grid), 256, 0, ctx->stream>>>(
         ctx->p_pairs.as<PolyPair>(), ctx->t_work.as<PtWork>(), ctx->t_pool.as<PtCand>(), seg_cap,
         ctx->t_counts.as<unsigned>(), ctx->t_na2ptr.as<const double*>(), ctx->t_sv.as<double>(),
-        ctx->t_rowkey.as<unsigned long long>(), stats, ctx->t_flags.as<int>(), ctx->p_flops.as<unsigned long long>());
+        ctx->t_rowkey.as<unsigned long long>(), row_theta, stats, ctx->t_flags.as<int>(), ctx->p_flops.as<unsigned long long>());
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     poly_cand_argmin_kernel<<<dim3(64, (unsigned)grid), 256, 0, ctx->stream>>>(
         ctx->p_pairs.as<PolyPair>(), ctx->t_pool.as<PtCand>(), seg_cap, ctx->t_counts.as<unsigned>(),

@@ -22,7 +22,9 @@
 // segment of a global pool.  The four threads of a row exchange theta through shared memory.  Expected
 // candidates per row: the records of a random sequence, ~ln(P2) + a few.
 //
-// Exact part.  poly_cand_eval_kernel evaluates every candidate with poly_dist2_f64<0> and takes the row
+// Exact part.  poly_cand_eval_kernel evaluates every candidate whose D lies below the row's FINAL theta (the
+// threads leave it in a per-row word at the end of an item; what was taken while theta was still loose and
+// lies at or above it is ruled out like a column never taken) with poly_dist2_f64<0> and takes the row
 // minimum of sqrt(v) (atomicMin on the bits of a non-negative double); poly_cand_argmin_kernel gives the row
 // the LOWEST column among the candidates that reach that minimum -- numpy's argmin; rows without a finite
 // candidate keep (0, inf) like the per-lane kernel.
@@ -86,6 +88,7 @@ struct PtWork {          // one image pair
   const uint8_t* b_exp;
   const float* f_a;
   const float* f_b;
+  long long out_row;     // first row of the pair in the per-row outputs
   int p1, p2;
   int a_rows_pad, b_rows_pad;
   int tile_begin;        // prefix sum of row tiles over the work list
@@ -95,6 +98,15 @@ struct __align__(16) PtCand {
   int pair, row, col;
   float d;
 };
+
+// order-preserving map float -> unsigned (for atomicMin on values of either sign) and back
+__device__ __forceinline__ unsigned pt_ordered(float x) {
+  const unsigned b = __float_as_uint(x);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float pt_unordered(unsigned k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
+}
 
 __device__ __forceinline__ uint32_t pt_tf32(float x) {
   uint32_t r;
@@ -241,7 +253,7 @@ __device__ __forceinline__ void pt_chunk(const uint32_t (&v)[PT_HALF], float& th
 __global__ void __launch_bounds__(PT_THREADS, 1)
 poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int total_tiles,
                            PtCand* __restrict__ pool, unsigned seg_cap, unsigned* __restrict__ cand_counts,
-                           int* __restrict__ flags) {
+                           unsigned* __restrict__ row_theta, int* __restrict__ flags) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + PT_A_BYTES;
@@ -402,6 +414,9 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
         if (__uint_as_float(v[0]) == 12345.678f && __uint_as_float(v[PT_HALF - 1]) == 1.0f) *my_slot = (float)col0;   // keeps the loads alive
 #endif
       }
+      // The row's FINAL theta (the smallest over its threads) for the exact part: a candidate taken early,
+      // with D at or above it, is ruled out like a column that was never taken and needs no FP64 evaluation.
+      if (row < w.p1) atomicMin(&row_theta[w.out_row + row], pt_ordered(theta));
       // every thread resets its slot between two meetings of the warpgroups, so that none of them reads a
       // theta of the previous row there
       asm volatile("bar.sync 1, %0;" ::"n"(32 * PT_EPI_WARPS) : "memory");
@@ -423,11 +438,13 @@ poly_screen_tcgen05_kernel(const PtWork* __restrict__ work, int n_work, int tota
 constexpr unsigned long long PT_KEY_NONE = 0x7FF0000000000000ull;   // +inf
 
 __global__ void __launch_bounds__(256)
-poly_cand_init_kernel(unsigned long long* __restrict__ row_key, int* __restrict__ argmin, long long rows) {
+poly_cand_init_kernel(unsigned long long* __restrict__ row_key, int* __restrict__ argmin,
+                      unsigned* __restrict__ row_theta, long long rows) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < rows) {
     row_key[i] = PT_KEY_NONE;
     argmin[i] = 0x7FFFFFFF;
+    row_theta[i] = 0xFFFFFFFFu;
   }
 }
 
@@ -436,7 +453,8 @@ __global__ void __launch_bounds__(256)
 poly_cand_eval_kernel(const PolyPair* __restrict__ pairs, const PtWork* __restrict__ work,
                       const PtCand* __restrict__ pool, unsigned seg_cap, const unsigned* __restrict__ cand_counts,
                       const double* const* __restrict__ na2_of_pair, double* __restrict__ pool_sv,
-                      unsigned long long* __restrict__ row_key, unsigned* __restrict__ stats,
+                      unsigned long long* __restrict__ row_key, const unsigned* __restrict__ row_theta,
+                      unsigned* __restrict__ stats,
                       int* __restrict__ flags, unsigned long long* __restrict__ executed_flops) {
   const unsigned seg = blockIdx.y;
   const unsigned n = cand_counts[seg];
@@ -446,6 +464,12 @@ poly_cand_eval_kernel(const PolyPair* __restrict__ pairs, const PtWork* __restri
     const size_t at = (size_t)seg * seg_cap + i;
     const PtCand c = pool[at];
     const PolyPair pp = pairs[c.pair];
+    // taken while the row's threshold was still loose and ruled out by where it ended (a candidate whose D the
+    // screen did not keep -- NaN -- is always evaluated)
+    if (c.d >= pt_unordered(row_theta[pp.out_row + c.row])) {
+      pool_sv[at] = INFINITY;
+      continue;
+    }
     double a[15];
 #pragma unroll
     for (int k = 0; k < 15; ++k) a[k] = pp.f1[(long long)c.row * 15 + k];
