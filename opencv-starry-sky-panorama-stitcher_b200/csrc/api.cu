@@ -85,7 +85,7 @@ int ssp_destroy(ssp_ctx* ctx) {
                          &ctx->p_md,       &ctx->p_flops,     &ctx->b_img,       &ctx->b_xy,        &ctx->b_disc,
                          &ctx->b_out,      &ctx->c_mask,      &ctx->c_work,      &ctx->c_blocks,    &ctx->c_cand,
                          &ctx->r_pairs,    &ctx->r_kp,        &ctx->r_out,
-                         &ctx->t_bank, &ctx->t_na2, &ctx->t_f, &ctx->t_imgs, &ctx->t_work, &ctx->t_na2ptr, &ctx->t_pool, &ctx->t_sv,
+                         &ctx->t_bank, &ctx->t_na2, &ctx->t_f, &ctx->t_imgs, &ctx->t_work, &ctx->t_na2ptr, &ctx->t_pool, &ctx->t_sv, &ctx->t_keep,
                          &ctx->t_counts, &ctx->t_rowkey, &ctx->t_flags};
   for (ssp::DevBuf* b : bufs) b->release();
   for (ssp::PolyImage& pi : ctx->poly) {

@@ -154,7 +154,7 @@ struct ssp_ctx {
   ssp::DevBuf p_pairs, p_argmin, p_mindist, p_counts, p_offsets, p_m1, p_m2, p_md, p_flops;
   // tensor-core screen of kernel 3 (polygon_tensor.cuh): operand banks, |a|^2 table, F per image, tables,
   // candidate pool (+ sqrt values), per-CTA counts, row keys, flags + stats
-  ssp::DevBuf t_bank, t_na2, t_f, t_imgs, t_work, t_na2ptr, t_pool, t_sv, t_counts, t_rowkey, t_flags;
+  ssp::DevBuf t_bank, t_na2, t_f, t_imgs, t_work, t_na2ptr, t_pool, t_sv, t_keep, t_counts, t_rowkey, t_flags;
   long long t_stats_off = 0;    // statistics word behind the F table
   int t_grid = 0;
   int t_used = 0;               // the last ssp_polygon_match_pairs call ran the tensor-core screen

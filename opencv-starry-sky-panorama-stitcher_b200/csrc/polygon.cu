@@ -1185,9 +1185,9 @@ static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ss
   if ((e = ctx->t_na2.ensure((size_t)(n_rows + 1) * 8)) != cudaSuccess) return e;
   if ((e = ctx->t_f.ensure(imgs.size() * 4 + 16)) != cudaSuccess) return e;   // + statistics word behind the table
   if ((e = ctx->t_imgs.ensure(imgs.size() * sizeof(PtBankImg))) != cudaSuccess) return e;
-  if ((e = ctx->t_flags.ensure(sizeof(int))) != cudaSuccess) return e;
+  if ((e = ctx->t_flags.ensure(2 * sizeof(int))) != cudaSuccess) return e;   // flags, number of kept candidates
   if ((e = cudaMemsetAsync(ctx->t_f.p, 0, imgs.size() * 4 + 16, ctx->stream)) != cudaSuccess) return e;
-  if ((e = cudaMemsetAsync(ctx->t_flags.p, 0, sizeof(int), ctx->stream)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(ctx->t_flags.p, 0, 2 * sizeof(int), ctx->stream)) != cudaSuccess) return e;
   // pageable sources: the runtime stages them before returning
   if ((e = cudaMemcpyAsync(ctx->t_imgs.p, imgs.data(), imgs.size() * sizeof(PtBankImg), cudaMemcpyHostToDevice,
                            ctx->stream)) != cudaSuccess)
@@ -1224,10 +1224,13 @@ static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ss
     return e;
   const int grid = total < ctx->sm_count ? (total > 0 ? total : 1) : ctx->sm_count;
   // candidate pool: ~ln(P2) + a few per row are expected; 24 per row and a floor per CTA, split evenly
-  const unsigned long long pool_total = 24ull * (unsigned long long)rows + 8192ull * (unsigned)grid;
+  // (pool positions are 32-bit: a call beyond that simply overflows the pool and goes to the CUDA-core kernels)
+  const unsigned long long pool_want = 24ull * (unsigned long long)rows + 8192ull * (unsigned)grid;
+  const unsigned long long pool_total = pool_want < 0xF0000000ull ? pool_want : 0xF0000000ull;
   const unsigned seg_cap = (unsigned)(pool_total / (unsigned)grid);
   if ((e = ctx->t_pool.ensure((size_t)seg_cap * grid * sizeof(PtCand))) != cudaSuccess) return e;
   if ((e = ctx->t_sv.ensure((size_t)seg_cap * grid * 8)) != cudaSuccess) return e;
+  if ((e = ctx->t_keep.ensure((size_t)seg_cap * grid * 4)) != cudaSuccess) return e;   // worst case: every candidate kept
   if ((e = ctx->t_counts.ensure((size_t)grid * 4)) != cudaSuccess) return e;
   if ((e = ctx->t_rowkey.ensure((size_t)(rows + 1) * 12)) != cudaSuccess) return e;   // row keys, then the rows' final thetas
   unsigned* row_theta = reinterpret_cast<unsigned*>(ctx->t_rowkey.as<unsigned long long>() + (rows + 1));
@@ -1252,13 +1255,19 @@ static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ss
         row_theta, ctx->t_flags.as<int>());
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     unsigned* stats = ctx->t_f.as<unsigned>() + imgs.size();
-    poly_cand_eval_kernel<<<dim3(64, (unsigned)grid), 256, 0, ctx->stream>>>(
-        ctx->p_pairs.as<PolyPair>(), ctx->t_work.as<PtWork>(), ctx->t_pool.as<PtCand>(), seg_cap,
-        ctx->t_counts.as<unsigned>(), ctx->t_na2ptr.as<const double*>(), ctx->t_sv.as<double>(),
-        ctx->t_rowkey.as<unsigned long long>(), row_theta, stats, ctx->t_flags.as<int>(), ctx->p_flops.as<unsigned long long>());
+    unsigned* n_keep = ctx->t_flags.as<unsigned>() + 1;
+    poly_cand_filter_kernel<<<dim3(64, (unsigned)grid), 256, 0, ctx->stream>>>(
+        ctx->p_pairs.as<PolyPair>(), ctx->t_pool.as<PtCand>(), seg_cap, ctx->t_counts.as<unsigned>(), row_theta,
+        ctx->t_keep.as<unsigned>(), n_keep);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    poly_cand_argmin_kernel<<<dim3(64, (unsigned)grid), 256, 0, ctx->stream>>>(
-        ctx->p_pairs.as<PolyPair>(), ctx->t_pool.as<PtCand>(), seg_cap, ctx->t_counts.as<unsigned>(),
+    const unsigned dense_grid = (unsigned)ctx->sm_count * 8u;
+    poly_cand_eval_kernel<<<dense_grid, 256, 0, ctx->stream>>>(
+        ctx->p_pairs.as<PolyPair>(), ctx->t_work.as<PtWork>(), ctx->t_pool.as<PtCand>(), ctx->t_keep.as<unsigned>(),
+        n_keep, ctx->t_na2ptr.as<const double*>(), ctx->t_sv.as<double>(), ctx->t_rowkey.as<unsigned long long>(),
+        stats, ctx->t_flags.as<int>(), ctx->p_flops.as<unsigned long long>());
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    poly_cand_argmin_kernel<<<dense_grid, 256, 0, ctx->stream>>>(
+        ctx->p_pairs.as<PolyPair>(), ctx->t_pool.as<PtCand>(), ctx->t_keep.as<unsigned>(), n_keep,
         ctx->t_sv.as<double>(), ctx->t_rowkey.as<unsigned long long>(), ctx->p_argmin.as<int>());
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
   }
@@ -1266,7 +1275,7 @@ static cudaError_t launch_poly_compare_tensor(ssp_ctx* ctx, const std::vector<ss
       ctx->t_rowkey.as<unsigned long long>(), ctx->p_argmin.as<int>(), ctx->p_mindist.as<double>(), rows);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   if ((e = cudaEventRecord(ctx->ev1, ctx->stream)) != cudaSuccess) return e;
-  ctx->p_launches += total > 0 ? 6 : 3;
+  ctx->p_launches += total > 0 ? 7 : 3;
   ctx->t_stats_off = (long long)imgs.size();
   ctx->t_grid = grid;
   return cudaSuccess;

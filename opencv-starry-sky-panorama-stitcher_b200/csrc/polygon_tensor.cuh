@@ -22,7 +22,7 @@
 // segment of a global pool.  The four threads of a row exchange theta through shared memory.  Expected
 // candidates per row: the records of a random sequence, ~ln(P2) + a few.
 //
-// Exact part.  poly_cand_eval_kernel evaluates every candidate whose D lies below the row's FINAL theta (the
+// Exact part.  poly_cand_filter_kernel + poly_cand_eval_kernel evaluate every candidate whose D lies below the row's FINAL theta (the
 // threads leave it in a per-row word at the end of an item; what was taken while theta was still loose and
 // lies at or above it is ruled out like a column never taken) with poly_dist2_f64<0> and takes the row
 // minimum of sqrt(v) (atomicMin on the bits of a non-negative double); poly_cand_argmin_kernel gives the row
@@ -448,28 +448,51 @@ poly_cand_init_kernel(unsigned long long* __restrict__ row_key, int* __restrict_
   }
 }
 
-// one thread per candidate slot of every CTA segment; stats[0] = max abs(|a|^2 + D - v) as float bits
+// Which candidates need the FP64 evaluation: those whose D lies below the row's final theta (a candidate whose D
+// the screen did not keep -- NaN -- always does).  Their pool positions go to a dense list (one atomicAdd per
+// warp), so that the evaluation below runs with full warps: at C4 nine of ten candidates are ruled out, and a
+// warp that evaluates one lane in eight costs as much as a full one.
 __global__ void __launch_bounds__(256)
-poly_cand_eval_kernel(const PolyPair* __restrict__ pairs, const PtWork* __restrict__ work,
-                      const PtCand* __restrict__ pool, unsigned seg_cap, const unsigned* __restrict__ cand_counts,
-                      const double* const* __restrict__ na2_of_pair, double* __restrict__ pool_sv,
-                      unsigned long long* __restrict__ row_key, const unsigned* __restrict__ row_theta,
-                      unsigned* __restrict__ stats,
-                      int* __restrict__ flags, unsigned long long* __restrict__ executed_flops) {
+poly_cand_filter_kernel(const PolyPair* __restrict__ pairs, const PtCand* __restrict__ pool, unsigned seg_cap,
+                        const unsigned* __restrict__ cand_counts, const unsigned* __restrict__ row_theta,
+                        unsigned* __restrict__ keep, unsigned* __restrict__ n_keep) {
+  constexpr unsigned FULL = 0xffffffffu;
   const unsigned seg = blockIdx.y;
   const unsigned n = cand_counts[seg];
+  const int lane = threadIdx.x & 31;
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n; i0 += stride) {   // warp-uniform
+    const unsigned i = i0 + lane;
+    bool kept = false;
+    unsigned at = 0;
+    if (i < n) {
+      at = seg * seg_cap + i;
+      const PtCand c = pool[at];
+      kept = !(c.d >= pt_unordered(row_theta[pairs[c.pair].out_row + c.row]));
+    }
+    const unsigned m = __ballot_sync(FULL, kept);
+    if (m == 0u) continue;
+    unsigned base = 0u;
+    if (lane == 0) base = atomicAdd(n_keep, (unsigned)__popc(m));
+    base = __shfl_sync(FULL, base, 0);
+    if (kept) keep[base + __popc(m & ((1u << lane) - 1u))] = at;
+  }
+}
+
+// one thread per KEPT candidate; stats[0] = max abs(|a|^2 + D - v) / F^2 as float bits
+__global__ void __launch_bounds__(256)
+poly_cand_eval_kernel(const PolyPair* __restrict__ pairs, const PtWork* __restrict__ work,
+                      const PtCand* __restrict__ pool, const unsigned* __restrict__ keep,
+                      const unsigned* __restrict__ n_keep, const double* const* __restrict__ na2_of_pair,
+                      double* __restrict__ keep_sv, unsigned long long* __restrict__ row_key,
+                      unsigned* __restrict__ stats, int* __restrict__ flags,
+                      unsigned long long* __restrict__ executed_flops) {
+  const unsigned n = *n_keep;
   unsigned evaluated = 0;
   float worst = 0.0f;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const size_t at = (size_t)seg * seg_cap + i;
-    const PtCand c = pool[at];
+    const PtCand c = pool[keep[i]];
     const PolyPair pp = pairs[c.pair];
-    // taken while the row's threshold was still loose and ruled out by where it ended (a candidate whose D the
-    // screen did not keep -- NaN -- is always evaluated)
-    if (c.d >= pt_unordered(row_theta[pp.out_row + c.row])) {
-      pool_sv[at] = INFINITY;
-      continue;
-    }
     double a[15];
 #pragma unroll
     for (int k = 0; k < 15; ++k) a[k] = pp.f1[(long long)c.row * 15 + k];
@@ -480,11 +503,11 @@ poly_cand_eval_kernel(const PolyPair* __restrict__ pairs, const PtWork* __restri
     const float f = fmaxf(*w.f_a, *w.f_b);
     const double e = (double)PT_ERR_COEF * (double)f * (double)f;
     const double diff = fabs(s_screen - v);
-    if (diff > e) atomicOr(flags, PT_FLAG_ERROR);            // NaN differences (NaN features) are not errors
+    if (diff > e) atomicOr(flags, PT_FLAG_ERROR);            // NaN differences (NaN features, D not kept) are not errors
     if (f > 0.0f) worst = fmaxf(worst, __double2float_ru(diff / ((double)f * (double)f)));
     const double sv = sqrt(v);
     const bool valid = v < INFINITY;                           // what `v < thr` admits from thr = inf on
-    pool_sv[at] = valid ? sv : INFINITY;
+    keep_sv[i] = valid ? sv : INFINITY;
     if (valid) atomicMin(&row_key[pp.out_row + c.row], (unsigned long long)__double_as_longlong(sv));
   }
   worst = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(worst)));
@@ -496,17 +519,17 @@ poly_cand_eval_kernel(const PolyPair* __restrict__ pairs, const PtWork* __restri
 }
 
 __global__ void __launch_bounds__(256)
-poly_cand_argmin_kernel(const PolyPair* __restrict__ pairs, const PtCand* __restrict__ pool, unsigned seg_cap,
-                        const unsigned* __restrict__ cand_counts, const double* __restrict__ pool_sv,
-                        const unsigned long long* __restrict__ row_key, int* __restrict__ argmin) {
-  const unsigned seg = blockIdx.y;
-  const unsigned n = cand_counts[seg];
+poly_cand_argmin_kernel(const PolyPair* __restrict__ pairs, const PtCand* __restrict__ pool,
+                        const unsigned* __restrict__ keep, const unsigned* __restrict__ n_keep,
+                        const double* __restrict__ keep_sv, const unsigned long long* __restrict__ row_key,
+                        int* __restrict__ argmin) {
+  const unsigned n = *n_keep;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const size_t at = (size_t)seg * seg_cap + i;
-    const PtCand c = pool[at];
-    const double sv = pool_sv[at];
+    const double sv = keep_sv[i];
+    if (!(sv < INFINITY)) continue;
+    const PtCand c = pool[keep[i]];
     const long long r = pairs[c.pair].out_row + c.row;
-    if (sv < INFINITY && (unsigned long long)__double_as_longlong(sv) == row_key[r]) atomicMin(&argmin[r], c.col);
+    if ((unsigned long long)__double_as_longlong(sv) == row_key[r]) atomicMin(&argmin[r], c.col);
   }
 }
 
